@@ -1,0 +1,216 @@
+"""Generate tests/golden/*.npz from the REAL reference (TEST INFRASTRUCTURE).
+
+Run in the build container only (needs /root/reference):
+
+    python -m oracle.make_golden
+
+Every fixture is produced by the unmodified reference classes imported through
+oracle/ref_loader.py; the only interventions are the documented RNG patches
+(np.random.dirichlet -> supplied noise, random.choice -> stream-indexed pick)
+and table/recording network objects standing in for `muzero_net`.
+
+Fixtures
+  nets_N{n}_C{c}.npz   reference MuZeroNet (main.py:127-142) outputs on fixed inputs
+  mcts_*.npz           reference MCTS visit counts with injected network outputs
+"""
+import os
+import random
+import sys
+
+import numpy as np
+import torch
+
+from . import gymgo, ref_loader
+
+OUT = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden")
+
+
+def midgame_obs(n, plies, seed):
+    rng = np.random.default_rng(seed)
+    st = gymgo.init_state(n)
+    for _ in range(plies):
+        if gymgo.game_ended(st):
+            break
+        v = np.nonzero(gymgo.valid_moves(st))[0]
+        a = int(v[rng.integers(len(v) - 1)]) if len(v) > 1 else int(v[0])
+        st = gymgo.next_state(st, a)
+    return st
+
+
+# --------------------------------------------------------------------------- nets
+def make_nets(n, c, batch, seed):
+    main = ref_loader.configure(ref_loader.load("main"), n)
+    A = n * n + 1
+    torch.manual_seed(seed)
+    net = main.MuZeroNet(c, A).eval()
+    # move biases / pass_logit / fc weights off their degenerate init so every term is exercised
+    with torch.no_grad():
+        net.prediction.pass_logit.fill_(0.37)
+    obs = np.stack([midgame_obs(n, 5 + 7 * i, seed + i) for i in range(batch)]).astype(np.float32)
+    rng = np.random.default_rng(seed)
+    actions = rng.integers(0, A, size=batch).astype(np.int64)
+    actions[0] = A - 1            # pass
+    actions[-1] = 0               # corner
+    with torch.no_grad():
+        latent, value, logits = net.initial_inference(torch.from_numpy(obs))
+        nxt, reward, value2, logits2 = net.recurrent_inference(latent, torch.from_numpy(actions))
+        nxt2, reward3, value3, logits3 = net.recurrent_inference(nxt, torch.from_numpy(actions[::-1].copy()))
+    sd = net.state_dict()
+    checksum = float(sum(v.double().sum() for v in sd.values()))
+    abs_checksum = float(sum(v.double().abs().sum() for v in sd.values()))
+    np.savez_compressed(
+        os.path.join(OUT, f"nets_N{n}_C{c}.npz"),
+        n=n, c=c, seed=seed, pass_logit=0.37, obs=obs, actions=actions,
+        weight_sum=checksum, weight_abs_sum=abs_checksum,
+        latent=latent.numpy(), value=value.numpy(), logits=logits.numpy(),
+        next_latent=nxt.numpy(), reward=reward.numpy(), value2=value2.numpy(), logits2=logits2.numpy(),
+        reward3=reward3.numpy(), value3=value3.numpy(), logits3=logits3.numpy(),
+        next_latent2_sum=float(nxt2.double().sum()))
+    print("nets", n, c, "weights", checksum)
+
+
+# --------------------------------------------------------------------------- mcts
+class TableNet:
+    """Stands in for `muzero_net`: returns pre-drawn outputs by call index."""
+
+    def __init__(self, init_logits, logits, rewards, values):
+        self.init_logits = torch.from_numpy(init_logits).view(1, -1)
+        self.logits = torch.from_numpy(logits)
+        self.rewards = torch.from_numpy(rewards)
+        self.values = torch.from_numpy(values)
+        self.calls = 0
+
+    def eval(self):
+        return self
+
+    def initial_inference(self, obs):
+        return torch.zeros(1, 1), torch.zeros(1, 1), self.init_logits
+
+    def recurrent_inference(self, latent, action):
+        i = self.calls
+        self.calls += 1
+        return torch.zeros(1, 1), self.rewards[i].view(1, 1), self.values[i].view(1, 1), self.logits[i:i + 1]
+
+
+class RecordingNet:
+    """Wraps a real reference net and records what the search consumed."""
+
+    def __init__(self, net):
+        self.net = net
+        self.logits, self.rewards, self.values = [], [], []
+        self.init_logits = None
+
+    def eval(self):
+        self.net.eval()
+        return self
+
+    def initial_inference(self, obs):
+        latent, value, logits = self.net.initial_inference(obs)
+        self.init_logits = logits.detach().numpy()[0].copy()
+        return latent, value, logits
+
+    def recurrent_inference(self, latent, action):
+        out = self.net.recurrent_inference(latent, action)
+        self.rewards.append(np.float32(out[1].item()))
+        self.values.append(np.float32(out[2].item()))
+        self.logits.append(out[3].detach().numpy()[0].copy())
+        return out
+
+
+def run_reference_mcts(modname, n, sims, obs, net, noise, stream, c_puct=None):
+    mod = ref_loader.configure(ref_loader.load(modname), n)
+    A = n * n + 1
+    trace_a, trace_d = [], []
+    calls = [0]
+
+    def fake_choice(seq):
+        k = int(stream[calls[0]]) % len(seq)
+        calls[0] += 1
+        return seq[k]
+
+    old_dir, old_choice = np.random.dirichlet, random.choice
+    np.random.dirichlet = lambda alpha: np.array(noise, dtype=np.float64)
+    random.choice = fake_choice
+    try:
+        mcts = mod.MCTS(net, A, sims) if c_puct is None else mod.MCTS(net, A, sims, c_puct=c_puct)
+        orig_select = mcts.select_leaf
+
+        def traced(*args):
+            path, action = orig_select(*args)
+            trace_a.append(-1 if action is None else action)
+            trace_d.append(len(path))
+            return path, action
+        mcts.select_leaf = traced
+        with torch.no_grad():
+            out = mcts.run(obs)
+    finally:
+        np.random.dirichlet, random.choice = old_dir, old_choice
+    root = out[0] if isinstance(out, tuple) else out
+    visit = np.array([ch['node'].visit_count if ch['node'] is not None else 0 for ch in root.children.values()],
+                     dtype=np.int64)
+    vsum = np.array([float(ch['node'].value_sum) if ch['node'] is not None else 0.0
+                     for ch in root.children.values()], dtype=np.float64)
+    priors = np.array([float(ch['prior']) for ch in root.children.values()], dtype=np.float64)
+    cfg = mod.config
+    return dict(visit=visit, child_value_sum=vsum, root_prior=priors, root_visit=root.visit_count,
+                root_value_sum=float(root.value_sum), sel_action=np.array(trace_a, dtype=np.int32),
+                sel_depth=np.array(trace_d, dtype=np.int32), c_puct=float(mcts.c_puct),
+                c_puct_is_int=isinstance(mcts.c_puct, int), discount=cfg.discount,
+                dirichlet_epsilon=cfg.dirichlet_epsilon, pass_epsilon=cfg.pass_epsilon)
+
+
+def make_mcts(tag, modname, n, sims, seed, mode, plies, c=16, c_puct=None):
+    A = n * n + 1
+    rng = np.random.default_rng(seed)
+    obs = midgame_obs(n, plies, seed)
+    noise = rng.dirichlet([0.3] * A)
+    stream = rng.integers(0, 2 ** 32, size=sims + 8, dtype=np.uint64).astype(np.uint32)
+    if mode == "table":
+        init_logits = rng.normal(0, 1.5, A).astype(np.float32)
+        logits = rng.normal(0, 2.0, (sims, A)).astype(np.float32)
+        rewards = rng.normal(0, 0.1, sims).astype(np.float32)
+        values = rng.normal(0, 0.5, sims).astype(np.float32)
+        net = TableNet(init_logits, logits, rewards, values)
+        res = run_reference_mcts(modname, n, sims, obs, net, noise, stream, c_puct)
+    else:  # a real random-init reference net, outputs recorded
+        mod = ref_loader.configure(ref_loader.load(modname), n)
+        torch.manual_seed(seed)
+        real = mod.MuZeroNet(c, A).eval()
+        with torch.no_grad():   # spread the outputs a little so the tree goes deep
+            real.prediction.policy_conv.weight.mul_(8.0)
+            real.prediction.value_fc.weight.fill_(3.0)
+        net = RecordingNet(real)
+        res = run_reference_mcts(modname, n, sims, obs, net, noise, stream, c_puct)
+        init_logits = net.init_logits.astype(np.float32)
+        logits = np.stack(net.logits).astype(np.float32)
+        rewards = np.array(net.rewards, dtype=np.float32)
+        values = np.array(net.values, dtype=np.float32)
+    # the injection boundary: post-softmax float32 priors, computed exactly like main.py:259/:298
+    init_soft = torch.softmax(torch.from_numpy(init_logits).view(1, -1), dim=1).numpy()[0]
+    soft = np.stack([torch.softmax(torch.from_numpy(l).view(1, -1), dim=1).numpy()[0] for l in logits])
+    np.savez_compressed(os.path.join(OUT, f"mcts_{tag}.npz"), variant=modname, n=n, sims=sims, obs=obs,
+                        noise=noise, stream=stream, init_soft=init_soft, soft=soft, rewards=rewards,
+                        values=values, **res)
+    print("mcts", tag, "root_visit", res["root_visit"], "max child", res["visit"].max(),
+          "depth hist", np.bincount(res["sel_depth"]))
+
+
+def main():
+    if not ref_loader.available():
+        sys.exit("reference not available here")
+    os.makedirs(OUT, exist_ok=True)
+    make_nets(9, 128, 4, seed=0)
+    make_nets(19, 128, 2, seed=1)
+    make_nets(6, 32, 3, seed=2)
+    make_mcts("main_N9_S50_table", "main", 9, 50, seed=10, mode="table", plies=12)
+    make_mcts("main_N9_S800_table", "main", 9, 800, seed=11, mode="table", plies=30)
+    make_mcts("main_N9_S400_net", "main", 9, 400, seed=12, mode="net", plies=8)
+    make_mcts("main_N6_S256_table", "main", 6, 256, seed=13, mode="table", plies=6)
+    make_mcts("main_N19_S800_table", "main", 19, 800, seed=14, mode="table", plies=150)
+    make_mcts("main_N5_S300_endgame", "main", 5, 300, seed=15, mode="table", plies=40)
+    make_mcts("play_N9_S300_table", "play", 9, 300, seed=16, mode="table", plies=20)
+    make_mcts("selfplay_N9_S300_table", "self_play", 9, 300, seed=17, mode="table", plies=20)
+
+
+if __name__ == "__main__":
+    main()
