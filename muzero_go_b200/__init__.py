@@ -1,0 +1,16 @@
+"""B200-native MuZero-Go self-play hot path (drop-in for Sir-Teo/MuZero-Go's MCTS / networks / GymGo surface).
+
+Everything that computes goes through libmzgo.so (hand-written sm_100a CUDA behind the C ABI of
+include/mzgo.h).  There is no CPU fallback.
+"""
+from . import _lib
+from ._lib import MzgoError
+from .rules import GoBoards, GoEnv, govars, make
+from .tree import SearchConfig, Tree
+from .networks import MuZeroNet
+from .mcts import MCTS, MCTSNode
+from .agent import MuZeroAgent
+from .selfplay import SelfPlayEngine
+
+__all__ = ["MzgoError", "GoBoards", "GoEnv", "govars", "make", "SearchConfig", "Tree", "MuZeroNet", "MCTS",
+           "MCTSNode", "MuZeroAgent", "SelfPlayEngine"]

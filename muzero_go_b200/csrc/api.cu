@@ -1,0 +1,37 @@
+// Error plumbing, ABI version, device probe and launch accounting for libmzgo.so.
+#include "common.cuh"
+
+static thread_local char g_err[512] = "";
+static thread_local int64_t g_launches = 0;
+
+void mzgo_set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+void mzgo_count_launch() { g_launches++; }
+void mzgo_count_launches(int k) { g_launches += k; }
+
+extern "C" const char* mzgo_last_error(void) { return g_err; }
+
+extern "C" int mzgo_abi_version(void) { return MZGO_ABI_VERSION; }
+
+extern "C" int mzgo_device_ok(void) {
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) {
+        cudaGetLastError();
+        return 0;
+    }
+    int dev = 0, major = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+    if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev) != cudaSuccess) return 0;
+    return major == 10;
+}
+
+extern "C" int64_t mzgo_launch_count(int reset) {
+    int64_t v = g_launches;
+    if (reset) g_launches = 0;
+    return v;
+}

@@ -1,0 +1,148 @@
+// Batched self-play driver: G games in lock step, launches only (no host synchronisation).
+//
+// Replaces the per-move body of /root/reference/main.py:656-702 (MCTS(...).run(obs), visit-count action
+// choice, env.step, trajectory append, two-pass / move-cap termination) and the game epilogue
+// main.py:703-711.  The host loop below only enqueues kernels; per simulation it enqueues
+// select -> recurrent inference -> expand/backup for the whole batch of games.
+#include "nets.cuh"
+
+namespace {
+
+constexpr int SP_THREADS = 128;
+
+// Start of a move: retire / restart finished games, set the per-game sampling temperature.
+__global__ void k_sp_begin_move(mzgo_selfplay_t sp) {
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= sp.tree.G) return;
+    uint32_t* rec = sp.boards + (size_t)g * MZGO_BOARD_WORDS;
+    bool over = ((rec[61] >> 1) & 1u) || sp.pass_streak[g] >= 2 || sp.move_count[g] >= sp.max_game_moves;
+    if (over && sp.restart_finished) {
+        for (int w = 0; w < MZGO_BOARD_WORDS; w++) rec[w] = 0u;   // GoEnv.reset, main.py:637
+        sp.move_count[g] = 0;
+        sp.pass_streak[g] = 0;
+        over = false;
+    }
+    sp.tree.active[g] = over ? 0 : 1;
+    sp.out_slot[g] = over ? -1 : g * sp.tree.M;   // the root latent lives in slot (g, node 0)
+    sp.game_temperature[g] = (sp.move_count[g] < sp.temperature_moves) ? sp.temperature : 0.f;
+}
+
+// After env.step: bookkeeping of main.py:690-711 and the trajectory row of this move.
+__global__ void k_sp_end_move(mzgo_selfplay_t sp, int t) {
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;
+    const int G = sp.tree.G;
+    if (g >= G) return;
+    const size_t row = (size_t)t * G + g;
+    if (!sp.tree.active[g]) {
+        sp.traj_action[row] = -1;
+        sp.traj_reward[row] = 0.f;
+        sp.traj_done[row] = 0;
+        sp.traj_winner[row] = 0;
+        return;
+    }
+    const int a = sp.action[g];
+    const uint32_t* rec = sp.boards + (size_t)g * MZGO_BOARD_WORDS;
+    const int pass_action = sp.n * sp.n;
+    const bool env_done = (rec[61] >> 1) & 1u;
+    int mc = sp.move_count[g] + 1;
+    int ps = (a == pass_action) ? sp.pass_streak[g] + 1 : 0;
+    sp.move_count[g] = mc;
+    sp.pass_streak[g] = ps;
+    const bool done = env_done || ps >= 2;
+    const bool capped = !done && mc >= sp.max_game_moves;
+    // GymGo reward_method='real': winner once the game has ended, else 0; env.winner() likewise (main.py:709)
+    const int winner = env_done ? sp.score_winner[g] : 0;
+    float reward = env_done ? (float)winner : 0.f;
+    if (capped) reward += -0.5f;                                    // main.py:703-706
+    sp.traj_action[row] = a;
+    sp.traj_reward[row] = reward;
+    sp.traj_done[row] = (done || capped) ? 1 : 0;
+    sp.traj_winner[row] = (int8_t)winner;
+    unsigned long long* c = (unsigned long long*)sp.counters;
+    atomicAdd(c + 0, 1ull);
+    atomicAdd(c + 1, (unsigned long long)sp.tree.sims_done[g]);
+    atomicAdd(c + 3, (unsigned long long)sp.tree.dropped[g]);
+    atomicAdd(c + 4, (unsigned long long)sp.tree.depth_sum[g]);
+    if (done || capped) {
+        atomicAdd(c + 2, 1ull);
+        if (winner > 0) atomicAdd(c + 5, 1ull);
+        if (winner < 0) atomicAdd(c + 6, 1ull);
+        if (capped) atomicAdd(c + 7, 1ull);
+    }
+}
+
+int check_sp(const mzgo_selfplay_t* sp) {
+    MZGO_CHECK_ARG(sp != nullptr, "selfplay is NULL");
+    MZGO_CHECK_ARG(sp->n * sp->n + 1 == sp->tree.A && sp->net.n == sp->n, "board size mismatch");
+    MZGO_CHECK_ARG(sp->num_simulations >= 0 && sp->num_simulations < sp->tree.M, "tree.M=%d must exceed simulations=%d",
+                   sp->tree.M, sp->num_simulations);
+    MZGO_CHECK_ARG(sp->boards && sp->arena && sp->root_policy && sp->root_value_net && sp->leaf_policy &&
+                       sp->leaf_reward && sp->leaf_value && sp->out_slot && sp->action && sp->move_count &&
+                       sp->pass_streak && sp->game_temperature && sp->score_winner && sp->counters,
+                   "selfplay has a NULL array");
+    MZGO_CHECK_ARG(sp->net.max_batch >= sp->tree.G, "net.max_batch=%d < G=%d", sp->net.max_batch, sp->tree.G);
+    return 0;
+}
+
+}  // namespace
+
+extern "C" int mzgo_search_run(const mzgo_selfplay_t* sp, const uint32_t* choice_stream, int stride, void* stream) {
+    if (int e = check_sp(sp)) return e;
+    const mzgo_tree_t* t = &sp->tree;
+    for (int s = 0; s < sp->num_simulations; s++) {
+        if (int e = mzgo_tree_select(t, &sp->params, choice_stream, stride, stream)) return e;
+        if (int e = mzgo_net_recurrent(&sp->net, sp->arena, t->leaf_in_slot, t->leaf_action, t->leaf_out_slot,
+                                       sp->leaf_reward, sp->leaf_value, sp->leaf_policy, 1, t->G, stream))
+            return e;
+        if (int e = mzgo_tree_expand_backup(t, &sp->params, sp->leaf_policy, sp->leaf_reward, sp->leaf_value, stream))
+            return e;
+    }
+    return MZGO_OK;
+}
+
+extern "C" int mzgo_selfplay_run(const mzgo_selfplay_t* sp_in, int num_moves, int traj_offset,
+                                 uint32_t first_move_index, void* stream) {
+    if (int e = check_sp(sp_in)) return e;
+    MZGO_CHECK_ARG(num_moves >= 0 && traj_offset >= 0 && traj_offset + num_moves <= sp_in->traj_capacity,
+                   "trajectory rows [%d,%d) outside capacity %d", traj_offset, traj_offset + num_moves,
+                   sp_in->traj_capacity);
+    MZGO_CHECK_ARG(sp_in->traj_boards && sp_in->traj_action && sp_in->traj_policy && sp_in->traj_root_value &&
+                       sp_in->traj_reward && sp_in->traj_done && sp_in->traj_winner,
+                   "selfplay has a NULL trajectory array");
+    mzgo_selfplay_t sp = *sp_in;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int G = sp.tree.G, A = sp.tree.A;
+    if (G == 0) return MZGO_OK;
+    const int blocks = ceil_div(G, SP_THREADS);
+    for (int i = 0; i < num_moves; i++) {
+        const int t = traj_offset + i;
+        const uint32_t move_index = first_move_index + (uint32_t)i;
+        sp.tree.move_index = (int32_t)move_index;
+        k_sp_begin_move<<<blocks, SP_THREADS, 0, st>>>(sp);
+        mzgo_count_launch();
+        MZGO_LAUNCH_CHECK();
+        // observation of this move (trajectory['observations'], main.py:640-645): the packed position
+        MZGO_CUDA(cudaMemcpyAsync(sp.traj_boards + (size_t)t * G * MZGO_BOARD_WORDS, sp.boards,
+                                  (size_t)G * MZGO_BOARD_WORDS * 4, cudaMemcpyDeviceToDevice, st));
+        // MCTS.run: initial inference + root preparation (main.py:256-288)
+        if (int e = mzgo_net_initial(&sp.net, nullptr, sp.boards, sp.arena, sp.out_slot, sp.root_value_net,
+                                     sp.root_policy, 1, G, stream))
+            return e;
+        if (int e = mzgo_tree_reset_roots(&sp.tree, &sp.params, sp.root_policy, sp.boards, sp.n, nullptr, move_index,
+                                          stream))
+            return e;
+        // the simulations (main.py:291-314)
+        if (int e = mzgo_search_run(&sp, nullptr, 0, stream)) return e;
+        // action + policy target (main.py:659-677), then env.step (main.py:681)
+        if (int e = mzgo_tree_choose_action(&sp.tree, &sp.params, 0.f, sp.game_temperature, move_index, sp.action,
+                                            sp.traj_policy + (size_t)t * G * A, sp.traj_root_value + (size_t)t * G,
+                                            stream))
+            return e;
+        if (int e = mzgo_rules_step(sp.boards, sp.action, nullptr, G, sp.n, stream)) return e;
+        if (int e = mzgo_rules_score(sp.boards, nullptr, sp.score_winner, sp.komi, G, sp.n, stream)) return e;
+        k_sp_end_move<<<blocks, SP_THREADS, 0, st>>>(sp, t);
+        mzgo_count_launch();
+        MZGO_LAUNCH_CHECK();
+    }
+    return MZGO_OK;
+}

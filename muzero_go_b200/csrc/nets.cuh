@@ -1,0 +1,40 @@
+// Internal declarations shared by nets_fp32.cu, nets_tc.cu, nets_api.cu and engine.cu.
+#pragma once
+#include "common.cuh"
+
+struct NetWorkspace {          // byte offsets into mzgo_net_t::workspace
+    long wT1, wT2, wT3, wTd;   // float32 conv weights as [Cin][9][Cout]
+    long act1, act2;           // float32 [max_batch][64][n*n] representation activations
+    long act3;                 // bf16 mode: float32 [max_batch][C][n*n] representation output before packing
+    long tc_w;                 // bf16 mode: dynamics conv weights in UMMA canonical layout
+    long tc_embbias;           // bf16 mode: float32 [A][9][C] per-action, per-border-class bias (embedding folded in)
+    long total;
+};
+
+NetWorkspace mzgo_net_layout(int n, int C, int precision, int max_batch);
+int mzgo_net_check(const mzgo_net_t* net);
+void mzgo_count_launch();
+void mzgo_count_launches(int k);
+
+int mzgo_net_prepare_fp32(const mzgo_net_t* net, cudaStream_t st);
+int mzgo_rep_fp32(const mzgo_net_t* net, const float* obs, const uint32_t* boards, float* out, const int32_t* out_idx,
+                  long out_stride, int B, cudaStream_t st);
+int mzgo_heads_fp32(const mzgo_net_t* net, const float* arena, const int32_t* slot, const int32_t* action,
+                    long slot_stride, float* reward, float* value, float* policy, int want_softmax, int B,
+                    cudaStream_t st);
+int mzgo_dyn_fp32(const mzgo_net_t* net, float* arena, const int32_t* in_slot, const int32_t* action,
+                  const int32_t* out_slot, int B, cudaStream_t st);
+int mzgo_copy_latent_f32(const float* src, const int32_t* src_idx, long src_stride, float* dst, const int32_t* dst_idx,
+                         long dst_stride, long count, int B, cudaStream_t st);
+
+// bf16 / tcgen05 path (nets_tc.cu)
+int mzgo_net_prepare_tc(const mzgo_net_t* net, cudaStream_t st);
+int mzgo_tc_pack_latent(const mzgo_net_t* net, const float* src, long src_stride, void* arena, const int32_t* slot,
+                        int B, cudaStream_t st);
+int mzgo_tc_unpack_latent(const mzgo_net_t* net, const void* arena, const int32_t* slot, float* dst, long dst_stride,
+                          int B, cudaStream_t st);
+int mzgo_tc_heads(const mzgo_net_t* net, const void* arena, const int32_t* slot, float* value, float* policy,
+                  int want_softmax, int B, cudaStream_t st);
+int mzgo_tc_recurrent(const mzgo_net_t* net, void* arena, const int32_t* in_slot, const int32_t* action,
+                      const int32_t* out_slot, float* reward, float* value, float* policy, int want_softmax, int B,
+                      cudaStream_t st);
