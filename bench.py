@@ -1,0 +1,331 @@
+#!/usr/bin/env python
+"""Self-play throughput bench (BASELINE.json metric: MCTS simulations/sec; moves/sec beside it).
+
+    python bench.py --gpus N --steps K --warmup W            # our arm: CUDA hot path through the C ABI
+    python bench.py --impl reference ...                      # CPU arm: the oracle port of the reference
+
+A step = one lock-step move of every concurrent game: initial inference, root preparation,
+`sims` x (select -> recurrent inference -> expand/backup), action choice, rules step, trajectory row.
+Prints ONE JSON line (rank 0).  See DESIGN.md "Measurement" for the definitions used here.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # BASELINE.json configs[1] / configs[3]
+    "9x9": dict(n=9, games=1024, sims=50, name="9x9 Go batched self-play, 1024 concurrent games, 50 sims/move"),
+    "19x19": dict(n=19, games=2048, sims=800, name="19x19 Go batched self-play, 2048 games, 800 sims/move"),
+}
+LATENT = 128
+
+
+def flops_recurrent(n, c=LATENT):
+    """dynamics conv3x3 + the three 1x1 heads, per simulation."""
+    return 2 * 9 * c * c * n * n + 2 * 3 * c * n * n
+
+
+def flops_initial(n, c=LATENT):
+    return 2 * 9 * n * n * (6 * 64 + 64 * 64 + 64 * c) + 2 * 2 * c * n * n
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as fh:
+            p = json.load(fh)
+        return dict(hbm_gbs=p["hbm_gbs"], bf16_burst=p["bf16_tflops"], bf16_sustained=p["bf16_tflops_sustained"],
+                    source="measured")
+    return dict(hbm_gbs=6650.0, bf16_burst=1590.0, bf16_sustained=1400.0, source="fallback")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], None, set()
+        for r in self.rows:
+            if len(r) < 7:
+                continue
+            try:
+                sm.append(float(r[0]))
+                mx = float(r[1])
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------ CPU arm
+def _cpu_worker(args):
+    """Oracle port of the reference's self-play move loop (main.py:656-702): reference networks in torch
+    fp32 on the CPU, the oracle MCTS restatement, the oracle GymGo restatement.  Runs for ~`budget` s."""
+    n, sims, budget, seed = args
+    import numpy as np
+    import torch
+    from oracle import gymgo, mcts_ref
+    from oracle.nets_ref import MuZeroNetRef
+    torch.set_num_threads(1)
+    torch.manual_seed(0)
+    net = MuZeroNetRef(LATENT, n * n + 1).eval()
+    initial, recurrent = mcts_ref.torch_net_callbacks(net)
+    rng = np.random.default_rng(seed)
+    A = n * n + 1
+    env = gymgo.GoEnv(n)
+    obs = env.reset()
+    sims_done = moves = 0
+    t0 = time.perf_counter()
+    while time.perf_counter() - t0 < budget:
+        noise = rng.dirichlet([0.03] * A)
+        stream = rng.integers(0, 2 ** 32, size=sims + 8, dtype=np.uint64).astype(np.uint32)
+        tree, mask = mcts_ref.run_mcts(obs, initial, recurrent, sims, noise, stream)
+        vc = tree.root_visit_counts(mask)
+        action, _ = mcts_ref.choose_action(vc, mask, int(rng.integers(1 << 30)))
+        obs, _, done, _ = env.step(action)
+        sims_done += tree.visit[0]
+        moves += 1
+        if done or moves % int(1.5 * n * n) == 0:
+            obs = env.reset()
+    return sims_done, moves, time.perf_counter() - t0
+
+
+def cpu_arm(n, sims, budget, procs):
+    import multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    with ctx.Pool(procs) as pool:
+        res = pool.map(_cpu_worker, [(n, sims, budget, 100 + i) for i in range(procs)])
+    total_s = sum(r[0] for r in res)
+    total_m = sum(r[1] for r in res)
+    wall = max(r[2] for r in res)
+    return total_s / wall, total_m / wall, wall
+
+
+def run_reference(args, wl):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    procs = os.cpu_count() or 1
+    n, sims = wl["n"], wl["sims"]
+    per_step = max(4.0, min(20.0, 120.0 / max(1, args.steps + args.warmup)))
+    for _ in range(args.warmup):
+        cpu_arm(n, sims, min(2.0, per_step), procs)
+    vals, mvals, t_total = [], [], 0.0
+    for _ in range(args.steps):
+        s, m, wall = cpu_arm(n, sims, per_step, procs)
+        vals.append(s)
+        mvals.append(m)
+        t_total += wall
+    v = sum(vals) / len(vals)
+    sample = (f"{procs} single-thread processes x {per_step:.0f} s of the oracle port of main.py's self-play loop "
+              f"({n}x{n}, {sims} sims/move, C={LATENT}, one game per process)")
+    line = {"impl": "reference", "metric": "mcts_simulations_per_sec", "value": v, "unit": "sims/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1000.0 * t_total / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": wl["name"], "board": n, "sims_per_move": sims, "latent_dim": LATENT},
+            "moves_per_sec": sum(mvals) / len(mvals),
+            "cpu_baseline": {"value": v, "unit": "sims/s", "cores": procs, "kind": "port", "sample": sample},
+            "e2e": {"value": v, "unit": "sims/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------ GPU arm
+def run_ours(args, wl):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    import muzero_go_b200 as mz
+    from muzero_go_b200 import _lib
+    from muzero_go_b200 import dist as mzdist
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    n, G, S = wl["n"], args.games or wl["games"], args.sims or wl["sims"]
+    A = n * n + 1
+    K, W = args.steps, args.warmup
+
+    torch.manual_seed(0)                                    # random-init weights of the reference architecture
+    net = mz.MuZeroNet(LATENT, A, precision=args.precision).to(dev).eval()
+    bytes_bcast = mzdist.broadcast_weights(net, src=0)       # weight version 0 from the learner rank
+    # fit the latent arena into HBM (19x19 / 800 sims / 2048 games needs ~152 GB in bf16)
+    free_b, _ = torch.cuda.mem_get_info()
+    per_game = (S + 1) * (net.slot_bytes() + A * 18 + 8) + 64 * 1024
+    if G * per_game > 0.92 * free_b:
+        G = int(0.92 * free_b / per_game) // 64 * 64
+    T = 2
+    eng = mz.SelfPlayEngine(net, n, G, S, search=mz.SearchConfig(seed=1000 + rank), traj_capacity=T,
+                            restart_finished=True)
+    lib = _lib.load()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step(row=0):
+        eng.run(1, traj_offset=row)
+        rows = eng.trajectory_rows(row, row + 1)
+        if world > 1:                                        # trajectory gather to the replay side, outside the search
+            mzdist.gather_trajectories(rows, A)
+        return rows
+
+    for _ in range(W):
+        step()
+    barrier()
+    lib.mzgo_launch_count(1)
+    c0 = eng.read_counters()
+    sampler = ClockSampler(local)
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(K):
+        step()
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    clocks = sampler.stop()
+    launches = int(lib.mzgo_launch_count(0))
+    c1 = eng.read_counters()
+    sims_done = c1["simulations"] - c0["simulations"]
+    moves_done = c1["moves"] - c0["moves"]
+    depth = (c1["leaf_depth_sum"] - c0["leaf_depth_sum"]) / max(1, sims_done)
+
+    # ---- end to end through the public API with HOST buffers: positions up, trajectory row down, every step
+    host_boards = torch.empty((G, 64), dtype=torch.int32).pin_memory()
+    host_boards.copy_(eng.boards.records)
+    row_bytes = mzdist.pack_rows(eng.trajectory_rows(0, 1))
+    host_row = torch.empty(row_bytes.shape, dtype=torch.uint8).pin_memory()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(K):
+        eng.boards.records.copy_(host_boards, non_blocking=True)
+        rows = step()
+        host_row.copy_(mzdist.pack_rows(rows), non_blocking=True)
+        torch.cuda.synchronize()
+        host_boards.copy_(eng.boards.records)                # next step's input comes from the host again
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    c2 = eng.read_counters()
+    e2e_sims = c2["simulations"] - c1["simulations"]
+
+    # ---- dominant kernel (recurrent inference of one leaf batch), timed alone with CUDA events
+    d = eng.descriptor()
+    reps = 20
+    eng.tree.select(eng.search, None)
+    k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    args_rec = (d.net, _lib.ptr(eng.arena), _lib.ptr(eng.tree.leaf_in_slot), _lib.ptr(eng.tree.leaf_action),
+                _lib.ptr(eng.tree.leaf_out_slot), _lib.ptr(eng.leaf_reward), _lib.ptr(eng.leaf_value),
+                _lib.ptr(eng.leaf_policy), 1, G, _lib.stream_ptr())
+    for _ in range(3):
+        _lib.check(lib.mzgo_net_recurrent(*args_rec))
+    torch.cuda.synchronize()
+    k0.record()
+    for _ in range(reps):
+        _lib.check(lib.mzgo_net_recurrent(*args_rec))
+    k1.record()
+    torch.cuda.synchronize()
+    kern_ms = k0.elapsed_time(k1) / reps
+    live = int((eng.tree.leaf_action >= 0).sum())
+    peaks = measured_peaks()
+    achieved = live * flops_recurrent(n) / (kern_ms * 1e-3) / 1e12
+    peak_tf = peaks["bf16_sustained"]
+
+    t = torch.tensor([ms, e2e_s * 1000.0], dtype=torch.float64, device=dev)
+    tot = torch.tensor([sims_done, moves_done, e2e_sims, launches, G], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+    ms, e2e_ms = t.tolist()
+    sims_all, moves_all, e2e_sims_all, launches_all, G_all = tot.tolist()
+
+    if rank == 0:
+        cpu = None
+        if world == 1 and not args.no_cpu_baseline:
+            procs = os.cpu_count() or 1
+            s, m, wall = cpu_arm(n, S, 12.0, procs)
+            cpu = {"value": s, "unit": "sims/s", "cores": procs, "kind": "port", "moves_per_sec": m,
+                   "sample": f"{procs} single-thread processes x 12 s of the oracle port of main.py's self-play loop "
+                             f"({n}x{n}, {S} sims/move, C={LATENT})"}
+        row_b = int(row_bytes.numel())
+        line = {"metric": "mcts_simulations_per_sec", "value": sims_all / (ms * 1e-3), "unit": "sims/s", "n_gpus": world,
+                "steps": K, "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "bf16" if args.precision == "bf16" else "f32", "data": "synthetic",
+                "config": {"workload": wl["name"], "board": n, "games_per_gpu": G, "games_total": int(G_all),
+                           "sims_per_move": S, "latent_dim": LATENT, "weights": "random-init (torch.manual_seed(0))",
+                           "cache": "inputs larger than L2 (latent arena %.1f GB per GPU)" % (eng.arena.numel() / 1e9),
+                           "parallelism": f"games sharded over {world} GPU(s), no collective inside the search"},
+                "moves_per_sec": moves_all / (ms * 1e-3), "mean_leaf_depth": depth,
+                "e2e": {"value": e2e_sims_all / (e2e_ms * 1e-3), "unit": "sims/s", "h2d_bytes_per_step": G * 256,
+                        "d2h_bytes_per_step": row_b + G * 256},
+                "gpu_launches": int(launches_all),
+                "roofline": {"bound": "tensor", "kernel": "mzgo_net_recurrent (dynamics conv3x3 + heads, one leaf batch)",
+                             "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved / peak_tf,
+                             "traffic": None, "peak_source": peaks["source"] + " bf16 sustained",
+                             "launch_ms": kern_ms, "leaves_per_launch": live},
+                "cpu_baseline": cpu, "clocks": clocks,
+                "weight_broadcast_bytes": bytes_bcast}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=4)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="9x9", choices=sorted(WORKLOADS))
+    ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--games", type=int, default=0)
+    ap.add_argument("--sims", type=int, default=0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 0)
+    wl = WORKLOADS[args.workload]
+    if args.impl == "reference":
+        run_reference(args, wl)
+    else:
+        run_ours(args, wl)
+
+
+if __name__ == "__main__":
+    main()

@@ -35,6 +35,9 @@ const char* mzgo_last_error(void);
 int mzgo_abi_version(void);
 /* 1 when a CUDA device with compute capability 10.x is usable, else 0 (never fails). */
 int mzgo_device_ok(void);
+/* sizeof of the descriptor structs as compiled: 0 mzgo_tree_t, 1 mzgo_search_params_t, 2 mzgo_net_t,
+ * 3 mzgo_selfplay_t (lets a binding check its struct mirrors); -1 for an unknown index. */
+int64_t mzgo_sizeof(int which);
 
 /* ------------------------------------------------------------------------------------------
  * 1. Go rules engine (replaces GymGo: call sites main.py:628,637,681,709; planes main.py:261)
@@ -223,6 +226,10 @@ int mzgo_net_initial(const mzgo_net_t* net, const float* obs /*device, optional*
 int mzgo_net_recurrent(const mzgo_net_t* net, void* arena /*device*/, const int32_t* in_slot,
                        const int32_t* action, const int32_t* out_slot, float* reward, float* value,
                        float* policy, int want_softmax, int B, void* stream);
+
+/* PredictionNetwork.forward alone (main.py:116-125) on the latents in slot[b]: value [B], policy [B][A]. */
+int mzgo_net_predict(const mzgo_net_t* net, const void* arena /*device*/, const int32_t* slot /*device [B]*/,
+                     float* value, float* policy, int want_softmax, int B, void* stream);
 
 /* Slot <-> reference tensor layout (float32 [B][C][n][n]); identity copy in fp32 mode. */
 int mzgo_net_export_latent(const mzgo_net_t* net, const void* arena, const int32_t* slot,

@@ -66,6 +66,7 @@ _PROTOS = {
     "mzgo_abi_version": (i32, []),
     "mzgo_device_ok": (i32, []),
     "mzgo_launch_count": (i64, [i32]),
+    "mzgo_sizeof": (i64, [i32]),
     "mzgo_rules_reset": (i32, [vp, i32, i32, vp]),
     "mzgo_rules_step": (i32, [vp, vp, vp, i32, i32, vp]),
     "mzgo_rules_score": (i32, [vp, vp, vp, f32, i32, i32, vp]),
@@ -82,6 +83,7 @@ _PROTOS = {
     "mzgo_net_prepare": (i32, [C.POINTER(NetDesc), vp]),
     "mzgo_net_initial": (i32, [C.POINTER(NetDesc), vp, vp, vp, vp, vp, vp, i32, i32, vp]),
     "mzgo_net_recurrent": (i32, [C.POINTER(NetDesc), vp, vp, vp, vp, vp, vp, vp, i32, i32, vp]),
+    "mzgo_net_predict": (i32, [C.POINTER(NetDesc), vp, vp, vp, vp, i32, i32, vp]),
     "mzgo_net_export_latent": (i32, [C.POINTER(NetDesc), vp, vp, vp, i32, vp]),
     "mzgo_net_import_latent": (i32, [C.POINTER(NetDesc), vp, vp, vp, i32, vp]),
     "mzgo_selfplay_run": (i32, [C.POINTER(SelfPlayDesc), i32, i32, u32, vp]),
@@ -112,6 +114,10 @@ def load():
         fn = getattr(lib, name)
         fn.restype = res
         fn.argtypes = args
+    for which, struct in enumerate((TreeDesc, SearchParams, NetDesc, SelfPlayDesc)):
+        if lib.mzgo_sizeof(which) != C.sizeof(struct):
+            raise MzgoError(f"{struct.__name__}: ctypes mirror is {C.sizeof(struct)} B, library says "
+                            f"{lib.mzgo_sizeof(which)} B (include/mzgo.h and _lib.py disagree)")
     _lib = lib
     return lib
 

@@ -35,3 +35,13 @@ extern "C" int64_t mzgo_launch_count(int reset) {
     if (reset) g_launches = 0;
     return v;
 }
+
+extern "C" int64_t mzgo_sizeof(int which) {
+    switch (which) {
+        case 0: return sizeof(mzgo_tree_t);
+        case 1: return sizeof(mzgo_search_params_t);
+        case 2: return sizeof(mzgo_net_t);
+        case 3: return sizeof(mzgo_selfplay_t);
+    }
+    return -1;
+}

@@ -52,6 +52,22 @@ extern "C" int mzgo_net_recurrent(const mzgo_net_t* net, void* arena, const int3
     return mzgo_tc_recurrent(net, arena, in_slot, action, out_slot, reward, value, policy, want_softmax, B, st);
 }
 
+extern "C" int mzgo_net_predict(const mzgo_net_t* net, const void* arena, const int32_t* slot, float* value,
+                                float* policy, int want_softmax, int B, void* stream) {
+    if (int e = mzgo_net_check(net)) return e;
+    MZGO_CHECK_ARG(arena && slot && value && policy, "NULL argument");
+    MZGO_CHECK_ARG(B >= 0 && B <= net->max_batch, "B=%d outside [0,max_batch=%d]", B, net->max_batch);
+    if (B == 0) return MZGO_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    const long cnt = (long)net->C * net->n * net->n;
+    if (net->precision == 0)
+        return mzgo_heads_fp32(net, (const float*)arena, slot, nullptr, cnt, nullptr, value, policy, want_softmax, B, st);
+    NetWorkspace w = mzgo_net_layout(net->n, net->C, net->precision, net->max_batch);
+    float* act3 = (float*)((char*)net->workspace + w.act3);
+    if (int e = mzgo_tc_unpack_latent(net, arena, slot, act3, cnt, B, st)) return e;
+    return mzgo_heads_fp32(net, act3, nullptr, slot, cnt, nullptr, value, policy, want_softmax, B, st);
+}
+
 extern "C" int mzgo_net_export_latent(const mzgo_net_t* net, const void* arena, const int32_t* slot, float* out, int B,
                                       void* stream) {
     if (int e = mzgo_net_check(net)) return e;

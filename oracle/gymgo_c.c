@@ -160,13 +160,39 @@ void gymgo_c_areas(const uint8_t* st, int n, int* black_area, int* white_area) {
     *black_area = b; *white_area = w;
 }
 
+static uint64_t mix64(uint64_t x) {
+    x ^= x >> 30; x *= 0xbf58476d1ce4e5b9ull;
+    x ^= x >> 27; x *= 0x94d049bb133111ebull;
+    x ^= x >> 31;
+    return x;
+}
+
+/* Order-independent hash of a GymGo state, the same function as mzgo_board_hash in
+ * muzero_go_b200/csrc/rules.cu: sum over rows of mix64(black | white<<20 | invalid<<40 | (row+1)<<59)
+ * plus mix64(0xabcd + turn + 2*pass + 4*done).  Lets 4096x722-ply playouts be compared ply by ply. */
+uint64_t gymgo_c_hash(const uint8_t* st, int n) {
+    int np = n * n;
+    uint64_t h = 0;
+    for (int r = 0; r < n; r++) {
+        uint64_t bl = 0, wh = 0, inv = 0;
+        for (int c = 0; c < n; c++) {
+            bl |= (uint64_t)(st[r * n + c] != 0) << c;
+            wh |= (uint64_t)(st[np + r * n + c] != 0) << c;
+            inv |= (uint64_t)(st[3 * np + r * n + c] != 0) << c;
+        }
+        h += mix64(bl | (wh << 20) | (inv << 40) | ((uint64_t)(r + 1) << 59));
+    }
+    h += mix64(0xabcdull + (uint64_t)(st[2 * np] != 0) + 2ull * (st[4 * np] != 0) + 4ull * (st[5 * np] != 0));
+    return h;
+}
+
 /* Config-3 playout: for each board, ply t plays the k-th (ascending) entry of
  * {valid board points} U {pass}, k = R[b*T + t] % n_valid.  Stops a board when
- * done.  trace (optional) receives the state after every ply:
+ * done.  hashes (optional) [nboards][T] gymgo_c_hash after every ply.  trace (optional) receives the state after every ply:
  * [nboards][T][6*n*n] bytes; actions (optional) [nboards][T] int32 (-1 = not played).
  * Returns total plies played. */
 long gymgo_c_playout(uint8_t* states, int n, int nboards, const uint32_t* R, int T,
-                     uint8_t* trace, int32_t* actions) {
+                     uint8_t* trace, int32_t* actions, uint64_t* hashes) {
     int np = n * n, S = 6 * np;
     long plies = 0;
     for (int b = 0; b < nboards; b++) {
@@ -185,6 +211,7 @@ long gymgo_c_playout(uint8_t* states, int n, int nboards, const uint32_t* R, int
             }
             if (actions) actions[(long)b * T + t] = a;
             if (trace) memcpy(trace + ((long)b * T + t) * S, st, S);
+            if (hashes) hashes[(long)b * T + t] = gymgo_c_hash(st, n);
         }
     }
     return plies;

@@ -33,7 +33,9 @@ def lib():
         L.gymgo_c_areas.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p]
         L.gymgo_c_areas.restype = None
         L.gymgo_c_playout.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p,
-                                      ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p]
+                                      ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+        L.gymgo_c_hash.argtypes = [ctypes.c_void_p, ctypes.c_int]
+        L.gymgo_c_hash.restype = ctypes.c_uint64
         L.gymgo_c_playout.restype = ctypes.c_long
         _lib = L
     return _lib
@@ -57,15 +59,24 @@ def areas(state_u8):
     return b.value, w.value
 
 
-def playout(states_u8, R, trace=False):
+def board_hash(state_u8):
+    st = np.ascontiguousarray(state_u8, dtype=np.uint8)
+    return int(lib().gymgo_c_hash(st.ctypes.data, st.shape[1]))
+
+
+def playout(states_u8, R, trace=False, hashes=False):
     """states_u8 [B,6,n,n] uint8 in place; R [B,T] uint32.
-    Returns (plies, actions[B,T] int32, trace[B,T,6,n,n] or None)."""
+    Returns (plies, actions[B,T] int32, trace[B,T,6,n,n] or None[, hashes[B,T] uint64])."""
     assert states_u8.dtype == np.uint8 and states_u8.flags.c_contiguous
     B, _, n, _ = states_u8.shape
     R = np.ascontiguousarray(R, dtype=np.uint32)
     T = R.shape[1]
     actions = np.full((B, T), -1, dtype=np.int32)
     tr = np.zeros((B, T, 6, n, n), dtype=np.uint8) if trace else None
+    hs = np.zeros((B, T), dtype=np.uint64) if hashes else None
     plies = lib().gymgo_c_playout(states_u8.ctypes.data, n, B, R.ctypes.data, T,
-                                  tr.ctypes.data if trace else None, actions.ctypes.data)
+                                  tr.ctypes.data if trace else None, actions.ctypes.data,
+                                  hs.ctypes.data if hashes else None)
+    if hashes:
+        return plies, actions, tr, hs
     return plies, actions, tr

@@ -1,0 +1,111 @@
+"""GPU: representation / dynamics / prediction networks through the C ABI against the golden outputs of
+the real reference MuZeroNet (tests/golden/nets_*.npz) and against the torch oracle on fresh inputs.
+Tolerances are north_star's: fp32 mode 1e-5, bf16 mode 1e-2 relative."""
+import glob
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle.nets_ref import MuZeroNetRef
+
+pytestmark = pytest.mark.gpu
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+FIXTURES = sorted(glob.glob(os.path.join(GOLDEN, "nets_*.npz")))
+
+
+def build_pair(n, c, seed, pass_logit, precision):
+    import muzero_go_b200 as mz
+    A = n * n + 1
+    torch.manual_seed(seed)
+    ref = MuZeroNetRef(c, A).eval()
+    with torch.no_grad():
+        ref.prediction.pass_logit.fill_(pass_logit)
+    net = mz.MuZeroNet(c, A, precision=precision)
+    net.load_state_dict(ref.state_dict())
+    return ref, net.cuda().eval()
+
+
+def close(got, want, rtol, atol, name):
+    np.testing.assert_allclose(got.detach().cpu().numpy(), want, rtol=rtol, atol=atol, err_msg=name)
+
+
+def rel_err(got, want):
+    got, want = got.detach().cpu().double().numpy(), np.asarray(want, dtype=np.float64)
+    return float(np.abs(got - want).max() / (np.abs(want).max() + 1e-12))
+
+
+@pytest.mark.parametrize("path", FIXTURES, ids=os.path.basename)
+def test_fp32_mode_matches_reference_golden(path):
+    g = np.load(path)
+    _, net = build_pair(int(g["n"]), int(g["c"]), int(g["seed"]), float(g["pass_logit"]), "fp32")
+    obs, actions = torch.from_numpy(g["obs"]).cuda(), torch.from_numpy(g["actions"]).cuda()
+    latent, value, logits = net.initial_inference(obs)
+    tol = dict(rtol=1e-5, atol=1e-5)
+    close(latent, g["latent"], name="latent", **tol)
+    close(value, g["value"], name="value", **tol)
+    close(logits, g["logits"], name="logits", **tol)
+    nxt, reward, value2, logits2 = net.recurrent_inference(latent, actions)
+    close(nxt, g["next_latent"], name="next_latent", **tol)
+    close(reward, g["reward"], name="reward", **tol)
+    close(value2, g["value2"], name="value2", **tol)
+    close(logits2, g["logits2"], name="logits2", **tol)
+    nxt2, reward3, value3, logits3 = net.recurrent_inference(nxt, actions.flip(0))
+    close(reward3, g["reward3"], name="reward3", **tol)
+    close(value3, g["value3"], name="value3", **tol)
+    close(logits3, g["logits3"], name="logits3", **tol)
+    assert float(nxt2.double().sum()) == pytest.approx(float(g["next_latent2_sum"]), rel=1e-5)
+    # the sub-modules keep the reference call signatures (main.py:80, :96, :116)
+    close(net.representation(obs), g["latent"], name="representation", **tol)
+    x, r = net.dynamics(latent, actions)
+    close(x, g["next_latent"], name="dynamics latent", **tol)
+    close(r, g["reward"], name="dynamics reward", **tol)
+    v, lg = net.prediction(latent)
+    close(v, g["value"], name="prediction value", **tol)
+    close(lg, g["logits"], name="prediction logits", **tol)
+
+
+@pytest.mark.parametrize("path", [p for p in FIXTURES if "_C128" in p], ids=os.path.basename)
+def test_bf16_mode_within_1e2_of_reference_golden(path):
+    g = np.load(path)
+    _, net = build_pair(int(g["n"]), int(g["c"]), int(g["seed"]), float(g["pass_logit"]), "bf16")
+    obs, actions = torch.from_numpy(g["obs"]).cuda(), torch.from_numpy(g["actions"]).cuda()
+    latent, value, logits = net.initial_inference(obs)
+    nxt, reward, value2, logits2 = net.recurrent_inference(latent, actions)
+    _, reward3, value3, logits3 = net.recurrent_inference(nxt, actions.flip(0))
+    errs = {"latent": rel_err(latent, g["latent"]), "value": rel_err(value, g["value"]),
+            "logits": rel_err(logits, g["logits"]), "next_latent": rel_err(nxt, g["next_latent"]),
+            "reward": rel_err(reward, g["reward"]), "value2": rel_err(value2, g["value2"]),
+            "logits2": rel_err(logits2, g["logits2"]), "reward3": rel_err(reward3, g["reward3"]),
+            "value3": rel_err(value3, g["value3"]), "logits3": rel_err(logits3, g["logits3"])}
+    print(errs)
+    assert max(errs.values()) < 1e-2, errs      # 1e-2 relative to the tensor's scale (north_star, bf16)
+
+
+@pytest.mark.parametrize("n,c,precision,tol", [(9, 128, "fp32", 1e-5), (19, 128, "fp32", 1e-5), (5, 16, "fp32", 1e-5),
+                                               (9, 96, "fp32", 1e-5), (9, 128, "bf16", 1e-2), (19, 128, "bf16", 1e-2)])
+def test_random_batches_match_torch_oracle(n, c, precision, tol):
+    """Scaled-up weights so every head is far from its degenerate init; all actions incl. pass and corners."""
+    A = n * n + 1
+    ref, net = build_pair(n, c, 7, 0.25, precision)
+    with torch.no_grad():
+        for p in ref.parameters():
+            p.mul_(1.7)
+        ref.dynamics.action_embedding.weight.mul_(0.3)
+    net.load_state_dict(ref.state_dict())
+    rng = np.random.default_rng(n * 100 + c)
+    B = 37
+    obs = torch.from_numpy((rng.random((B, 6, n, n)) < 0.3).astype(np.float32))
+    actions = torch.from_numpy(rng.integers(0, A, B).astype(np.int64))
+    actions[:4] = torch.tensor([0, n - 1, n * n - 1, n * n])
+    with torch.no_grad():
+        rl, rv, rlog = ref.initial_inference(obs)
+        rn, rr, rv2, rlog2 = ref.recurrent_inference(rl, actions)
+    latent, value, logits = net.initial_inference(obs.cuda())
+    nxt, reward, value2, logits2 = net.recurrent_inference(rl.cuda(), actions.cuda())
+    errs = {"latent": rel_err(latent, rl), "value": rel_err(value, rv), "logits": rel_err(logits, rlog),
+            "next_latent": rel_err(nxt, rn), "reward": rel_err(reward, rr), "value2": rel_err(value2, rv2),
+            "logits2": rel_err(logits2, rlog2)}
+    print(precision, n, c, errs)
+    assert max(errs.values()) < tol, errs

@@ -1,0 +1,110 @@
+"""GPU: the CUDA rules engine (through the C ABI) against the oracle restatements of GymGo.
+Bit-exact: every plane after every ply, actions, areas, winner."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import gymgo, gymgo_fast
+
+pytestmark = pytest.mark.gpu
+
+
+def philox_table(seed, shape):
+    return np.random.Generator(np.random.Philox(seed)).integers(0, 2 ** 32, size=shape, dtype=np.uint64).astype(np.uint32)
+
+
+@pytest.mark.parametrize("n,boards,T", [(2, 16, 24), (5, 64, 80), (6, 64, 100), (9, 64, 200), (13, 16, 400), (19, 16, 722)])
+def test_playout_trace_bit_exact(n, boards, T):
+    import muzero_go_b200 as mz
+    R = philox_table(100 + n, (boards, T))
+    ref_states = gymgo_fast.init_states(boards, n)
+    plies, ref_actions, ref_trace = gymgo_fast.playout(ref_states, R, trace=True)
+    gb = mz.GoBoards(boards, n).reset()
+    acts, hsh, trace = gb.playout(R, want_hash=True, want_trace=True)
+    assert np.array_equal(acts.cpu().numpy(), ref_actions)
+    got = trace.cpu().numpy()
+    if not np.array_equal(got, ref_trace):
+        bad = np.argwhere((got != ref_trace).reshape(boards, T, -1).any(axis=2))[0]
+        raise AssertionError(f"first mismatch at board {bad[0]} ply {bad[1]} action {ref_actions[bad[0], bad[1]]}")
+    assert np.array_equal(gb.planes(torch.uint8).cpu().numpy(), ref_states)
+    # the state hash agrees with the oracle's implementation of the same function
+    ref_hash = np.array([[gymgo_fast.board_hash(ref_trace[b, t]) for t in range(0, T, 7)] for b in range(boards)], dtype=np.uint64)
+    assert np.array_equal(hsh.cpu().numpy().view(np.uint64)[:, ::7], ref_hash)
+    # areas / winner on the final positions
+    areas, winner = gb.score(0.0)
+    ref_areas = np.array([gymgo_fast.areas(s) for s in ref_states])
+    assert np.array_equal(areas.cpu().numpy(), ref_areas)
+    assert np.array_equal(winner.cpu().numpy(), np.sign(ref_areas[:, 0] - ref_areas[:, 1]))
+    assert plies == int((ref_actions >= 0).sum())
+
+
+def test_config3_full_size_4096_boards():
+    """BASELINE.json configs[2]: 19x19, 4096 boards, up to 722 plies; per-ply state hashes, actions,
+    final planes and areas against the C oracle."""
+    import muzero_go_b200 as mz
+    n, boards, T = 19, 4096, 722
+    R = philox_table(0, (boards, T))
+    ref_states = gymgo_fast.init_states(boards, n)
+    plies, ref_actions, _, ref_hash = gymgo_fast.playout(ref_states, R, hashes=True)
+    gb = mz.GoBoards(boards, n).reset()
+    acts, hsh, _ = gb.playout(R, want_hash=True)
+    assert np.array_equal(acts.cpu().numpy(), ref_actions)
+    assert np.array_equal(hsh.cpu().numpy().view(np.uint64), ref_hash)
+    assert np.array_equal(gb.planes(torch.uint8).cpu().numpy(), ref_states)
+    areas, _ = gb.score(0.0)
+    assert np.array_equal(areas.cpu().numpy(), np.array([gymgo_fast.areas(s) for s in ref_states]))
+    assert plies > boards * 300
+
+
+def test_step_api_matches_python_oracle_and_reports_errors():
+    import muzero_go_b200 as mz
+    n, boards = 7, 32
+    rng = np.random.default_rng(5)
+    gb = mz.GoBoards(boards, n).reset()
+    states = [gymgo.init_state(n) for _ in range(boards)]
+    for t in range(90):
+        actions = np.full(boards, -1, dtype=np.int32)
+        for b, st in enumerate(states):
+            if gymgo.game_ended(st) or (b + t) % 11 == 0:
+                continue                      # -1: leave this board alone
+            v = np.nonzero(gymgo.valid_moves(st))[0]
+            actions[b] = v[rng.integers(len(v))] if rng.random() < 0.9 else n * n
+            states[b] = gymgo.next_state(st, int(actions[b]))
+        status = gb.step(torch.from_numpy(actions))
+        assert int(status.abs().sum()) == 0
+        assert np.array_equal(gb.planes(torch.float64).cpu().numpy(), np.stack(states))
+    # errors leave the board untouched
+    before = gb.records.clone()
+    bad = np.zeros(boards, dtype=np.int32)
+    for b, st in enumerate(states):
+        occupied = np.nonzero((st[0] + st[1]).flatten())[0]
+        bad[b] = occupied[0] if len(occupied) else n * n + 5
+    status = gb.step(torch.from_numpy(bad)).cpu().numpy()
+    for b, st in enumerate(states):
+        assert status[b] == (-2 if gymgo.game_ended(st) else -1)
+    assert torch.equal(before, gb.records)
+
+
+def test_pack_expand_round_trip_and_env():
+    import muzero_go_b200 as mz
+    n = 9
+    R = philox_table(9, (8, 60))
+    gb = mz.GoBoards(8, n).reset()
+    gb.playout(R)
+    planes = gb.planes(torch.float32)
+    gb2 = mz.GoBoards(8, n).load_planes(planes)
+    assert torch.equal(gb2.planes(torch.float32), planes)
+    # GoEnv: same trajectory as the oracle env, including reward / done / winner
+    env, ref = mz.make("gym_go:go-v0", size=5, komi=0, reward_method="real"), gymgo.GoEnv(5)
+    assert np.array_equal(env.reset(), ref.reset())
+    rng = np.random.default_rng(0)
+    done = False
+    while not done:
+        v = np.nonzero(ref.valid_moves())[0]
+        a = int(v[rng.integers(len(v))])
+        s1, r1, d1, i1 = env.step(a)
+        s2, r2, d2, i2 = ref.step(a)
+        assert np.array_equal(s1, s2) and r1 == r2 and d1 == d2 and i1["turn"] == i2["turn"]
+        assert np.array_equal(i1["invalid_moves"], i2["invalid_moves"])
+        done = d1
+    assert env.winner() == ref.winner()

@@ -1,0 +1,159 @@
+"""GPU: the drop-in MCTS.run / MuZeroAgent surface and the batched self-play engine."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import gymgo, mcts_ref
+from oracle.nets_ref import MuZeroNetRef
+
+pytestmark = pytest.mark.gpu
+
+
+def make_net(n, c, seed, precision="fp32"):
+    import muzero_go_b200 as mz
+    torch.manual_seed(seed)
+    ref = MuZeroNetRef(c, n * n + 1).eval()
+    with torch.no_grad():     # spread the outputs so the search goes deeper than the root's children
+        ref.prediction.policy_conv.weight.mul_(8.0)
+        ref.prediction.value_fc.weight.fill_(3.0)
+    net = mz.MuZeroNet(c, n * n + 1, precision=precision)
+    net.load_state_dict(ref.state_dict())
+    return ref, net.cuda().eval()
+
+
+def test_mcts_run_drop_in_matches_oracle_search_with_same_network_outputs():
+    """MCTS(net, A, sims).run(obs) on the GPU vs the oracle search driven by the SAME float32 network
+    outputs: the oracle's callbacks evaluate our CUDA fp32 network (so both sides consume identical
+    numbers, as north_star specifies) and apply the same softmax kernel."""
+    import muzero_go_b200 as mz
+    from oracle.make_golden import midgame_obs
+    n, c, sims = 6, 32, 150
+    A = n * n + 1
+    _, net = make_net(n, c, 21)
+    obs = midgame_obs(n, 7, 3)
+    rng = np.random.default_rng(0)
+    noise = rng.dirichlet([0.3] * A)
+    stream = rng.integers(0, 2 ** 32, size=sims + 8, dtype=np.uint64).astype(np.uint32)
+    mcts = mz.MCTS(net, A, sims)
+    root = mcts.run(obs, noise=noise, choice_stream=stream)
+
+    def initial(o):
+        lat, v, p = net._run_initial(torch.from_numpy(np.asarray(o, dtype=np.float32))[None].cuda(), want_softmax=True)
+        return lat, v.cpu().numpy().reshape(-1)[0], p.cpu().numpy()[0]
+
+    def recurrent(lat, a):
+        nxt, r, v, p = net._run_recurrent(lat, torch.tensor([a]).cuda(), want_softmax=True)
+        return nxt, r.cpu().numpy().reshape(-1)[0], v.cpu().numpy().reshape(-1)[0], p.cpu().numpy()[0]
+
+    tree, mask = mcts_ref.run_mcts(obs, initial, recurrent, sims, noise, stream)
+    got = np.array([ch["node"].visit_count if ch["node"] is not None else 0 for ch in root.children.values()])
+    assert np.array_equal(got, tree.root_visit_counts(mask))
+    assert root.visit_count == tree.visit[0] == sims
+    assert root.value() == pytest.approx(tree.q(0), rel=1e-12)
+    assert max(tree.depths) >= 2
+    priors = np.array([float(ch["prior"]) for ch in root.children.values()])
+    assert np.array_equal(priors, np.asarray(tree.prior[0], dtype=np.float64))
+    # a child view exposes the reference's fields too
+    a_best = int(np.argmax(got))
+    child = root.children[a_best]["node"]
+    assert child.visit_count == got[a_best] and tuple(child.latent.shape) == (c, n, n)
+    assert sum(ch["node"].visit_count for ch in child.children.values() if ch["node"] is not None) == child.visit_count - 1
+
+
+def test_agent_plays_a_legal_game_against_the_oracle_env():
+    import muzero_go_b200 as mz
+    n = 5
+    agent = mz.MuZeroAgent(n, 16, n * n + 1, 20)
+    env = gymgo.GoEnv(n)
+    obs, done, moves = env.reset(), False, 0
+    while not done and moves < 30:
+        if moves % 2 == 0:
+            a = agent.select_action(obs)
+        else:
+            a, pol, rv = agent.select_action(obs, 1.0)
+            assert pol.shape == (n * n + 1,) and abs(pol.sum() - 1) < 1e-9
+        assert env.valid_moves()[a] == 1
+        obs, _, done, _ = env.step(a)
+        moves += 1
+    assert moves > 4
+
+
+@pytest.mark.parametrize("n,c,G,S,precision", [(5, 16, 64, 12, "fp32"), (9, 128, 32, 20, "fp32"), (9, 128, 32, 20, "bf16")])
+def test_engine_invariants(n, c, G, S, precision):
+    import muzero_go_b200 as mz
+    _, net = make_net(n, c, 5, precision)
+    T = 2 * int(n * n * 1.5) + 6
+    eng = mz.SelfPlayEngine(net, n, G, S, traj_capacity=T, restart_finished=True)
+    eng.run(T)
+    torch.cuda.synchronize()
+    ctr = eng.read_counters()
+    assert ctr["moves"] == G * T
+    assert ctr["simulations"] + ctr["dropped_simulations"] == G * T * S
+    assert ctr["games_finished"] >= G          # every slot finished at least one game and restarted
+    act = eng.traj_action.cpu().numpy()
+    pol = eng.traj_policy.cpu().numpy()
+    done = eng.traj_done.cpu().numpy()
+    rows = eng.traj_boards.cpu().numpy().view(np.uint32)
+    assert act.min() >= 0 and act.max() <= n * n
+    np.testing.assert_allclose(pol.sum(axis=2), 1.0, atol=1e-5)
+    # replay every recorded game through the oracle rules: positions before each move must match
+    for g in range(min(G, 8)):
+        st = gymgo.init_state(n)
+        count, passes = 0, 0
+        for t in range(T):
+            r = rows[t, g]
+            black = np.array([[(r[i] >> j) & 1 for j in range(n)] for i in range(n)])
+            white = np.array([[(r[n + i] >> j) & 1 for j in range(n)] for i in range(n)])
+            inv = np.array([[(r[2 * n + i] >> j) & 1 for j in range(n)] for i in range(n)])
+            assert np.array_equal(black, st[0]) and np.array_equal(white, st[1]) and np.array_equal(inv, st[3]), (g, t)
+            a = int(act[t, g])
+            assert gymgo.valid_moves(st)[a] == 1
+            assert pol[t, g, a] > 0
+            st = gymgo.next_state(st, a)
+            count += 1
+            passes = passes + 1 if a == n * n else 0
+            over = bool(gymgo.game_ended(st)) or passes >= 2 or count >= int(n * n * 1.5)
+            assert bool(done[t, g]) == over
+            if over:
+                if gymgo.game_ended(st):
+                    assert int(eng.traj_winner[t, g]) == int(gymgo.winning(st))
+                st, count, passes = gymgo.init_state(n), 0, 0
+
+
+def test_engine_equals_stepwise_api():
+    """mzgo_selfplay_run is the composition of the exported pieces: same seed => same moves as driving
+    net/tree/rules call by call from Python."""
+    import muzero_go_b200 as mz
+    from muzero_go_b200 import _lib
+    n, c, G, S = 5, 16, 16, 10
+    _, net = make_net(n, c, 9)
+    cfg = mz.SearchConfig(seed=1234)
+    eng = mz.SelfPlayEngine(net, n, G, S, search=cfg, traj_capacity=6, restart_finished=True)
+    eng.run(6)
+    torch.cuda.synchronize()
+    # step by step
+    A, M = n * n + 1, S + 1
+    dev = torch.device("cuda")
+    boards = mz.GoBoards(G, n).reset()
+    tree = mz.Tree(G, A, M)
+    arena = net.new_arena(G * M)
+    d = net.descriptor(G)
+    L, s = _lib.load(), _lib.stream_ptr()
+    roots = (torch.arange(G, dtype=torch.int32, device=dev) * M).contiguous()
+    val = torch.empty(G, device=dev)
+    pol = torch.empty((G, A), device=dev)
+    rew = torch.empty(G, device=dev)
+    for t in range(6):
+        _lib.check(L.mzgo_net_initial(d, None, _lib.ptr(boards.records), _lib.ptr(arena), _lib.ptr(roots),
+                                      _lib.ptr(val), _lib.ptr(pol), 1, G, s))
+        tree.reset_roots(cfg, pol, boards, n, noise=None, move_index=t)
+        for _ in range(S):
+            tree.select(cfg, None)
+            _lib.check(L.mzgo_net_recurrent(d, _lib.ptr(arena), _lib.ptr(tree.leaf_in_slot), _lib.ptr(tree.leaf_action),
+                                            _lib.ptr(tree.leaf_out_slot), _lib.ptr(rew), _lib.ptr(val), _lib.ptr(pol),
+                                            1, G, s))
+            tree.expand_backup(cfg, pol, rew, val)
+        action, policy, _ = tree.choose_action(cfg, 0.0, move_index=t)
+        assert torch.equal(action, eng.traj_action[t]), t
+        assert torch.equal(policy, eng.traj_policy[t])
+        boards.step(action)

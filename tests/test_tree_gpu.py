@@ -1,0 +1,149 @@
+"""GPU: the SoA MCTS kernels (through the C ABI) against (a) the golden fixtures produced by the real
+reference MCTS (oracle/make_golden.py) and (b) the oracle restatement on fresh random tables, with
+identical float32 network outputs injected on both sides.  Everything is bit-exact."""
+import glob
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import mcts_ref
+
+pytestmark = pytest.mark.gpu
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+MAIN_LIKE = sorted(glob.glob(os.path.join(GOLDEN, "mcts_main_*.npz")) + glob.glob(os.path.join(GOLDEN, "mcts_play_*.npz")))
+
+
+def run_gpu_search(n, obs_list, init_soft, soft, rewards, values, noise, streams, sims, cfg):
+    """G independent searches in lock step; soft/rewards/values are per-game call-indexed tables
+    ([G][sims][A], [G][sims], [G][sims]), consumed in the order each game's simulations complete."""
+    import muzero_go_b200 as mz
+    G, A = len(obs_list), n * n + 1
+    dev = torch.device("cuda")
+    boards = mz.GoBoards(G, n).load_planes(np.stack(obs_list).astype(np.float32))
+    tree = mz.Tree(G, A, sims + 1)
+    tree.reset_roots(cfg, torch.from_numpy(np.stack(init_soft)).to(dev), boards, n, noise=np.stack(noise))
+    stream_t = mz.Tree.stream_tensor(np.stack(streams), dev)
+    soft_t = torch.from_numpy(np.stack(soft)).to(dev)            # [G][sims][A]
+    rew_t = torch.from_numpy(np.stack(rewards)).to(dev)
+    val_t = torch.from_numpy(np.stack(values)).to(dev)
+    calls = torch.zeros(G, dtype=torch.int64, device=dev)
+    gi = torch.arange(G, device=dev)
+    depths = [[] for _ in range(G)]
+    for _ in range(sims):
+        tree.select(cfg, stream_t)
+        live = tree.leaf_action >= 0
+        idx = calls.clamp(max=sims - 1)
+        tree.expand_backup(cfg, soft_t[gi, idx].contiguous(), rew_t[gi, idx].contiguous(), val_t[gi, idx].contiguous())
+        calls += live.long()
+        d = tree.leaf_depth.cpu().numpy()
+        for g in np.nonzero(live.cpu().numpy())[0]:
+            depths[g].append(int(d[g]))
+    return tree, depths
+
+
+def cfg_from_fixture(g):
+    import muzero_go_b200 as mz
+    c = float(g["c_puct"])
+    return mz.SearchConfig(c_puct=int(c) if bool(g["c_puct_is_int"]) else c, discount=float(g["discount"]),
+                           dirichlet_epsilon=float(g["dirichlet_epsilon"]), pass_epsilon=float(g["pass_epsilon"]))
+
+
+@pytest.mark.parametrize("path", MAIN_LIKE, ids=os.path.basename)
+def test_visit_counts_bit_exact_vs_reference_fixture(path):
+    g = np.load(path)
+    n, sims = int(g["n"]), int(g["sims"])
+    cfg = cfg_from_fixture(g)
+    # two copies of the same game in one batch: lock-step batching must not couple games
+    tree, depths = run_gpu_search(n, [g["obs"]] * 2, [g["init_soft"]] * 2, [g["soft"]] * 2, [g["rewards"]] * 2,
+                                  [g["values"]] * 2, [g["noise"]] * 2, [g["stream"]] * 2, sims, cfg)
+    for k in range(2):
+        assert np.array_equal(tree.root_prior[k].cpu().numpy(), g["root_prior"]), "root priors (float64) differ"
+        assert np.array_equal(tree.edge_visit[k, 0].cpu().numpy().astype(np.int64), g["visit"])
+        assert np.array_equal(tree.visit_counts()[k].cpu().numpy().astype(np.int64), g["visit"] * (g["root_prior"] > 0))
+        assert int(tree.root_visit[k]) == int(g["root_visit"])
+        assert float(tree.root_vsum[k]) == float(g["root_value_sum"])
+        assert np.array_equal(tree.edge_vsum[k, 0].cpu().numpy(), g["child_value_sum"])
+        assert np.array_equal(np.array(depths[k]), g["sel_depth"][g["sel_action"] >= 0])
+        assert int(tree.dropped[k]) == int((g["sel_action"] < 0).sum())
+
+
+@pytest.mark.parametrize("n,sims,G,c_puct", [(5, 120, 6, 2), (9, 260, 4, 2), (9, 150, 3, 10.0), (19, 500, 2, 2)])
+def test_batched_search_matches_oracle_on_random_tables(n, sims, G, c_puct):
+    """Different positions / tables per game; also exercises games whose simulations get dropped."""
+    import muzero_go_b200 as mz
+    from oracle.make_golden import midgame_obs
+    A = n * n + 1
+    rng = np.random.default_rng(1000 + n + sims)
+    cfg = mz.SearchConfig(c_puct=c_puct, discount=0.99, dirichlet_epsilon=0.25, pass_epsilon=0.05)
+    obs, init_soft, soft, rew, val, noise, streams, trees = [], [], [], [], [], [], [], []
+    for k in range(G):
+        o = midgame_obs(n, plies=int(rng.integers(0, n * n)), seed=int(rng.integers(1 << 30)))
+        if k == G - 1:           # an almost-finished position: few legal points, some simulations dropped
+            o = o.copy()
+            o[3] = 1
+            o[3].flat[int(rng.integers(n * n))] = 0
+        il = rng.normal(0, 1.5, A).astype(np.float32)
+        lg = rng.normal(0, 2.0, (sims, A)).astype(np.float32)
+        obs.append(o)
+        init_soft.append(torch.softmax(torch.from_numpy(il).view(1, -1), dim=1).numpy()[0])
+        soft.append(torch.softmax(torch.from_numpy(lg), dim=1).numpy())
+        rew.append(rng.normal(0, 0.1, sims).astype(np.float32))
+        val.append(rng.normal(0, 0.5, sims).astype(np.float32))
+        noise.append(rng.dirichlet([0.3] * A))
+        streams.append(rng.integers(0, 2 ** 32, size=sims + 8, dtype=np.uint64).astype(np.uint32))
+        calls = [0]
+
+        def recurrent(latent, action, k=k, calls=calls):
+            i = calls[0]
+            calls[0] += 1
+            return None, rew[k][i], val[k][i], soft[k][i]
+        t, mask = mcts_ref.run_mcts(o, lambda ob, k=k: (None, np.float32(0), init_soft[k]), recurrent, sims, noise[k],
+                                    streams[k], c_puct=c_puct, discount=0.99, dirichlet_epsilon=0.25, pass_epsilon=0.05)
+        trees.append((t, mask))
+    tree, depths = run_gpu_search(n, obs, init_soft, soft, rew, val, noise, streams, sims, cfg)
+    vc = tree.visit_counts().cpu().numpy()
+    for k, (t, mask) in enumerate(trees):
+        assert np.array_equal(tree.root_prior[k].cpu().numpy(), np.asarray(t.prior[0], dtype=np.float64))
+        assert np.array_equal(vc[k], t.root_visit_counts(mask)), f"game {k}"
+        assert np.array_equal(tree.edge_vsum[k, 0].cpu().numpy(), t.root_child_value_sums())
+        assert int(tree.root_visit[k]) == t.visit[0] and int(tree.dropped[k]) == t.dropped
+        assert depths[k] == t.depths
+        assert int(tree.n_nodes[k]) == len(t.visit)
+    # action choice, main.py:670-677
+    action, policy, root_value = tree.choose_action(cfg)
+    for k, (t, mask) in enumerate(trees):
+        a_ref, pol_ref = mcts_ref.choose_action(t.root_visit_counts(mask), mask)
+        if t.root_visit_counts(mask).sum() > 0:
+            assert int(action[k]) == a_ref
+            np.testing.assert_allclose(policy[k].cpu().numpy(), pol_ref, rtol=1e-6, atol=1e-7)
+        else:
+            assert mask[int(action[k])] > 0
+        assert float(root_value[k]) == pytest.approx(t.q(0), rel=1e-6, abs=1e-7)
+
+
+def test_idle_trees_are_left_alone():
+    import muzero_go_b200 as mz
+    n, G, sims = 5, 4, 20
+    A = n * n + 1
+    dev = torch.device("cuda")
+    cfg = mz.SearchConfig()
+    boards = mz.GoBoards(G, n).reset()
+    tree = mz.Tree(G, A, sims + 1)
+    tree.active[1] = 0
+    soft = torch.full((G, A), 1.0 / A, device=dev)
+    tree.reset_roots(cfg, soft, boards, n, noise=None, move_index=3)     # device Dirichlet sampler
+    rp = tree.root_prior.cpu().numpy()
+    assert np.all(rp[0] > 0) and abs(rp[0].sum() - 1.0) < 1e-3 and np.all(rp[1] == 0)
+    z = torch.zeros(G, device=dev)
+    for _ in range(sims):
+        tree.select(cfg, None)                                           # device RNG for random.choice
+        tree.expand_backup(cfg, soft, z, z)
+    assert tree.root_visit.cpu().tolist() == [sims, 0, sims, sims]
+    action, policy, _ = tree.choose_action(cfg)
+    assert int(action[1]) == -1 and float(policy[1].sum()) == 0.0
+    assert all(0 <= int(action[k]) < A for k in (0, 2, 3))
+    # Dirichlet noise: the mixed-in part sums to epsilon and differs between games
+    assert np.all(rp[[0, 2, 3]] >= 0)
+    assert not np.allclose(rp[0], rp[2])
