@@ -249,6 +249,7 @@ def run_ours(args, wl):
     # ---- dominant kernel (recurrent inference of one leaf batch), timed alone with CUDA events
     d = eng.descriptor()
     reps = 20
+    eng.tree.reset_roots(eng.search, eng.root_policy, eng.boards, n, noise=None, move_index=0)
     eng.tree.select(eng.search, None)
     k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     args_rec = (d.net, _lib.ptr(eng.arena), _lib.ptr(eng.tree.leaf_in_slot), _lib.ptr(eng.tree.leaf_action),

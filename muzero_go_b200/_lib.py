@@ -140,3 +140,12 @@ def ptr(t):
 def stream_ptr():
     import torch
     return torch.cuda.current_stream().cuda_stream
+
+
+def norm_device(device):
+    """torch.device with an explicit index ('cuda' -> 'cuda:<current>'), so device comparisons are exact."""
+    import torch
+    d = torch.device(device)
+    if d.type == "cuda" and d.index is None:
+        d = torch.device("cuda", torch.cuda.current_device())
+    return d

@@ -8,6 +8,7 @@ struct NetWorkspace {          // byte offsets into mzgo_net_t::workspace
     long act3;                 // bf16 mode: float32 [max_batch][C][n*n] representation output before packing
     long tc_w;                 // bf16 mode: dynamics conv weights in UMMA canonical layout
     long tc_embbias;           // bf16 mode: float32 [A][9][C] per-action, per-border-class bias (embedding folded in)
+    long tc_headw;             // bf16 mode: float32 [3][C] policy / value / reward 1x1 conv weights
     long total;
 };
 
@@ -33,8 +34,6 @@ int mzgo_tc_pack_latent(const mzgo_net_t* net, const float* src, long src_stride
                         int B, cudaStream_t st);
 int mzgo_tc_unpack_latent(const mzgo_net_t* net, const void* arena, const int32_t* slot, float* dst, long dst_stride,
                           int B, cudaStream_t st);
-int mzgo_tc_heads(const mzgo_net_t* net, const void* arena, const int32_t* slot, float* value, float* policy,
-                  int want_softmax, int B, cudaStream_t st);
 int mzgo_tc_recurrent(const mzgo_net_t* net, void* arena, const int32_t* in_slot, const int32_t* action,
                       const int32_t* out_slot, float* reward, float* value, float* policy, int want_softmax, int B,
                       cudaStream_t st);

@@ -243,6 +243,7 @@ NetWorkspace mzgo_net_layout(int n, int C, int precision, int max_batch) {
     w.act3 = precision == 1 ? take((long)max_batch * C * n * n * 4) : 0;
     w.tc_w = precision == 1 ? take((long)C * 9 * C * 2) : 0;
     w.tc_embbias = precision == 1 ? take((long)(n * n + 1) * 9 * C * 4) : 0;
+    w.tc_headw = precision == 1 ? take(3L * C * 4) : 0;
     w.total = o;
     return w;
 }

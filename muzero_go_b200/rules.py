@@ -34,7 +34,7 @@ class GoBoards:
         if not 2 <= size <= _lib.MAX_N:
             raise ValueError(f"board size {size} outside [2,{_lib.MAX_N}]")
         self.num, self.size = int(num), int(size)
-        self.device = torch.device(device)
+        self.device = _lib.norm_device(device)
         self.records = torch.zeros((self.num, _lib.BOARD_WORDS), dtype=torch.int32, device=self.device)
 
     @property

@@ -30,7 +30,7 @@ class SelfPlayEngine:
         self.A = self.n * self.n + 1
         self.M = self.S + 1
         self.search = search or SearchConfig()
-        dev = self.device = torch.device(device) if device is not None else net.prediction.pass_logit.device
+        dev = self.device = _lib.norm_device(device if device is not None else net.prediction.pass_logit.device)
         self.max_game_moves = int(self.n * self.n * 1.5) if max_game_moves is None else int(max_game_moves)  # main.py:53
         self.temperature, self.temperature_moves = float(temperature), int(temperature_moves)
         self.komi, self.restart_finished = float(komi), bool(restart_finished)

@@ -46,7 +46,7 @@ class Tree:
         if not 2 <= M <= 32767:
             raise ValueError("capacity outside [2,32767]")
         self.G, self.A, self.M = G, A, M
-        dev = self.device = torch.device(device)
+        dev = self.device = _lib.norm_device(device)
 
         def z(shape, dtype):
             return torch.zeros(shape, dtype=dtype, device=dev)
