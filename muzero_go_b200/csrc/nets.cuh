@@ -8,7 +8,9 @@ struct NetWorkspace {          // byte offsets into mzgo_net_t::workspace
     long act3;                 // bf16 mode: float32 [max_batch][C][n*n] representation output before packing
     long tc_w;                 // bf16 mode: dynamics conv weights in UMMA canonical layout
     long tc_embbias;           // bf16 mode: float32 [A][9][C] per-action, per-border-class bias (embedding folded in)
-    long tc_headw;             // bf16 mode: float32 [3][C] policy / value / reward 1x1 conv weights
+    long tc_headw;             // bf16 mode: float32 [3][C] policy / value / reward 1x1 conv weights + 56 head scalars
+    long tc_w2, tc_w3;         // bf16 mode: representation conv2 / conv3 weights in UMMA canonical layout
+    long tc_act1, tc_act2;     // bf16 mode: bf16 [max_batch][8][PS][8] representation activations (zero padded)
     long total;
 };
 
@@ -34,6 +36,8 @@ int mzgo_tc_pack_latent(const mzgo_net_t* net, const float* src, long src_stride
                         int B, cudaStream_t st);
 int mzgo_tc_unpack_latent(const mzgo_net_t* net, const void* arena, const int32_t* slot, float* dst, long dst_stride,
                           int B, cudaStream_t st);
+int mzgo_tc_initial(const mzgo_net_t* net, const float* obs, const uint32_t* boards, void* arena,
+                    const int32_t* out_slot, float* value, float* policy, int want_softmax, int B, cudaStream_t st);
 int mzgo_tc_recurrent(const mzgo_net_t* net, void* arena, const int32_t* in_slot, const int32_t* action,
                       const int32_t* out_slot, float* reward, float* value, float* policy, int want_softmax, int B,
                       cudaStream_t st);

@@ -27,12 +27,7 @@ extern "C" int mzgo_net_initial(const mzgo_net_t* net, const float* obs, const u
         return mzgo_heads_fp32(net, (const float*)arena, out_slot, nullptr, stride, nullptr, value, policy,
                                want_softmax, B, st);
     }
-    NetWorkspace w = mzgo_net_layout(net->n, net->C, net->precision, net->max_batch);
-    float* act3 = (float*)((char*)net->workspace + w.act3);
-    if (int e = mzgo_rep_fp32(net, obs, boards, act3, nullptr, net->C * np, B, st)) return e;
-    if (int e = mzgo_tc_pack_latent(net, act3, net->C * np, arena, out_slot, B, st)) return e;
-    // heads from the float32 activations (before bf16 rounding), like the fused epilogue of the recurrent kernel
-    return mzgo_heads_fp32(net, act3, nullptr, out_slot, net->C * np, nullptr, value, policy, want_softmax, B, st);
+    return mzgo_tc_initial(net, obs, boards, arena, out_slot, value, policy, want_softmax, B, st);
 }
 
 extern "C" int mzgo_net_recurrent(const mzgo_net_t* net, void* arena, const int32_t* in_slot, const int32_t* action,

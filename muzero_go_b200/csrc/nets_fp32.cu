@@ -238,12 +238,18 @@ NetWorkspace mzgo_net_layout(int n, int C, int precision, int max_batch) {
     w.wT2 = take(64L * 9 * 64 * 4);
     w.wT3 = take(64L * 9 * C * 4);
     w.wTd = take((long)C * 9 * C * 4);
-    w.act1 = take((long)max_batch * 64 * n * n * 4);
-    w.act2 = take((long)max_batch * 64 * n * n * 4);
-    w.act3 = precision == 1 ? take((long)max_batch * C * n * n * 4) : 0;
+    // float32 activations of the representation network: fp32 mode only (bf16 mode keeps bf16 slabs)
+    w.act1 = precision == 0 ? take((long)max_batch * 64 * n * n * 4) : 0;
+    w.act2 = precision == 0 ? take((long)max_batch * 64 * n * n * 4) : 0;
+    w.act3 = precision == 1 ? take((long)max_batch * C * n * n * 4) : 0;      // mzgo_net_predict staging
     w.tc_w = precision == 1 ? take((long)C * 9 * C * 2) : 0;
     w.tc_embbias = precision == 1 ? take((long)(n * n + 1) * 9 * C * 4) : 0;
-    w.tc_headw = precision == 1 ? take(3L * C * 4) : 0;
+    w.tc_headw = precision == 1 ? take((3L * C + 56) * 4) : 0;
+    w.tc_w2 = precision == 1 ? take(64L * 9 * 64 * 2) : 0;
+    w.tc_w3 = precision == 1 ? take(64L * 9 * C * 2) : 0;
+    const long slab64 = 8L * ((n + 2) * (n + 1) + 2) * 16;
+    w.tc_act1 = precision == 1 ? take(slab64 * max_batch) : 0;
+    w.tc_act2 = precision == 1 ? take(slab64 * max_batch) : 0;
     w.total = o;
     return w;
 }

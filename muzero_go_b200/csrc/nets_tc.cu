@@ -1,35 +1,43 @@
-// bf16 / tcgen05 path of the networks: the dynamics conv3x3 (the dominant cost of every simulation,
-// /root/reference/main.py:96-106) as an implicit GEMM on the 5th-generation tensor cores, fused with the
-// reward head, the prediction heads (main.py:116-125) and the softmax of main.py:298.
+// bf16 / tcgen05 path of the networks: every 3x3 convolution with >= 64 input channels -- the dynamics
+// conv (the dominant cost of every simulation, /root/reference/main.py:96-106) and conv2 / conv3 of the
+// representation network (main.py:80-84) -- as an implicit GEMM on the 5th-generation tensor cores,
+// fused with the reward head, the prediction heads (main.py:116-125) and the softmax of main.py:298.
 //
-// Formulation.  A latent lives in the arena as bf16 [C/8][PS][8]: 8-channel chunks, each a run of PS
+// Formulation.  A latent lives in HBM as bf16 [C/8][PS][8]: 8-channel chunks, each a run of PS
 // zero-padded flat positions with row stride n+1 (pixel (r,c) at q = (r+1)(n+1)+c+1, one shared zero
 // column between rows, one zero row above and below).  With that layout
-//   * a whole latent is ONE contiguous blob: one cp.async.bulk (TMA bulk copy, SASS UBLKCP) brings it
+//   * a whole latent is ONE contiguous blob: cp.async.bulk (TMA bulk copy, SASS UBLKCP) brings it
 //     into shared memory exactly in the UMMA "K-major, no swizzle" canonical layout
 //     (8 rows x 16 B core matrices, SBO = 128 B, LBO = PS*16 B);
-//   * the 9 taps of the convolution are the SAME shared-memory slab read through 9 descriptors whose
+//   * the 9 taps of the convolution are the SAME shared-memory slab read through descriptors whose
 //     start address is shifted by (dy*(n+1)+dx)*16 B -- no im2col, the slab is read from L2 once;
-//   * M tile = 128 consecutive flat positions, N = 128 output channels, K = 9 taps x 128 channels;
-//     accumulators (up to 4 tiles x 128 fp32 columns) live in TMEM.
+//   * M tile = 128 consecutive flat positions, N = Cout output channels, K = 9 taps x Cin channels;
+//     accumulators live in four 128-column TMEM slots that rotate from group to group, so the MMAs of
+//     the next group start on the free slot while the epilogue still drains the previous ones.
 // The action embedding (main.py:98-100) is linear in the conv, so it is folded at weight-load time into
 // a per-action, per-border-class bias table [A][9][C] (border pixels see fewer taps).
 //
-// Warp roles (192 threads): warp 0 TMA producer, warp 1 TMEM owner + MMA issuer, warps 2-5 epilogue
-// (tcgen05.ld -> bias/ReLU -> heads -> bf16 -> coalesced 16 B stores in the arena layout).
+// Warp roles (320 threads): warp 0 TMA producer (latent slab in two 64-channel halves, weight k-blocks
+// through an mbarrier ring), warp 1 TMEM owner + MMA issuer (descriptors precomputed, ~4 instructions
+// per tcgen05.mma), warps 2-9 epilogue (tcgen05.ld -> bias/ReLU -> heads with the 1x1 weights read as
+// kernel-parameter constants -> bf16 -> coalesced 16 B stores in the arena layout).
 #include <cuda_bf16.h>
+
+#include <mutex>
+#include <unordered_map>
 
 #include "nets.cuh"
 
 namespace {
 
 constexpr int TC_C = 128;               // latent_dim of the tensor-core path
-constexpr int TC_KC = TC_C / 8;         // 8-channel chunks
-constexpr int TC_THREADS = 192;
-constexpr int TC_STAGES = 4;            // weight k-block ring
-constexpr int TC_KBLOCKS = 18;          // 9 taps x 2 halves of 64 input channels
-constexpr int TC_BSTAGE_BYTES = 8 * 128 * 16;   // [8 chunks][128 out channels][8 in channels] bf16 = 16 KB
-constexpr int TC_MAX_TILES = 4;         // 4 x 128 TMEM columns
+constexpr int TC_THREADS = 320;
+constexpr int TC_EPI_THREADS = 256;
+constexpr int TC_MAX_STAGES = 8;        // weight k-block ring (as many as fit)
+constexpr int TC_SLOTS = 4;             // 4 x 128 TMEM columns
+constexpr int TC_SMEM_LIMIT = 232448;   // 227 KB
+
+enum { MODE_PLAIN = 0, MODE_HEADS = 1, MODE_DYN = 2 };
 
 __host__ __device__ inline int tc_ps(int n) { return (n + 2) * (n + 1) + 2; }
 __host__ __device__ inline int tc_tiles_per_image(int n) { return (n * (n + 1) + 127) / 128; }
@@ -74,26 +82,31 @@ __device__ __forceinline__ void umma_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
                  : "memory");
 }
-// D[tmem] (+)= A[smem] * B[smem]^T, bf16 x bf16 -> fp32, M=128 N=128 K=16
-__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+// D[tmem] (+)= A[smem] * B[smem]^T, bf16 x bf16 -> fp32, M=128, N from idesc, K=16.
+// Descriptors are passed as (lo, hi) words: only lo (start address, LBO) changes between MMAs.
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi,
+                                          uint32_t idesc, uint32_t acc) {
     asm volatile(
         "{\n\t"
         ".reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
-        "}" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc) : "memory");
+        ".reg .b64 da, db;\n\t"
+        "mov.b64 da, {%1, %2};\n\t"
+        "mov.b64 db, {%3, %4};\n\t"
+        "setp.ne.b32 p, %6, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, p;\n\t"
+        "}" ::"r"(tmem_d), "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(acc) : "memory");
 }
-// K-major, SWIZZLE_NONE shared-memory matrix descriptor (cute::UMMA::SmemDescriptor bit layout)
-__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
-    uint64_t d = 0;
-    d |= (uint64_t)((saddr >> 4) & 0x3FFF);
-    d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
-    d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
-    d |= (uint64_t)1 << 46;   // descriptor version (Blackwell)
-    return d;                 // base_offset 0, lbo_mode 0, layout_type 0 = no swizzle
+// K-major, SWIZZLE_NONE shared-memory matrix descriptor (cute::UMMA::SmemDescriptor bit layout):
+//   lo = start address >> 4 (14 bits) | leading-dimension byte offset >> 4 << 16
+//   hi = stride-dimension byte offset >> 4 | descriptor version 1 at bit 46
+__device__ __forceinline__ uint32_t desc_lo(uint32_t saddr, uint32_t lbo_bytes) {
+    return ((saddr >> 4) & 0x3FFFu) | (((lbo_bytes >> 4) & 0x3FFFu) << 16);
 }
-// kind::f16 instruction descriptor: D fp32, A/B bf16, both K-major, N=128, M=128
-constexpr uint32_t TC_IDESC = (1u << 4) | (1u << 7) | (1u << 10) | ((128u >> 3) << 17) | ((128u >> 4) << 24);
+__device__ __forceinline__ uint32_t desc_hi(uint32_t sbo_bytes) { return ((sbo_bytes >> 4) & 0x3FFFu) | (1u << 14); }
+// kind::f16 instruction descriptor: D fp32, A/B bf16, both K-major, M=128
+__host__ __device__ constexpr uint32_t tc_idesc(int n_cols) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n_cols >> 3) << 17) | ((128u >> 4) << 24);
+}
 
 #define TMEM_LD_32X32B_X32(taddr, r)                                                                                  \
     asm volatile(                                                                                                     \
@@ -106,83 +119,136 @@ constexpr uint32_t TC_IDESC = (1u << 4) | (1u << 7) | (1u << 10) | ((128u >> 3) 
           "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])                   \
         : "r"(taddr))
 
+struct TcScalars {   // the scalar head parameters (main.py:93-94, :111-114), host copies
+    float pol_b, val_b, rew_b, vfc_w, vfc_b, pass_logit, ro_b, pad;
+    float rh_w[16], rh_b[16], ro_w[16];
+};
+
 struct TcArgs {
-    const __nv_bfloat16* arena_in;
-    __nv_bfloat16* arena_out;
-    const int32_t* in_slot;
-    const int32_t* action;
-    const int32_t* out_slot;
-    const __nv_bfloat16* wB;     // [18][8][128][8]
-    const float* tbl;            // [A][9][128]: conv bias + embedding contribution per border class
-    const float* head_w;         // [3][128]: policy, value, reward 1x1 conv weights
-    mzgo_net_t net;              // scalar head parameters are read through the reference pointers
+    const __nv_bfloat16* in;     // input slabs: item i at in + in_slot(i) * (CIN/8)*ps*8
+    __nv_bfloat16* out;          // output slabs: item i at out + out_slot(i) * (COUT/8)*ps*8
+    const int32_t* in_slot;      // optional (identity when NULL)
+    const int32_t* out_slot;     // optional (identity when NULL); < 0 skips the item
+    const int32_t* action;       // MODE_DYN: table row; < 0 skips the item.  Otherwise optional gate.
+    const __nv_bfloat16* wB;     // [9*CIN/64][8][COUT][8]
+    const float* tbl;            // MODE_DYN: [A][9][COUT] bias table; otherwise [COUT] bias
     float* reward;
     float* value;
     float* policy;
     int want_softmax;
     int B;                       // items
-    int n, ps, tiles_per_image, images_per_group, num_groups;
+    int n, ps, tiles_per_image, images_per_group, num_groups, stages;
+    TcScalars sc;
+    float hw[3 * TC_C];          // policy / value / reward 1x1 conv weights: read as constant-bank operands
 };
 
 struct TcSmemLayout {
-    uint32_t a_bytes, b_off, tbl_off, headw_off, logit_off, part_off, bar_off, total;
+    uint32_t a_bytes, b_off, tbl_off, pol_off, part_off, bar_off, total;
 };
-__host__ __device__ inline TcSmemLayout tc_smem_layout(int n) {
+__host__ __device__ inline TcSmemLayout tc_smem_layout(int n, int cin, int cout, int stages) {
     TcSmemLayout L;
-    const int tiles = tc_tiles_per_image(n), images = TC_MAX_TILES / tiles;
-    L.a_bytes = (uint32_t)images * TC_KC * tc_ps(n) * 16;
+    const int tiles = tc_tiles_per_image(n), images = TC_SLOTS / tiles;
+    L.a_bytes = (uint32_t)images * (cin / 8) * tc_ps(n) * 16;
     L.b_off = (L.a_bytes + 127) / 128 * 128;
-    L.tbl_off = L.b_off + TC_STAGES * TC_BSTAGE_BYTES;
-    L.headw_off = L.tbl_off + (uint32_t)images * 9 * TC_C * 4;
-    L.logit_off = L.headw_off + 3 * TC_C * 4;
-    L.part_off = L.logit_off + (uint32_t)images * 384 * 4;
-    L.bar_off = L.part_off + TC_MAX_TILES * 4 * 2 * 4;          // [tile][warp][value, reward] partial sums
-    L.total = L.bar_off + 16 * 8 + 16;
+    L.tbl_off = L.b_off + (uint32_t)stages * cout * 128;
+    L.pol_off = L.tbl_off + (uint32_t)images * 9 * cout * 4;
+    L.part_off = L.pol_off + 2u * images * 384 * 4;               // [column half][image][position] partial logits
+    L.bar_off = L.part_off + TC_SLOTS * 8 * 2 * 4;                // [tile][warp][value, reward] partial sums
+    L.total = L.bar_off + (4 + 2 * TC_SLOTS + 2 * TC_MAX_STAGES) * 8 + 16;
     return L;
 }
 
-__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
 
 __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
     __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
     return *reinterpret_cast<uint32_t*>(&v);
 }
 
+// ---------------------------------------------------------------------------------------- epilogue of one tile
+// One thread = one output position x COUT/2 channels (column half CHH of the accumulator tile).
+template <int COUT, int MODE, int CHH>
+__device__ __forceinline__ void tc_epilogue_tile(const TcArgs& a, uint32_t taddr, uint64_t* acc_empty_bar, bool live,
+                                                 const float* tb, uint4* dst, int ps, bool valid, bool store_ok,
+                                                 float& pol, float& val, float& rew) {
+    constexpr int CPT = COUT / 2;
+    constexpr int CH0 = CHH * CPT;
+    uint32_t rr[CPT];
+    if (live) {
+        TMEM_LD_32X32B_X32(taddr + CH0, rr);
+        if (CPT == 64) TMEM_LD_32X32B_X32(taddr + CH0 + 32, (rr + 32));
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+    }
+    // the accumulator now lives in registers: hand the TMEM slot back to the MMA warp at once
+    tc_fence_before();
+    __syncwarp();
+    if ((threadIdx.x & 31) == 0) mbar_arrive(acc_empty_bar);
+    if (!live) return;
+    pol = 0.f; val = 0.f; rew = 0.f;
+#pragma unroll
+    for (int k = 0; k < CPT / 8; k++) {
+        const float4 b0 = *reinterpret_cast<const float4*>(tb + CH0 + k * 8);
+        const float4 b1 = *reinterpret_cast<const float4*>(tb + CH0 + k * 8 + 4);
+        const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+        float x[8];
+#pragma unroll
+        for (int e = 0; e < 8; e++) {
+            x[e] = fmaxf(__uint_as_float(rr[k * 8 + e]) + bb[e], 0.f);
+            if (MODE != MODE_PLAIN) {
+                pol = fmaf(x[e], a.hw[CH0 + k * 8 + e], pol);
+                val = fmaf(x[e], a.hw[TC_C + CH0 + k * 8 + e], val);
+            }
+            if (MODE == MODE_DYN) rew = fmaf(x[e], a.hw[2 * TC_C + CH0 + k * 8 + e], rew);
+        }
+        if (store_ok) {
+            uint4 w;
+            w.x = pack_bf16(x[0], x[1]);
+            w.y = pack_bf16(x[2], x[3]);
+            w.z = pack_bf16(x[4], x[5]);
+            w.w = pack_bf16(x[6], x[7]);
+            if (!valid) w = make_uint4(0u, 0u, 0u, 0u);      // padding positions stay zero for the next conv
+            dst[(size_t)(CH0 / 8 + k) * ps] = w;
+        }
+    }
+    if (!valid) { val = 0.f; rew = 0.f; }
+}
+
 // ---------------------------------------------------------------------------------------- the fused kernel
+template <int CIN, int COUT, int MODE>
 __global__ void __launch_bounds__(TC_THREADS, 1)
-k_tc_recurrent(const TcArgs a) {
+k_tc_conv(const __grid_constant__ TcArgs a) {
+    constexpr int KC_IN = CIN / 8, KC_OUT = COUT / 8, NH = CIN / 64;
+    constexpr uint32_t STAGE_BYTES = COUT * 128;          // [8 chunks][COUT][8] bf16
+    constexpr uint32_t IDESC = tc_idesc(COUT);
     extern __shared__ __align__(128) uint8_t smem[];
-    const TcSmemLayout L = tc_smem_layout(a.n);
+    const TcSmemLayout L = tc_smem_layout(a.n, CIN, COUT, a.stages);
     uint8_t* sA = smem;
     uint8_t* sB = smem + L.b_off;
-    float* s_tbl = reinterpret_cast<float*>(smem + L.tbl_off);       // [images][9][128]
-    float* s_hw = reinterpret_cast<float*>(smem + L.headw_off);      // [3][128]
-    float* s_logit = reinterpret_cast<float*>(smem + L.logit_off);   // [images][384]
+    float* s_tbl = reinterpret_cast<float*>(smem + L.tbl_off);       // DYN: [images][9][COUT]; else [COUT]
+    float* s_pol = reinterpret_cast<float*>(smem + L.pol_off);       // [2][images][384]
     float* s_part = reinterpret_cast<float*>(smem + L.part_off);     // [tile][warp][2]
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L.bar_off);
-    uint64_t* a_full = bars + 0;
-    uint64_t* a_empty = bars + 1;
-    uint64_t* acc_full = bars + 2;
-    uint64_t* acc_empty = bars + 3;
-    uint64_t* b_full = bars + 4;                    // [TC_STAGES]
-    uint64_t* b_empty = bars + 4 + TC_STAGES;       // [TC_STAGES]
-    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 4 + 2 * TC_STAGES);
+    uint64_t* a_full = bars + 0;                    // [2] input slab halves
+    uint64_t* a_empty = bars + 2;                   // [2]
+    uint64_t* acc_full = bars + 4;                  // [TC_SLOTS]
+    uint64_t* acc_empty = bars + 4 + TC_SLOTS;      // [TC_SLOTS]
+    uint64_t* b_full = bars + 4 + 2 * TC_SLOTS;     // [TC_MAX_STAGES]
+    uint64_t* b_empty = b_full + TC_MAX_STAGES;     // [TC_MAX_STAGES]
+    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(b_empty + TC_MAX_STAGES);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n = a.n, ps = a.ps, np = n * n;
-    const int tpi = a.tiles_per_image, images = a.images_per_group;
-    const uint32_t slab_bytes = (uint32_t)TC_KC * ps * 16;
+    const int tpi = a.tiles_per_image, images = a.images_per_group, NT = images * tpi;
+    const uint32_t slab_bytes = (uint32_t)KC_IN * ps * 16;
+    const uint32_t half_bytes = slab_bytes / NH;
     const int q0 = n + 2;                           // flat position of pixel (0,0)
 
     if (threadIdx.x == 0) {
-        mbar_init(a_full, 1);
-        mbar_init(a_empty, 1);
-        mbar_init(acc_full, 1);
-        mbar_init(acc_empty, 4);
-        for (int s = 0; s < TC_STAGES; s++) { mbar_init(b_full + s, 1); mbar_init(b_empty + s, 1); }
+        for (int h = 0; h < 2; h++) { mbar_init(a_full + h, 1); mbar_init(a_empty + h, 1); }
+        for (int s = 0; s < TC_SLOTS; s++) { mbar_init(acc_full + s, 1); mbar_init(acc_empty + s, 8); }
+        for (int s = 0; s < TC_MAX_STAGES; s++) { mbar_init(b_full + s, 1); mbar_init(b_empty + s, 1); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    for (int i = threadIdx.x; i < 3 * TC_C; i += TC_THREADS) s_hw[i] = a.head_w[i];
     if (warp == 1) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(s_tmem)) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
@@ -192,12 +258,15 @@ k_tc_recurrent(const TcArgs a) {
     tc_fence_after();
     const uint32_t tmem_base = *s_tmem;
 
-    // which images of a group are live (action >= 0): every role evaluates this the same way
+    // which images of a group are live: every role evaluates this the same way
     auto live_mask = [&](int grp) -> uint32_t {
         uint32_t m = 0;
         for (int i = 0; i < images; i++) {
-            int item = grp * images + i;
-            if (item < a.B && a.action[item] >= 0 && a.in_slot[item] >= 0 && a.out_slot[item] >= 0) m |= 1u << i;
+            const int item = grp * images + i;
+            if (item >= a.B) break;
+            const bool ok = (!a.action || a.action[item] >= 0) && (!a.in_slot || a.in_slot[item] >= 0) &&
+                            (!a.out_slot || a.out_slot[item] >= 0);
+            if (ok) m |= 1u << i;
         }
         return m;
     };
@@ -205,24 +274,28 @@ k_tc_recurrent(const TcArgs a) {
     if (warp == 0) {
         // ===================================================== TMA producer
         if (lane == 0) {
-            uint32_t it = 0, kbc = 0;
+            uint32_t it = 0, s = 0, bph = 0;
             for (int grp = blockIdx.x; grp < a.num_groups; grp += gridDim.x) {
                 const uint32_t live = live_mask(grp);
                 if (!live) continue;
-                mbar_wait(a_empty, (it & 1) ^ 1);
-                mbar_expect_tx(a_full, slab_bytes * __popc(live));
-                for (int i = 0; i < images; i++) {
-                    if (!(live & (1u << i))) continue;
-                    const int item = grp * images + i;
-                    const uint8_t* src = reinterpret_cast<const uint8_t*>(a.arena_in) + (size_t)a.in_slot[item] * slab_bytes;
-                    bulk_g2s(sA + (size_t)i * slab_bytes, src, slab_bytes, a_full);
-                }
-                for (int kb = 0; kb < TC_KBLOCKS; kb++, kbc++) {
-                    const uint32_t s = kbc % TC_STAGES, ph = (kbc / TC_STAGES) & 1;
-                    mbar_wait(b_empty + s, ph ^ 1);
-                    mbar_expect_tx(b_full + s, TC_BSTAGE_BYTES);
-                    bulk_g2s(sB + s * TC_BSTAGE_BYTES, reinterpret_cast<const uint8_t*>(a.wB) + (size_t)kb * TC_BSTAGE_BYTES,
-                             TC_BSTAGE_BYTES, b_full + s);
+                for (int h = 0; h < NH; h++) {
+                    mbar_wait(a_empty + h, (it & 1) ^ 1);
+                    mbar_expect_tx(a_full + h, half_bytes * __popc(live));
+                    for (int i = 0; i < images; i++) {
+                        if (!(live & (1u << i))) continue;
+                        const int item = grp * images + i;
+                        const int slot = a.in_slot ? a.in_slot[item] : item;
+                        const uint8_t* src = reinterpret_cast<const uint8_t*>(a.in) + (size_t)slot * slab_bytes + (size_t)h * half_bytes;
+                        bulk_g2s(sA + (size_t)i * slab_bytes + (size_t)h * half_bytes, src, half_bytes, a_full + h);
+                    }
+                    for (int tap = 0; tap < 9; tap++) {
+                        mbar_wait(b_empty + s, bph ^ 1);
+                        mbar_expect_tx(b_full + s, STAGE_BYTES);
+                        bulk_g2s(sB + s * STAGE_BYTES,
+                                 reinterpret_cast<const uint8_t*>(a.wB) + (size_t)(h * 9 + tap) * STAGE_BYTES, STAGE_BYTES,
+                                 b_full + s);
+                        if (++s == (uint32_t)a.stages) { s = 0; bph ^= 1; }
+                    }
                 }
                 it++;
             }
@@ -230,138 +303,147 @@ k_tc_recurrent(const TcArgs a) {
     } else if (warp == 1) {
         // ===================================================== MMA issuer (one thread)
         if (lane == 0) {
-            uint32_t it = 0, kbc = 0;
-            const uint32_t sA_addr = smem_u32(sA), sB_addr = smem_u32(sB);
+            uint32_t it = 0, s = 0, bph = 0, tile_ctr = 0;
+            const uint32_t a_hi = desc_hi(128), b_hi = desc_hi(128);
+            const uint32_t b_lo0 = desc_lo(smem_u32(sB), COUT * 16);
+            uint32_t a_lo[TC_SLOTS];
+#pragma unroll
+            for (int j = 0; j < TC_SLOTS; j++) {
+                const int img = j / tpi, tt = j - img * tpi;
+                a_lo[j] = desc_lo(smem_u32(sA) + img * slab_bytes + (uint32_t)(q0 + tt * 128) * 16, ps * 16);
+            }
             for (int grp = blockIdx.x; grp < a.num_groups; grp += gridDim.x) {
                 const uint32_t live = live_mask(grp);
                 if (!live) continue;
-                mbar_wait(acc_empty, (it & 1) ^ 1);
-                mbar_wait(a_full, it & 1);
-                tc_fence_after();
-                for (int kb = 0; kb < TC_KBLOCKS; kb++, kbc++) {
-                    const uint32_t s = kbc % TC_STAGES, ph = (kbc / TC_STAGES) & 1;
-                    mbar_wait(b_full + s, ph);
-                    tc_fence_after();
-                    const int tap = kb >> 1, half = kb & 1;
-                    const int shift = (tap / 3 - 1) * (n + 1) + (tap % 3 - 1);
+                uint32_t d_col[TC_SLOTS];
 #pragma unroll
-                    for (int ks = 0; ks < 4; ks++) {
-                        const uint64_t bdesc = umma_desc(sB_addr + s * TC_BSTAGE_BYTES + ks * 2 * 128 * 16, 128 * 16, 128);
-                        const int chunk = half * 8 + ks * 2;
-                        for (int t = 0; t < images * tpi; t++) {
-                            const int img = t / tpi, tt = t - img * tpi;
-                            if (!(live & (1u << img))) continue;
-                            const uint32_t aaddr = sA_addr + img * slab_bytes + (uint32_t)chunk * ps * 16 +
-                                                   (uint32_t)(q0 + tt * 128 + shift) * 16;
-                            umma_bf16(tmem_base + t * 128, umma_desc(aaddr, ps * 16, 128), bdesc, TC_IDESC, (kb | ks) != 0);
+                for (int j = 0; j < TC_SLOTS; j++) d_col[j] = tmem_base + ((tile_ctr + j) & (TC_SLOTS - 1)) * 128;
+                for (int h = 0; h < NH; h++) {
+                    mbar_wait(a_full + h, it & 1);
+                    tc_fence_after();
+                    for (int tap = 0; tap < 9; tap++) {
+                        mbar_wait(b_full + s, bph);
+                        tc_fence_after();
+                        const int dy = (tap * 11) >> 5;                       // tap / 3 for tap < 9
+                        const int shift = (dy - 1) * (n + 1) + (tap - 3 * dy - 1);
+                        const uint32_t a_off = (uint32_t)(h * 8 * ps + shift);       // 16-byte units
+                        const uint32_t b_lo = b_lo0 + s * (STAGE_BYTES >> 4);
+                        const bool first = (h | tap) == 0;
+#pragma unroll
+                        for (int ks = 0; ks < 4; ks++) {
+#pragma unroll
+                            for (int j = 0; j < TC_SLOTS; j++) {
+                                if (j < NT) {
+                                    if (first && ks == 0) {     // first touch of this TMEM slot: the epilogue must have drained it
+                                        const uint32_t c = tile_ctr + j;
+                                        mbar_wait(acc_empty + (c & (TC_SLOTS - 1)), ((c >> 2) & 1) ^ 1);
+                                        tc_fence_after();
+                                    }
+                                    umma_bf16(d_col[j], a_lo[j] + a_off + ks * 2 * ps, a_hi, b_lo + ks * (2 * COUT), b_hi, IDESC,
+                                              (first && ks == 0) ? 0u : 1u);
+                                }
+                            }
                         }
+                        umma_commit(b_empty + s);     // frees the weight stage when these MMAs retire
+                        if (++s == (uint32_t)a.stages) { s = 0; bph ^= 1; }
                     }
-                    umma_commit(b_empty + s);     // frees the weight stage when these MMAs retire
+                    umma_commit(a_empty + h);         // this half of the input slab may be overwritten
                 }
-                umma_commit(a_empty);             // the latent slab may be overwritten
-                umma_commit(acc_full);            // accumulators complete
+                for (int j = 0; j < NT; j++) umma_commit(acc_full + ((tile_ctr + j) & (TC_SLOTS - 1)));
+                tile_ctr += NT;
                 it++;
             }
         }
     } else {
-        // ===================================================== epilogue (4 warps, TMEM lane quarter = warp % 4)
-        const int ew = warp - 2, wq = warp & 3;
-        const int et = threadIdx.x - 64;              // 0..127
-        uint32_t it = 0;
+        // ===================================================== epilogue (8 warps: TMEM lane quarter x column half)
+        const int ew = warp - 2, wq = warp & 3, chh = ew >> 2;
+        const int et = threadIdx.x - 64;              // 0..255
+        uint32_t tile_ctr = 0;
+        if (MODE != MODE_DYN) {
+            for (int k = et; k < COUT; k += TC_EPI_THREADS) s_tbl[k] = a.tbl[k];
+        }
         for (int grp = blockIdx.x; grp < a.num_groups; grp += gridDim.x) {
             const uint32_t live = live_mask(grp);
             if (!live) continue;
-            epi_bar_sync();                            // previous group's finalisation has read s_logit / s_part
-            for (int i = 0; i < images; i++) {
-                if (!(live & (1u << i))) continue;
-                const float* src = a.tbl + (size_t)a.action[grp * images + i] * 9 * TC_C;
-                for (int k = et; k < 9 * TC_C; k += 128) s_tbl[i * 9 * TC_C + k] = src[k];
+            epi_bar_sync();                            // previous group's finalisation has read s_pol / s_part / s_tbl
+            if (MODE == MODE_DYN) {
+                for (int i = 0; i < images; i++) {
+                    if (!(live & (1u << i))) continue;
+                    const float4* src = reinterpret_cast<const float4*>(a.tbl + (size_t)a.action[grp * images + i] * 9 * COUT);
+                    float4* dstt = reinterpret_cast<float4*>(s_tbl + i * 9 * COUT);
+                    for (int k = et; k < 9 * COUT / 4; k += TC_EPI_THREADS) dstt[k] = src[k];
+                }
             }
             epi_bar_sync();
-            mbar_wait(acc_full, it & 1);
-            tc_fence_after();
-            for (int t = 0; t < images * tpi; t++) {
-                const int img = t / tpi, tt = t - img * tpi;
-                if (!(live & (1u << img))) continue;
+            for (int j = 0; j < NT; j++) {
+                const int img = j / tpi, tt = j - img * tpi;
+                const uint32_t c = tile_ctr + j, slot = c & (TC_SLOTS - 1);
+                const bool is_live = (live >> img) & 1u;
                 const int item = grp * images + img;
                 const int o = tt * 128 + wq * 32 + lane;            // flat output row of this thread
-                const int r = o / (n + 1), c = o - r * (n + 1);
-                const bool valid = (r < n) && (c < n);
-                const int cls = (r == 0 ? 0 : (r == n - 1 ? 2 : 1)) * 3 + (c == 0 ? 0 : (c == n - 1 ? 2 : 1));
+                const int r = o / (n + 1), cc = o - r * (n + 1);
+                const bool valid = (r < n) && (cc < n);
+                const int cls = (r == 0 ? 0 : (r == n - 1 ? 2 : 1)) * 3 + (cc == 0 ? 0 : (cc == n - 1 ? 2 : 1));
                 const int q = q0 + o;
                 const bool store_ok = q < ps;
-                const float* tb = s_tbl + (img * 9 + (valid ? cls : 4)) * TC_C;
-                uint4* dst = reinterpret_cast<uint4*>(a.arena_out) + (size_t)a.out_slot[item] * TC_KC * ps + q;
-                float pol = 0.f, val = 0.f, rew = 0.f;
-#pragma unroll 1
-                for (int cc = 0; cc < 4; cc++) {
-                    uint32_t rr[32];
-                    TMEM_LD_32X32B_X32(tmem_base + ((uint32_t)(wq * 32) << 16) + t * 128 + cc * 32, rr);
-                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-                    float v[32];
-#pragma unroll
-                    for (int j = 0; j < 32; j++) {
-                        const int ch = cc * 32 + j;
-                        float x = fmaxf(__uint_as_float(rr[j]) + tb[ch], 0.f);
-                        x = valid ? x : 0.f;
-                        v[j] = x;
-                        pol = fmaf(x, s_hw[ch], pol);
-                        val = fmaf(x, s_hw[TC_C + ch], val);
-                        rew = fmaf(x, s_hw[2 * TC_C + ch], rew);
-                    }
-                    if (store_ok) {
-#pragma unroll
-                        for (int k = 0; k < 4; k++) {
-                            uint4 w;
-                            w.x = pack_bf16(v[k * 8 + 0], v[k * 8 + 1]);
-                            w.y = pack_bf16(v[k * 8 + 2], v[k * 8 + 3]);
-                            w.z = pack_bf16(v[k * 8 + 4], v[k * 8 + 5]);
-                            w.w = pack_bf16(v[k * 8 + 6], v[k * 8 + 7]);
-                            dst[(size_t)(cc * 4 + k) * ps] = w;
-                        }
-                    }
+                const float* tb = (MODE == MODE_DYN) ? s_tbl + (img * 9 + (valid ? cls : 4)) * COUT : s_tbl;
+                uint4* dst = nullptr;
+                if (is_live) {
+                    const int oslot = a.out_slot ? a.out_slot[item] : item;
+                    dst = reinterpret_cast<uint4*>(a.out) + (size_t)oslot * KC_OUT * ps + q;
                 }
-                if (valid) s_logit[img * 384 + r * n + c] = pol + a.net.pol_b[0];
-                val = warp_sum_f(val);
-                rew = warp_sum_f(rew);
-                if (lane == 0) { s_part[(t * 4 + ew) * 2] = val; s_part[(t * 4 + ew) * 2 + 1] = rew; }
+                mbar_wait(acc_full + slot, (c >> 2) & 1);
+                tc_fence_after();
+                const uint32_t taddr = tmem_base + ((uint32_t)(wq * 32) << 16) + slot * 128;
+                float pol, val, rew;
+                if (chh) tc_epilogue_tile<COUT, MODE, 1>(a, taddr, acc_empty + slot, is_live, tb, dst, ps, valid, store_ok, pol, val, rew);
+                else     tc_epilogue_tile<COUT, MODE, 0>(a, taddr, acc_empty + slot, is_live, tb, dst, ps, valid, store_ok, pol, val, rew);
+                if (MODE != MODE_PLAIN && is_live) {
+                    if (valid) s_pol[(chh * images + img) * 384 + r * n + cc] = pol;
+                    val = warp_sum_f(val);
+                    if (MODE == MODE_DYN) rew = warp_sum_f(rew);
+                    if (lane == 0) { s_part[(j * 8 + ew) * 2] = val; s_part[(j * 8 + ew) * 2 + 1] = rew; }
+                }
             }
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(acc_empty);     // TMEM may be overwritten by the next group
+            tile_ctr += NT;
+            if (MODE == MODE_PLAIN) continue;
             epi_bar_sync();
             // ---- per-image finalisation: value / reward heads and the policy softmax (one warp per image)
-            for (int img = ew; img < images; img += 4) {
+            for (int img = ew; img < images; img += 8) {
                 if (!(live & (1u << img))) continue;
                 const int item = grp * images + img;
                 float vs = 0.f, rs = 0.f;
                 for (int tt = 0; tt < tpi; tt++)
-                    for (int w = 0; w < 4; w++) { vs += s_part[((img * tpi + tt) * 4 + w) * 2]; rs += s_part[((img * tpi + tt) * 4 + w) * 2 + 1]; }
+                    for (int w = 0; w < 8; w++) { vs += s_part[((img * tpi + tt) * 8 + w) * 2]; rs += s_part[((img * tpi + tt) * 8 + w) * 2 + 1]; }
                 if (lane == 0) {
-                    const float vm = vs / (float)np + a.net.val_b[0];
-                    a.value[item] = fmaf(a.net.vfc_w[0], vm, a.net.vfc_b[0]);
-                    const float rm = rs / (float)np + a.net.rew_b[0];
-                    float rw = a.net.ro_b[0];
-                    for (int j = 0; j < 16; j++) rw = fmaf(a.net.ro_w[j], fmaxf(fmaf(a.net.rh_w[j], rm, a.net.rh_b[j]), 0.f), rw);
-                    a.reward[item] = rw;
+                    const float vm = vs / (float)np + a.sc.val_b;
+                    a.value[item] = fmaf(a.sc.vfc_w, vm, a.sc.vfc_b);
+                    if (MODE == MODE_DYN) {
+                        const float rm = rs / (float)np + a.sc.rew_b;
+                        float rw = a.sc.ro_b;
+#pragma unroll
+                        for (int k = 0; k < 16; k++) rw = fmaf(a.sc.ro_w[k], fmaxf(fmaf(a.sc.rh_w[k], rm, a.sc.rh_b[k]), 0.f), rw);
+                        a.reward[item] = rw;
+                    }
                 }
-                float* lg = s_logit + img * 384;
-                if (lane == 0) lg[np] = a.net.pass_logit[0];
+                const float* l0 = s_pol + img * 384;
+                float* l1 = s_pol + (images + img) * 384;             // reused for the summed logits
+                for (int k = lane; k < np; k += 32) l1[k] = l0[k] + l1[k] + a.sc.pol_b;
+                if (lane == 0) l1[np] = a.sc.pass_logit;
                 __syncwarp();
                 float* pol_out = a.policy + (size_t)item * (np + 1);
                 if (!a.want_softmax) {
-                    for (int k = lane; k <= np; k += 32) pol_out[k] = lg[k];
+                    for (int k = lane; k <= np; k += 32) pol_out[k] = l1[k];
                 } else {
                     float m = -INFINITY;
-                    for (int k = lane; k <= np; k += 32) m = fmaxf(m, lg[k]);
+                    for (int k = lane; k <= np; k += 32) m = fmaxf(m, l1[k]);
                     m = warp_max_f(m);
                     float se = 0.f;
-                    for (int k = lane; k <= np; k += 32) { float e = expf(lg[k] - m); lg[k] = e; se += e; }
+                    for (int k = lane; k <= np; k += 32) { float e = expf(l1[k] - m); l1[k] = e; se += e; }
                     se = warp_sum_f(se);
-                    for (int k = lane; k <= np; k += 32) pol_out[k] = lg[k] / se;
+                    for (int k = lane; k <= np; k += 32) pol_out[k] = l1[k] / se;
                 }
             }
-            it++;
         }
     }
     tc_fence_before();
@@ -373,14 +455,14 @@ k_tc_recurrent(const TcArgs a) {
 }
 
 // ---------------------------------------------------------------------------------------- weight preparation
-// wB[kb = tap*2 + half][kc][co][e] = bf16(W[co][half*64 + kc*8 + e][tap])
-__global__ void k_tc_prep_w(const float* __restrict__ w, __nv_bfloat16* __restrict__ wB) {
-    const int total = TC_KBLOCKS * 8 * 128 * 8;
+// wB[kb = half*9 + tap][kc][co][e] = bf16(W[co][half*64 + kc*8 + e][tap])      (W = [Cout][Cin][3][3])
+__global__ void k_tc_prep_w(const float* __restrict__ w, __nv_bfloat16* __restrict__ wB, int cin, int cout) {
+    const int total = 9 * cin * cout;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
-        int e = i & 7, co = (i >> 3) & 127, kc = (i >> 10) & 7, kb = i >> 13;
-        int tap = kb >> 1, half = kb & 1;
-        int ci = half * 64 + kc * 8 + e;
-        wB[i] = __float2bfloat16_rn(w[((size_t)co * TC_C + ci) * 9 + tap]);
+        const int e = i & 7, co = (i >> 3) % cout, kc = ((i >> 3) / cout) & 7, kb = (i >> 3) / (cout * 8);
+        const int half = kb / 9, tap = kb - half * 9;
+        const int ci = half * 64 + kc * 8 + e;
+        wB[i] = __float2bfloat16_rn(w[((size_t)co * cin + ci) * 9 + tap]);
     }
 }
 
@@ -413,11 +495,91 @@ __global__ void k_tc_prep_tbl(const float* __restrict__ w, const float* __restri
     }
 }
 
-__global__ void k_tc_prep_headw(mzgo_net_t net, float* hw) {
+// the parameters the epilogue reads as kernel-argument constants, gathered into one device buffer
+__global__ void k_tc_gather_heads(mzgo_net_t net, float* out /* [3*128 + sizeof(TcScalars)/4] */) {
     for (int i = threadIdx.x; i < TC_C; i += blockDim.x) {
-        hw[i] = net.pol_w[i];
-        hw[TC_C + i] = net.val_w[i];
-        hw[2 * TC_C + i] = net.rew_w[i];
+        out[i] = net.pol_w[i];
+        out[TC_C + i] = net.val_w[i];
+        out[2 * TC_C + i] = net.rew_w[i];
+    }
+    float* sc = out + 3 * TC_C;
+    if (threadIdx.x == 0) {
+        sc[0] = net.pol_b[0]; sc[1] = net.val_b[0]; sc[2] = net.rew_b[0]; sc[3] = net.vfc_w[0];
+        sc[4] = net.vfc_b[0]; sc[5] = net.pass_logit[0]; sc[6] = net.ro_b[0]; sc[7] = 0.f;
+    }
+    if (threadIdx.x < 16) {
+        sc[8 + threadIdx.x] = net.rh_w[threadIdx.x];
+        sc[24 + threadIdx.x] = net.rh_b[threadIdx.x];
+        sc[40 + threadIdx.x] = net.ro_w[threadIdx.x];
+    }
+}
+
+// ---------------------------------------------------------------------------------------- representation conv1
+// main.py:75/:81: conv3x3 6 -> 64 + ReLU on CUDA cores (0.3 % of the network FLOPs), reading the packed
+// board (or float32 GymGo planes) and writing the bf16 slab layout [8][PS][8] that conv2 consumes.
+constexpr int C1_THREADS = 256;
+__global__ void __launch_bounds__(C1_THREADS)
+k_rep_conv1_bf16(const float* __restrict__ obs, const uint32_t* __restrict__ boards, const int32_t* __restrict__ gate,
+                 const float* __restrict__ w /* [64][6][3][3] */, const float* __restrict__ bias,
+                 __nv_bfloat16* __restrict__ out, int n) {
+    __shared__ float s_w[54 * 64];                                  // [ci*9+tap][co]
+    __shared__ float s_x[6 * (MZGO_MAX_N + 2) * (MZGO_MAX_N + 2)];  // zero-padded planes
+    __shared__ float s_b[64];
+    const int item = blockIdx.x;
+    if (gate && gate[item] < 0) return;
+    const int np = n * n, pw = n + 2, pp = pw * pw, ps = tc_ps(n);
+    for (int i = threadIdx.x; i < 54 * 64; i += C1_THREADS) {
+        const int co = i & 63, k = i >> 6;
+        s_w[i] = w[co * 54 + k];
+    }
+    if (threadIdx.x < 64) s_b[threadIdx.x] = bias[threadIdx.x];
+    const uint32_t* rec = boards ? boards + (size_t)item * MZGO_BOARD_WORDS : nullptr;
+    for (int i = threadIdx.x; i < 6 * pp; i += C1_THREADS) {
+        const int ci = i / pp, q = i - ci * pp;
+        const int r = q / pw - 1, c = q - (q / pw) * pw - 1;
+        float v = 0.f;
+        if (r >= 0 && r < n && c >= 0 && c < n) {
+            if (rec) {
+                uint32_t bit;
+                if (ci < 2) bit = (rec[ci * n + r] >> c) & 1u;
+                else if (ci == 3) bit = (rec[2 * n + r] >> c) & 1u;
+                else if (ci == 2) bit = rec[60] & 1u;
+                else if (ci == 4) bit = rec[61] & 1u;
+                else bit = (rec[61] >> 1) & 1u;
+                v = (float)bit;
+            } else {
+                v = obs[((size_t)item * 6 + ci) * np + r * n + c];
+            }
+        }
+        s_x[i] = v;
+    }
+    __syncthreads();
+    uint4* o = reinterpret_cast<uint4*>(out) + (size_t)item * 8 * ps;
+    for (int i = threadIdx.x; i < 8 * np; i += C1_THREADS) {
+        const int kc = i / np, p = i - kc * np;
+        const int r = p / n, c = p - r * n;
+        float acc[8];
+#pragma unroll
+        for (int e = 0; e < 8; e++) acc[e] = s_b[kc * 8 + e];
+#pragma unroll
+        for (int ci = 0; ci < 6; ci++) {
+#pragma unroll
+            for (int tap = 0; tap < 9; tap++) {
+                const float x = s_x[ci * pp + (r + tap / 3) * pw + (c + tap % 3)];
+                const float4 w0 = *reinterpret_cast<const float4*>(s_w + (ci * 9 + tap) * 64 + kc * 8);
+                const float4 w1 = *reinterpret_cast<const float4*>(s_w + (ci * 9 + tap) * 64 + kc * 8 + 4);
+                acc[0] = fmaf(w0.x, x, acc[0]); acc[1] = fmaf(w0.y, x, acc[1]);
+                acc[2] = fmaf(w0.z, x, acc[2]); acc[3] = fmaf(w0.w, x, acc[3]);
+                acc[4] = fmaf(w1.x, x, acc[4]); acc[5] = fmaf(w1.y, x, acc[5]);
+                acc[6] = fmaf(w1.z, x, acc[6]); acc[7] = fmaf(w1.w, x, acc[7]);
+            }
+        }
+        uint4 v;
+        v.x = pack_bf16(fmaxf(acc[0], 0.f), fmaxf(acc[1], 0.f));
+        v.y = pack_bf16(fmaxf(acc[2], 0.f), fmaxf(acc[3], 0.f));
+        v.z = pack_bf16(fmaxf(acc[4], 0.f), fmaxf(acc[5], 0.f));
+        v.w = pack_bf16(fmaxf(acc[6], 0.f), fmaxf(acc[7], 0.f));
+        o[(size_t)kc * ps + (r + 1) * (n + 1) + c + 1] = v;
     }
 }
 
@@ -427,7 +589,7 @@ __global__ void k_tc_pack(const float* __restrict__ src, long src_stride, __nv_b
     const int item = blockIdx.y;
     const int s = slot ? slot[item] : item;
     if (s < 0) return;
-    const int ps = tc_ps(n), np = n * n, total = TC_KC * ps;
+    const int ps = tc_ps(n), np = n * n, total = (TC_C / 8) * ps;
     const float* in = src + (size_t)item * src_stride;
     uint4* out = reinterpret_cast<uint4*>(arena) + (size_t)s * total;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
@@ -453,7 +615,7 @@ __global__ void k_tc_unpack(const __nv_bfloat16* __restrict__ arena, const int32
     const int s = slot ? slot[item] : item;
     if (s < 0) return;
     const int ps = tc_ps(n), np = n * n, total = TC_C * np;
-    const __nv_bfloat16* in = arena + (size_t)s * TC_KC * ps * 8;
+    const __nv_bfloat16* in = arena + (size_t)s * (TC_C / 8) * ps * 8;
     float* out = dst + (size_t)item * dst_stride;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
         const int ch = i / np, p = i - ch * np;
@@ -463,22 +625,93 @@ __global__ void k_tc_unpack(const __nv_bfloat16* __restrict__ arena, const int32
     }
 }
 
+// ---- host copies of the head parameters, keyed by the workspace they were prepared into ----
+struct HostHeads {
+    float hw[3 * TC_C];
+    TcScalars sc;
+};
+std::mutex g_heads_mu;
+std::unordered_map<const void*, HostHeads> g_heads;
+
+int num_sms() {
+    static int n = 0;
+    if (n == 0) {
+        int dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess)
+            n = 148;
+    }
+    return n;
+}
+
+template <int CIN, int COUT, int MODE>
+int launch_tc_conv(TcArgs& a, int n, int B, cudaStream_t st) {
+    static bool attr_set = false;
+    if (!attr_set) {
+        MZGO_CUDA(cudaFuncSetAttribute(k_tc_conv<CIN, COUT, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_LIMIT));
+        attr_set = true;
+    }
+    a.B = B;
+    a.n = n;
+    a.ps = tc_ps(n);
+    a.tiles_per_image = tc_tiles_per_image(n);
+    a.images_per_group = TC_SLOTS / a.tiles_per_image;
+    a.num_groups = ceil_div(B, a.images_per_group);
+    const int kblocks = 9 * CIN / 64;
+    const TcSmemLayout L0 = tc_smem_layout(n, CIN, COUT, 0);
+    int stages = ((int)TC_SMEM_LIMIT - (int)L0.total) / (COUT * 128);
+    if (stages > TC_MAX_STAGES) stages = TC_MAX_STAGES;
+    if (stages > kblocks) stages = kblocks;
+    MZGO_CHECK_ARG(stages >= 2, "shared memory layout of %u B leaves no room for the weight ring", L0.total);
+    a.stages = stages;
+    const TcSmemLayout L = tc_smem_layout(n, CIN, COUT, stages);
+    const int grid = a.num_groups < num_sms() ? a.num_groups : num_sms();
+    k_tc_conv<CIN, COUT, MODE><<<grid, TC_THREADS, L.total, st>>>(a);
+    mzgo_count_launch();
+    MZGO_LAUNCH_CHECK();
+    return MZGO_OK;
+}
+
+int fill_heads(const mzgo_net_t* net, TcArgs& a) {
+    std::lock_guard<std::mutex> lk(g_heads_mu);
+    auto it = g_heads.find(net->workspace);
+    MZGO_CHECK_ARG(it != g_heads.end(), "mzgo_net_prepare was not called for this workspace");
+    memcpy(a.hw, it->second.hw, sizeof(a.hw));
+    a.sc = it->second.sc;
+    return 0;
+}
+
 }  // namespace
 
+// Synchronous on `st` (it downloads 1.7 KB of head parameters for the kernel-argument constants).
 int mzgo_net_prepare_tc(const mzgo_net_t* net, cudaStream_t st) {
     char* ws = (char*)net->workspace;
     NetWorkspace w = mzgo_net_layout(net->n, net->C, net->precision, net->max_batch);
-    k_tc_prep_w<<<144, 256, 0, st>>>(net->dyn_w, (__nv_bfloat16*)(ws + w.tc_w));
+    k_tc_prep_w<<<144, 256, 0, st>>>(net->dyn_w, (__nv_bfloat16*)(ws + w.tc_w), TC_C, TC_C);
+    k_tc_prep_w<<<72, 256, 0, st>>>(net->rep_w2, (__nv_bfloat16*)(ws + w.tc_w2), 64, 64);
+    k_tc_prep_w<<<72, 256, 0, st>>>(net->rep_w3, (__nv_bfloat16*)(ws + w.tc_w3), 64, TC_C);
     k_tc_prep_tbl<<<296, 128, 0, st>>>(net->dyn_w, net->dyn_b, net->emb, (float*)(ws + w.tc_embbias), net->A);
-    k_tc_prep_headw<<<1, 128, 0, st>>>(*net, (float*)(ws + w.tc_headw));
-    mzgo_count_launches(3);
+    k_tc_gather_heads<<<1, 128, 0, st>>>(*net, (float*)(ws + w.tc_headw));
+    mzgo_count_launches(5);
     MZGO_LAUNCH_CHECK();
+    // the bf16 activation slabs of the representation network rely on zero padding that is never rewritten
+    const size_t slab64 = (size_t)8 * tc_ps(net->n) * 16;
+    MZGO_CUDA(cudaMemsetAsync(ws + w.tc_act1, 0, slab64 * net->max_batch, st));
+    MZGO_CUDA(cudaMemsetAsync(ws + w.tc_act2, 0, slab64 * net->max_batch, st));
+    HostHeads h;
+    static_assert(sizeof(TcScalars) == 56 * 4, "TcScalars layout");
+    float tmp[3 * TC_C + 56];
+    MZGO_CUDA(cudaMemcpyAsync(tmp, ws + w.tc_headw, sizeof(tmp), cudaMemcpyDeviceToHost, st));
+    MZGO_CUDA(cudaStreamSynchronize(st));
+    memcpy(h.hw, tmp, sizeof(h.hw));
+    memcpy(&h.sc, tmp + 3 * TC_C, sizeof(TcScalars));
+    std::lock_guard<std::mutex> lk(g_heads_mu);
+    g_heads[net->workspace] = h;
     return MZGO_OK;
 }
 
 int mzgo_tc_pack_latent(const mzgo_net_t* net, const float* src, long src_stride, void* arena, const int32_t* slot,
                         int B, cudaStream_t st) {
-    dim3 grid(ceil_div(TC_KC * tc_ps(net->n), 256), B);
+    dim3 grid(ceil_div((TC_C / 8) * tc_ps(net->n), 256), B);
     k_tc_pack<<<grid, 256, 0, st>>>(src, src_stride, (__nv_bfloat16*)arena, slot, net->n);
     mzgo_count_launch();
     MZGO_LAUNCH_CHECK();
@@ -494,43 +727,43 @@ int mzgo_tc_unpack_latent(const mzgo_net_t* net, const void* arena, const int32_
     return MZGO_OK;
 }
 
+// initial_inference in bf16 mode: conv1 on CUDA cores, conv2 / conv3 + prediction heads on tcgen05
+int mzgo_tc_initial(const mzgo_net_t* net, const float* obs, const uint32_t* boards, void* arena,
+                    const int32_t* out_slot, float* value, float* policy, int want_softmax, int B, cudaStream_t st) {
+    char* ws = (char*)net->workspace;
+    NetWorkspace w = mzgo_net_layout(net->n, net->C, net->precision, net->max_batch);
+    __nv_bfloat16* act1 = (__nv_bfloat16*)(ws + w.tc_act1);
+    __nv_bfloat16* act2 = (__nv_bfloat16*)(ws + w.tc_act2);
+    k_rep_conv1_bf16<<<B, C1_THREADS, 0, st>>>(obs, boards, out_slot, net->rep_w1, net->rep_b1, act1, net->n);
+    mzgo_count_launch();
+    MZGO_LAUNCH_CHECK();
+    TcArgs a{};
+    a.in = act1; a.out = act2; a.action = out_slot;          // gate: items without an output slot are skipped
+    a.wB = (const __nv_bfloat16*)(ws + w.tc_w2);
+    a.tbl = net->rep_b2;
+    if (int e = launch_tc_conv<64, 64, MODE_PLAIN>(a, net->n, B, st)) return e;
+    TcArgs b{};
+    b.in = act2; b.out = (__nv_bfloat16*)arena; b.out_slot = out_slot;
+    b.wB = (const __nv_bfloat16*)(ws + w.tc_w3);
+    b.tbl = net->rep_b3;
+    b.value = value; b.policy = policy; b.want_softmax = want_softmax;
+    if (int e = fill_heads(net, b)) return e;
+    return launch_tc_conv<64, TC_C, MODE_HEADS>(b, net->n, B, st);
+}
+
 int mzgo_tc_recurrent(const mzgo_net_t* net, void* arena, const int32_t* in_slot, const int32_t* action,
                       const int32_t* out_slot, float* reward, float* value, float* policy, int want_softmax, int B,
                       cudaStream_t st) {
-    static int num_sms = 0;
-    static bool attr_set = false;
-    if (num_sms == 0) {
-        int dev = 0;
-        MZGO_CUDA(cudaGetDevice(&dev));
-        MZGO_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
-    }
-    if (!attr_set) {
-        MZGO_CUDA(cudaFuncSetAttribute(k_tc_recurrent, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448));
-        attr_set = true;
-    }
     char* ws = (char*)net->workspace;
     NetWorkspace w = mzgo_net_layout(net->n, net->C, net->precision, net->max_batch);
     TcArgs a{};
-    a.arena_in = (const __nv_bfloat16*)arena;
-    a.arena_out = (__nv_bfloat16*)arena;
+    a.in = (const __nv_bfloat16*)arena;
+    a.out = (__nv_bfloat16*)arena;
     a.in_slot = in_slot; a.action = action; a.out_slot = out_slot;
     a.wB = (const __nv_bfloat16*)(ws + w.tc_w);
     a.tbl = (const float*)(ws + w.tc_embbias);
-    a.head_w = (const float*)(ws + w.tc_headw);
-    a.net = *net;
     a.reward = reward; a.value = value; a.policy = policy;
     a.want_softmax = want_softmax;
-    a.B = B;
-    a.n = net->n;
-    a.ps = tc_ps(net->n);
-    a.tiles_per_image = tc_tiles_per_image(net->n);
-    a.images_per_group = TC_MAX_TILES / a.tiles_per_image;
-    a.num_groups = ceil_div(B, a.images_per_group);
-    const TcSmemLayout L = tc_smem_layout(net->n);
-    MZGO_CHECK_ARG(L.total <= 232448, "shared memory layout of %u B does not fit", L.total);
-    const int grid = a.num_groups < num_sms ? a.num_groups : num_sms;
-    k_tc_recurrent<<<grid, TC_THREADS, L.total, st>>>(a);
-    mzgo_count_launch();
-    MZGO_LAUNCH_CHECK();
-    return MZGO_OK;
+    if (int e = fill_heads(net, a)) return e;
+    return launch_tc_conv<TC_C, TC_C, MODE_DYN>(a, net->n, B, st);
 }
