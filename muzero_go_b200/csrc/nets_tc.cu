@@ -138,6 +138,7 @@ struct TcArgs {
     int want_softmax;
     int B;                       // items
     int n, ps, tiles_per_image, images_per_group, num_groups, stages;
+    int dbg;
     TcScalars sc;
     float hw[3 * TC_C];          // policy / value / reward 1x1 conv weights: read as constant-bank operands
 };
@@ -165,25 +166,56 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
     return *reinterpret_cast<uint32_t*>(&v);
 }
 
-// ---------------------------------------------------------------------------------------- epilogue of one tile
-// One thread = one output position x COUT/2 channels (column half CHH of the accumulator tile).
-template <int COUT, int MODE, int CHH>
-__device__ __forceinline__ void tc_epilogue_tile(const TcArgs& a, uint32_t taddr, uint64_t* acc_empty_bar, bool live,
-                                                 const float* tb, uint4* dst, int ps, bool valid, bool store_ok,
-                                                 float& pol, float& val, float& rew) {
+// ---------------------------------------------------------------------------------------- warp-uniform helpers
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "elect.sync _|p, 0xffffffff;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t"
+        "}"
+        : "=r"(pred));
+    return pred != 0;
+}
+
+// Which images of a group are live (bit i = image i).  Lane i looks at image i and the result is a
+// ballot, so every role of the kernel sees the same warp-uniform mask.
+__device__ __forceinline__ uint32_t tc_live_mask(const TcArgs& a, int grp, int images, int lane) {
+    const int item = grp * images + lane;
+    bool ok = lane < images && item < a.B;
+    if (ok) ok = (!a.action || a.action[item] >= 0) && (!a.in_slot || a.in_slot[item] >= 0) &&
+                 (!a.out_slot || a.out_slot[item] >= 0);
+    return __ballot_sync(FULL_MASK, ok);
+}
+
+// ---------------------------------------------------------------------------------------- epilogue pieces
+// One epilogue thread = one output position x COUT/2 channels (column half CHH of the accumulator tile).
+
+// TMEM -> registers, then hand the TMEM slot back to the MMA warp at once.
+template <int COUT, int CHH>
+__device__ __forceinline__ void tc_epi_load(uint32_t taddr, uint64_t* acc_full_bar, uint32_t parity,
+                                            uint64_t* acc_empty_bar, bool live, uint32_t (&rr)[COUT / 2]) {
     constexpr int CPT = COUT / 2;
     constexpr int CH0 = CHH * CPT;
-    uint32_t rr[CPT];
+    mbar_wait(acc_full_bar, parity);
+    tc_fence_after();
     if (live) {
         TMEM_LD_32X32B_X32(taddr + CH0, rr);
         if (CPT == 64) TMEM_LD_32X32B_X32(taddr + CH0 + 32, (rr + 32));
         asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
     }
-    // the accumulator now lives in registers: hand the TMEM slot back to the MMA warp at once
     tc_fence_before();
     __syncwarp();
     if ((threadIdx.x & 31) == 0) mbar_arrive(acc_empty_bar);
-    if (!live) return;
+}
+
+// bias + ReLU + heads + bf16 pack + store of one tile held in registers
+template <int COUT, int MODE, int CHH>
+__device__ __forceinline__ void tc_epi_process(const TcArgs& a, const uint32_t (&rr)[COUT / 2], const float* tb, uint4* dst,
+                                               int ps, bool valid, bool store_ok, float& pol, float& val, float& rew) {
+    constexpr int CPT = COUT / 2;
+    constexpr int CH0 = CHH * CPT;
     pol = 0.f; val = 0.f; rew = 0.f;
 #pragma unroll
     for (int k = 0; k < CPT / 8; k++) {
@@ -213,20 +245,138 @@ __device__ __forceinline__ void tc_epilogue_tile(const TcArgs& a, uint32_t taddr
     if (!valid) { val = 0.f; rew = 0.f; }
 }
 
+struct TcEpiCtx {
+    float* s_tbl;
+    float* s_pol;
+    float* s_part;
+    uint64_t* acc_full;
+    uint64_t* acc_empty;
+    uint32_t tmem_base;
+};
+
+// The epilogue role: 8 warps, warp (wq, CHH) owns TMEM lane quarter wq and column half CHH.  Tiles are
+// double-buffered in registers: tile j+1 is pulled out of TMEM (and its slot released) before tile j is
+// processed, so with three tiles per group every slot the next group needs is free almost at once.
+template <int COUT, int MODE, int CHH>
+__device__ __forceinline__ void tc_epilogue_role(const TcArgs& a, const TcEpiCtx& cx) {
+    constexpr int CPT = COUT / 2, KC_OUT = COUT / 8;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int ew = warp - 2, wq = warp & 3;
+    const int et = threadIdx.x - 64;              // 0..255
+    const int n = a.n, ps = a.ps, np = n * n, q0 = n + 2;
+    const int tpi = a.tiles_per_image, images = a.images_per_group, NT = images * tpi;
+    uint32_t tile_ctr = 0;
+    uint32_t live = 0;
+    int grp = 0;
+
+    auto load_tile = [&](int j, uint32_t (&rr)[CPT]) {
+        const int img = j / tpi;
+        const uint32_t c = tile_ctr + j, slot = c & (TC_SLOTS - 1);
+        const uint32_t taddr = cx.tmem_base + ((uint32_t)(wq * 32) << 16) + slot * 128;
+        tc_epi_load<COUT, CHH>(taddr, cx.acc_full + slot, (c >> 2) & 1, cx.acc_empty + slot, (live >> img) & 1u, rr);
+    };
+    auto process_tile = [&](int j, const uint32_t (&rr)[CPT]) {
+        const int img = j / tpi, tt = j - img * tpi;
+        if (!((live >> img) & 1u)) return;
+        const int item = grp * images + img;
+        const int o = tt * 128 + wq * 32 + lane;            // flat output row of this thread
+        const int r = o / (n + 1), cc = o - r * (n + 1);
+        const bool valid = (r < n) && (cc < n);
+        const int cls = (r == 0 ? 0 : (r == n - 1 ? 2 : 1)) * 3 + (cc == 0 ? 0 : (cc == n - 1 ? 2 : 1));
+        const int q = q0 + o;
+        const float* tb = (MODE == MODE_DYN) ? cx.s_tbl + (img * 9 + (valid ? cls : 4)) * COUT : cx.s_tbl;
+        const int oslot = a.out_slot ? a.out_slot[item] : item;
+        uint4* dst = reinterpret_cast<uint4*>(a.out) + (size_t)oslot * KC_OUT * ps + q;
+        float pol, val, rew;
+        tc_epi_process<COUT, MODE, CHH>(a, rr, tb, dst, ps, valid, q < ps, pol, val, rew);
+        if (MODE != MODE_PLAIN) {
+            if (valid) cx.s_pol[(CHH * images + img) * 384 + r * n + cc] = pol;
+            val = warp_sum_f(val);
+            if (MODE == MODE_DYN) rew = warp_sum_f(rew);
+            if (lane == 0) { cx.s_part[(j * 8 + ew) * 2] = val; cx.s_part[(j * 8 + ew) * 2 + 1] = rew; }
+        }
+    };
+
+    if (MODE != MODE_DYN) {
+        for (int k = et; k < COUT; k += TC_EPI_THREADS) cx.s_tbl[k] = a.tbl[k];
+    }
+    for (grp = blockIdx.x; grp < a.num_groups; grp += gridDim.x) {
+        live = tc_live_mask(a, grp, images, lane);
+        if (!live) continue;
+        epi_bar_sync();                            // previous group's finalisation has read s_pol / s_part / s_tbl
+        if (MODE == MODE_DYN) {
+            for (int i = 0; i < images; i++) {
+                if (!(live & (1u << i))) continue;
+                const float4* src = reinterpret_cast<const float4*>(a.tbl + (size_t)a.action[grp * images + i] * 9 * COUT);
+                float4* dstt = reinterpret_cast<float4*>(cx.s_tbl + i * 9 * COUT);
+                for (int k = et; k < 9 * COUT / 4; k += TC_EPI_THREADS) dstt[k] = src[k];
+            }
+        }
+        epi_bar_sync();
+        uint32_t ra[CPT], rb[CPT];
+        load_tile(0, ra);
+        for (int j = 0; j < NT; j += 2) {
+            if (j + 1 < NT) load_tile(j + 1, rb);
+            process_tile(j, ra);
+            if (j + 2 < NT) load_tile(j + 2, ra);
+            if (j + 1 < NT) process_tile(j + 1, rb);
+        }
+        tile_ctr += NT;
+        if (MODE == MODE_PLAIN) continue;
+        epi_bar_sync();
+        // ---- per-image finalisation: value / reward heads and the policy softmax (one warp per image)
+        for (int img = ew; img < images; img += 8) {
+            if (!(live & (1u << img))) continue;
+            const int item = grp * images + img;
+            float vs = 0.f, rs = 0.f;
+            for (int tt = 0; tt < tpi; tt++)
+                for (int w = 0; w < 8; w++) {
+                    vs += cx.s_part[((img * tpi + tt) * 8 + w) * 2];
+                    rs += cx.s_part[((img * tpi + tt) * 8 + w) * 2 + 1];
+                }
+            if (lane == 0) {
+                const float vm = vs / (float)np + a.sc.val_b;
+                a.value[item] = fmaf(a.sc.vfc_w, vm, a.sc.vfc_b);
+                if (MODE == MODE_DYN) {
+                    const float rm = rs / (float)np + a.sc.rew_b;
+                    float rw = a.sc.ro_b;
+#pragma unroll
+                    for (int k = 0; k < 16; k++) rw = fmaf(a.sc.ro_w[k], fmaxf(fmaf(a.sc.rh_w[k], rm, a.sc.rh_b[k]), 0.f), rw);
+                    a.reward[item] = rw;
+                }
+            }
+            const float* l0 = cx.s_pol + img * 384;
+            float* l1 = cx.s_pol + (images + img) * 384;             // reused for the summed logits
+            for (int k = lane; k < np; k += 32) l1[k] = l0[k] + l1[k] + a.sc.pol_b;
+            if (lane == 0) l1[np] = a.sc.pass_logit;
+            __syncwarp();
+            float* pol_out = a.policy + (size_t)item * (np + 1);
+            if (!a.want_softmax) {
+                for (int k = lane; k <= np; k += 32) pol_out[k] = l1[k];
+            } else {
+                float m = -INFINITY;
+                for (int k = lane; k <= np; k += 32) m = fmaxf(m, l1[k]);
+                m = warp_max_f(m);
+                float se = 0.f;
+                for (int k = lane; k <= np; k += 32) { float e = expf(l1[k] - m); l1[k] = e; se += e; }
+                se = warp_sum_f(se);
+                for (int k = lane; k <= np; k += 32) pol_out[k] = l1[k] / se;
+            }
+        }
+    }
+}
+
 // ---------------------------------------------------------------------------------------- the fused kernel
 template <int CIN, int COUT, int MODE>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 k_tc_conv(const __grid_constant__ TcArgs a) {
-    constexpr int KC_IN = CIN / 8, KC_OUT = COUT / 8, NH = CIN / 64;
+    constexpr int KC_IN = CIN / 8, NH = CIN / 64;
     constexpr uint32_t STAGE_BYTES = COUT * 128;          // [8 chunks][COUT][8] bf16
     constexpr uint32_t IDESC = tc_idesc(COUT);
     extern __shared__ __align__(128) uint8_t smem[];
     const TcSmemLayout L = tc_smem_layout(a.n, CIN, COUT, a.stages);
     uint8_t* sA = smem;
     uint8_t* sB = smem + L.b_off;
-    float* s_tbl = reinterpret_cast<float*>(smem + L.tbl_off);       // DYN: [images][9][COUT]; else [COUT]
-    float* s_pol = reinterpret_cast<float*>(smem + L.pol_off);       // [2][images][384]
-    float* s_part = reinterpret_cast<float*>(smem + L.part_off);     // [tile][warp][2]
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L.bar_off);
     uint64_t* a_full = bars + 0;                    // [2] input slab halves
     uint64_t* a_empty = bars + 2;                   // [2]
@@ -237,7 +387,7 @@ k_tc_conv(const __grid_constant__ TcArgs a) {
     uint32_t* s_tmem = reinterpret_cast<uint32_t*>(b_empty + TC_MAX_STAGES);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int n = a.n, ps = a.ps, np = n * n;
+    const int n = a.n, ps = a.ps;
     const int tpi = a.tiles_per_image, images = a.images_per_group, NT = images * tpi;
     const uint32_t slab_bytes = (uint32_t)KC_IN * ps * 16;
     const uint32_t half_bytes = slab_bytes / NH;
@@ -258,193 +408,108 @@ k_tc_conv(const __grid_constant__ TcArgs a) {
     tc_fence_after();
     const uint32_t tmem_base = *s_tmem;
 
-    // which images of a group are live: every role evaluates this the same way
-    auto live_mask = [&](int grp) -> uint32_t {
-        uint32_t m = 0;
-        for (int i = 0; i < images; i++) {
-            const int item = grp * images + i;
-            if (item >= a.B) break;
-            const bool ok = (!a.action || a.action[item] >= 0) && (!a.in_slot || a.in_slot[item] >= 0) &&
-                            (!a.out_slot || a.out_slot[item] >= 0);
-            if (ok) m |= 1u << i;
-        }
-        return m;
-    };
-
     if (warp == 0) {
-        // ===================================================== TMA producer
-        if (lane == 0) {
-            uint32_t it = 0, s = 0, bph = 0;
-            for (int grp = blockIdx.x; grp < a.num_groups; grp += gridDim.x) {
-                const uint32_t live = live_mask(grp);
-                if (!live) continue;
-                for (int h = 0; h < NH; h++) {
-                    mbar_wait(a_empty + h, (it & 1) ^ 1);
-                    mbar_expect_tx(a_full + h, half_bytes * __popc(live));
-                    for (int i = 0; i < images; i++) {
-                        if (!(live & (1u << i))) continue;
-                        const int item = grp * images + i;
-                        const int slot = a.in_slot ? a.in_slot[item] : item;
-                        const uint8_t* src = reinterpret_cast<const uint8_t*>(a.in) + (size_t)slot * slab_bytes + (size_t)h * half_bytes;
-                        bulk_g2s(sA + (size_t)i * slab_bytes + (size_t)h * half_bytes, src, half_bytes, a_full + h);
-                    }
-                    for (int tap = 0; tap < 9; tap++) {
-                        mbar_wait(b_empty + s, bph ^ 1);
+        // ===================================================== TMA producer (lane 0 issues, the warp stays converged)
+        uint32_t it = 0, s = 0, bph = 0;
+        for (int grp = blockIdx.x; grp < a.num_groups; grp += gridDim.x) {
+            const uint32_t live = tc_live_mask(a, grp, images, lane);
+            if (!live) continue;
+            for (int h = 0; h < NH; h++) {
+                mbar_wait(a_empty + h, (it & 1) ^ 1);
+                if (lane == 0) mbar_expect_tx(a_full + h, half_bytes * __popc(live));
+                __syncwarp();
+                if (lane < images && ((live >> lane) & 1u)) {
+                    const int item = grp * images + lane;
+                    const int slot = a.in_slot ? a.in_slot[item] : item;
+                    const uint8_t* src = reinterpret_cast<const uint8_t*>(a.in) + (size_t)slot * slab_bytes + (size_t)h * half_bytes;
+                    bulk_g2s(sA + (size_t)lane * slab_bytes + (size_t)h * half_bytes, src, half_bytes, a_full + h);
+                }
+                for (int tap = 0; tap < 9; tap++) {
+                    mbar_wait(b_empty + s, bph ^ 1);
+                    if (lane == 0) {
                         mbar_expect_tx(b_full + s, STAGE_BYTES);
                         bulk_g2s(sB + s * STAGE_BYTES,
                                  reinterpret_cast<const uint8_t*>(a.wB) + (size_t)(h * 9 + tap) * STAGE_BYTES, STAGE_BYTES,
                                  b_full + s);
-                        if (++s == (uint32_t)a.stages) { s = 0; bph ^= 1; }
                     }
+                    if (++s == (uint32_t)a.stages) { s = 0; bph ^= 1; }
                 }
-                it++;
             }
+            it++;
         }
     } else if (warp == 1) {
-        // ===================================================== MMA issuer (one thread)
-        if (lane == 0) {
-            uint32_t it = 0, s = 0, bph = 0, tile_ctr = 0;
-            const uint32_t a_hi = desc_hi(128), b_hi = desc_hi(128);
-            const uint32_t b_lo0 = desc_lo(smem_u32(sB), COUT * 16);
-            uint32_t a_lo[TC_SLOTS];
+        // ===================================================== MMA issuer
+        // The whole warp runs the loop so that every value stays warp-uniform (uniform registers, no
+        // per-thread serialisation around UTCHMMA); one elected lane issues tcgen05.mma / tcgen05.commit.
+        const bool leader = elect_one();
+        uint32_t it = 0, s = 0, bph = 0, tile_ctr = 0;
+        const uint32_t a_hi = desc_hi(128), b_hi = desc_hi(128);
+        const uint32_t b_lo0 = desc_lo(smem_u32(sB), COUT * 16);
+        uint32_t a_lo[TC_SLOTS];
 #pragma unroll
-            for (int j = 0; j < TC_SLOTS; j++) {
-                const int img = j / tpi, tt = j - img * tpi;
-                a_lo[j] = desc_lo(smem_u32(sA) + img * slab_bytes + (uint32_t)(q0 + tt * 128) * 16, ps * 16);
-            }
-            for (int grp = blockIdx.x; grp < a.num_groups; grp += gridDim.x) {
-                const uint32_t live = live_mask(grp);
-                if (!live) continue;
-                uint32_t d_col[TC_SLOTS];
+        for (int j = 0; j < TC_SLOTS; j++) {
+            const int img = j / tpi, tt = j - img * tpi;
+            a_lo[j] = desc_lo(smem_u32(sA) + img * slab_bytes + (uint32_t)(q0 + tt * 128) * 16, ps * 16);
+        }
+        for (int grp = blockIdx.x; grp < a.num_groups; grp += gridDim.x) {
+            const uint32_t live = tc_live_mask(a, grp, images, lane);
+            if (!live) continue;
+            uint32_t d_col[TC_SLOTS];
 #pragma unroll
-                for (int j = 0; j < TC_SLOTS; j++) d_col[j] = tmem_base + ((tile_ctr + j) & (TC_SLOTS - 1)) * 128;
-                for (int h = 0; h < NH; h++) {
-                    mbar_wait(a_full + h, it & 1);
+            for (int j = 0; j < TC_SLOTS; j++) d_col[j] = tmem_base + ((tile_ctr + j) & (TC_SLOTS - 1)) * 128;
+            for (int h = 0; h < NH; h++) {
+                mbar_wait(a_full + h, it & 1);
+                for (int tap = 0; tap < 9; tap++) {
+                    mbar_wait(b_full + s, bph);
                     tc_fence_after();
-                    for (int tap = 0; tap < 9; tap++) {
-                        mbar_wait(b_full + s, bph);
-                        tc_fence_after();
-                        const int dy = (tap * 11) >> 5;                       // tap / 3 for tap < 9
-                        const int shift = (dy - 1) * (n + 1) + (tap - 3 * dy - 1);
-                        const uint32_t a_off = (uint32_t)(h * 8 * ps + shift);       // 16-byte units
-                        const uint32_t b_lo = b_lo0 + s * (STAGE_BYTES >> 4);
-                        const bool first = (h | tap) == 0;
-#pragma unroll
-                        for (int ks = 0; ks < 4; ks++) {
-#pragma unroll
-                            for (int j = 0; j < TC_SLOTS; j++) {
-                                if (j < NT) {
-                                    if (first && ks == 0) {     // first touch of this TMEM slot: the epilogue must have drained it
-                                        const uint32_t c = tile_ctr + j;
-                                        mbar_wait(acc_empty + (c & (TC_SLOTS - 1)), ((c >> 2) & 1) ^ 1);
-                                        tc_fence_after();
-                                    }
-                                    umma_bf16(d_col[j], a_lo[j] + a_off + ks * 2 * ps, a_hi, b_lo + ks * (2 * COUT), b_hi, IDESC,
-                                              (first && ks == 0) ? 0u : 1u);
-                                }
-                            }
+                    const int dy = (tap * 11) >> 5;                       // tap / 3 for tap < 9
+                    int shift = (dy - 1) * (n + 1) + (tap - 3 * dy - 1);
+                    if (a.dbg == 1) shift = 0;
+                    if (a.dbg == 2) shift = ((shift + q0) & ~7) - q0;
+                    const uint32_t a_off = (uint32_t)(h * 8 * ps + shift);       // 16-byte units
+                    const uint32_t b_lo = b_lo0 + s * (STAGE_BYTES >> 4);
+                    const bool first = (h | tap) == 0;
+                    if (first) {
+                        // first touch of the TMEM slots of this group: the epilogue must have drained them
+                        for (int j = 0; j < NT; j++) {
+                            const uint32_t c = tile_ctr + j;
+                            mbar_wait(acc_empty + (c & (TC_SLOTS - 1)), ((c >> 2) & 1) ^ 1);
                         }
-                        umma_commit(b_empty + s);     // frees the weight stage when these MMAs retire
-                        if (++s == (uint32_t)a.stages) { s = 0; bph ^= 1; }
+                        tc_fence_after();
                     }
-                    umma_commit(a_empty + h);         // this half of the input slab may be overwritten
+#pragma unroll
+                    for (int ks = 0; ks < 4; ks++) {
+#pragma unroll
+                        for (int j = 0; j < TC_SLOTS; j++) {
+                            if (j < NT && leader)
+                                umma_bf16(d_col[j], a_lo[j] + a_off + ks * 2 * ps, a_hi, b_lo + ks * (2 * COUT), b_hi, IDESC,
+                                          (first && ks == 0) ? 0u : 1u);
+                        }
+                    }
+                    if (leader) umma_commit(b_empty + s);     // frees the weight stage when these MMAs retire
+                    __syncwarp();
+                    if (++s == (uint32_t)a.stages) { s = 0; bph ^= 1; }
                 }
-                for (int j = 0; j < NT; j++) umma_commit(acc_full + ((tile_ctr + j) & (TC_SLOTS - 1)));
-                tile_ctr += NT;
-                it++;
+                if (leader) umma_commit(a_empty + h);         // this half of the input slab may be overwritten
             }
+            if (leader) {
+                for (int j = 0; j < NT; j++) umma_commit(acc_full + ((tile_ctr + j) & (TC_SLOTS - 1)));
+            }
+            __syncwarp();
+            tile_ctr += NT;
+            it++;
         }
     } else {
         // ===================================================== epilogue (8 warps: TMEM lane quarter x column half)
-        const int ew = warp - 2, wq = warp & 3, chh = ew >> 2;
-        const int et = threadIdx.x - 64;              // 0..255
-        uint32_t tile_ctr = 0;
-        if (MODE != MODE_DYN) {
-            for (int k = et; k < COUT; k += TC_EPI_THREADS) s_tbl[k] = a.tbl[k];
-        }
-        for (int grp = blockIdx.x; grp < a.num_groups; grp += gridDim.x) {
-            const uint32_t live = live_mask(grp);
-            if (!live) continue;
-            epi_bar_sync();                            // previous group's finalisation has read s_pol / s_part / s_tbl
-            if (MODE == MODE_DYN) {
-                for (int i = 0; i < images; i++) {
-                    if (!(live & (1u << i))) continue;
-                    const float4* src = reinterpret_cast<const float4*>(a.tbl + (size_t)a.action[grp * images + i] * 9 * COUT);
-                    float4* dstt = reinterpret_cast<float4*>(s_tbl + i * 9 * COUT);
-                    for (int k = et; k < 9 * COUT / 4; k += TC_EPI_THREADS) dstt[k] = src[k];
-                }
-            }
-            epi_bar_sync();
-            for (int j = 0; j < NT; j++) {
-                const int img = j / tpi, tt = j - img * tpi;
-                const uint32_t c = tile_ctr + j, slot = c & (TC_SLOTS - 1);
-                const bool is_live = (live >> img) & 1u;
-                const int item = grp * images + img;
-                const int o = tt * 128 + wq * 32 + lane;            // flat output row of this thread
-                const int r = o / (n + 1), cc = o - r * (n + 1);
-                const bool valid = (r < n) && (cc < n);
-                const int cls = (r == 0 ? 0 : (r == n - 1 ? 2 : 1)) * 3 + (cc == 0 ? 0 : (cc == n - 1 ? 2 : 1));
-                const int q = q0 + o;
-                const bool store_ok = q < ps;
-                const float* tb = (MODE == MODE_DYN) ? s_tbl + (img * 9 + (valid ? cls : 4)) * COUT : s_tbl;
-                uint4* dst = nullptr;
-                if (is_live) {
-                    const int oslot = a.out_slot ? a.out_slot[item] : item;
-                    dst = reinterpret_cast<uint4*>(a.out) + (size_t)oslot * KC_OUT * ps + q;
-                }
-                mbar_wait(acc_full + slot, (c >> 2) & 1);
-                tc_fence_after();
-                const uint32_t taddr = tmem_base + ((uint32_t)(wq * 32) << 16) + slot * 128;
-                float pol, val, rew;
-                if (chh) tc_epilogue_tile<COUT, MODE, 1>(a, taddr, acc_empty + slot, is_live, tb, dst, ps, valid, store_ok, pol, val, rew);
-                else     tc_epilogue_tile<COUT, MODE, 0>(a, taddr, acc_empty + slot, is_live, tb, dst, ps, valid, store_ok, pol, val, rew);
-                if (MODE != MODE_PLAIN && is_live) {
-                    if (valid) s_pol[(chh * images + img) * 384 + r * n + cc] = pol;
-                    val = warp_sum_f(val);
-                    if (MODE == MODE_DYN) rew = warp_sum_f(rew);
-                    if (lane == 0) { s_part[(j * 8 + ew) * 2] = val; s_part[(j * 8 + ew) * 2 + 1] = rew; }
-                }
-            }
-            tile_ctr += NT;
-            if (MODE == MODE_PLAIN) continue;
-            epi_bar_sync();
-            // ---- per-image finalisation: value / reward heads and the policy softmax (one warp per image)
-            for (int img = ew; img < images; img += 8) {
-                if (!(live & (1u << img))) continue;
-                const int item = grp * images + img;
-                float vs = 0.f, rs = 0.f;
-                for (int tt = 0; tt < tpi; tt++)
-                    for (int w = 0; w < 8; w++) { vs += s_part[((img * tpi + tt) * 8 + w) * 2]; rs += s_part[((img * tpi + tt) * 8 + w) * 2 + 1]; }
-                if (lane == 0) {
-                    const float vm = vs / (float)np + a.sc.val_b;
-                    a.value[item] = fmaf(a.sc.vfc_w, vm, a.sc.vfc_b);
-                    if (MODE == MODE_DYN) {
-                        const float rm = rs / (float)np + a.sc.rew_b;
-                        float rw = a.sc.ro_b;
-#pragma unroll
-                        for (int k = 0; k < 16; k++) rw = fmaf(a.sc.ro_w[k], fmaxf(fmaf(a.sc.rh_w[k], rm, a.sc.rh_b[k]), 0.f), rw);
-                        a.reward[item] = rw;
-                    }
-                }
-                const float* l0 = s_pol + img * 384;
-                float* l1 = s_pol + (images + img) * 384;             // reused for the summed logits
-                for (int k = lane; k < np; k += 32) l1[k] = l0[k] + l1[k] + a.sc.pol_b;
-                if (lane == 0) l1[np] = a.sc.pass_logit;
-                __syncwarp();
-                float* pol_out = a.policy + (size_t)item * (np + 1);
-                if (!a.want_softmax) {
-                    for (int k = lane; k <= np; k += 32) pol_out[k] = l1[k];
-                } else {
-                    float m = -INFINITY;
-                    for (int k = lane; k <= np; k += 32) m = fmaxf(m, l1[k]);
-                    m = warp_max_f(m);
-                    float se = 0.f;
-                    for (int k = lane; k <= np; k += 32) { float e = expf(l1[k] - m); l1[k] = e; se += e; }
-                    se = warp_sum_f(se);
-                    for (int k = lane; k <= np; k += 32) pol_out[k] = l1[k] / se;
-                }
-            }
-        }
+        TcEpiCtx cx;
+        cx.s_tbl = reinterpret_cast<float*>(smem + L.tbl_off);       // DYN: [images][9][COUT]; else [COUT]
+        cx.s_pol = reinterpret_cast<float*>(smem + L.pol_off);       // [2][images][384]
+        cx.s_part = reinterpret_cast<float*>(smem + L.part_off);     // [tile][warp][2]
+        cx.acc_full = acc_full;
+        cx.acc_empty = acc_empty;
+        cx.tmem_base = tmem_base;
+        if ((warp - 2) >> 2) tc_epilogue_role<COUT, MODE, 1>(a, cx);
+        else tc_epilogue_role<COUT, MODE, 0>(a, cx);
     }
     tc_fence_before();
     __syncthreads();
@@ -663,6 +728,7 @@ int launch_tc_conv(TcArgs& a, int n, int B, cudaStream_t st) {
     if (stages > kblocks) stages = kblocks;
     MZGO_CHECK_ARG(stages >= 2, "shared memory layout of %u B leaves no room for the weight ring", L0.total);
     a.stages = stages;
+    { const char* d = getenv("MZGO_TC_DBG"); a.dbg = d ? atoi(d) : 0; }
     const TcSmemLayout L = tc_smem_layout(n, CIN, COUT, stages);
     const int grid = a.num_groups < num_sms() ? a.num_groups : num_sms();
     k_tc_conv<CIN, COUT, MODE><<<grid, TC_THREADS, L.total, st>>>(a);
