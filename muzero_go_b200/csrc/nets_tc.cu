@@ -31,7 +31,7 @@
 namespace {
 
 constexpr int TC_C = 128;               // latent_dim of the tensor-core path
-constexpr int TC_THREADS = 320;
+constexpr int TC_THREADS = 352;         // producer, MMA issuer, 8 epilogue warps, finaliser
 constexpr int TC_EPI_THREADS = 256;
 constexpr int TC_MAX_STAGES = 8;        // weight k-block ring (as many as fit)
 constexpr int TC_SLOTS = 4;             // 4 x 128 TMEM columns
@@ -138,24 +138,27 @@ struct TcArgs {
     int want_softmax;
     int B;                       // items
     int n, ps, tiles_per_image, images_per_group, num_groups, stages;
-    int dbg;
     TcScalars sc;
     float hw[3 * TC_C];          // policy / value / reward 1x1 conv weights: read as constant-bank operands
 };
 
+constexpr int TC_NUM_BARS = 4 + 2 * TC_SLOTS + 2 * TC_MAX_STAGES + 6;
 struct TcSmemLayout {
-    uint32_t a_bytes, b_off, tbl_off, pol_off, part_off, bar_off, total;
+    uint32_t a_bytes, b_off, tbl_off, tbl_stride, pol_off, pol_stride, part_off, bar_off, total;
 };
-__host__ __device__ inline TcSmemLayout tc_smem_layout(int n, int cin, int cout, int stages) {
+// mode_dyn: per-action bias tables (double buffered, loaded by TMA per group); otherwise one [cout] bias vector
+__host__ __device__ inline TcSmemLayout tc_smem_layout(int n, int cin, int cout, int stages, bool mode_dyn) {
     TcSmemLayout L;
     const int tiles = tc_tiles_per_image(n), images = TC_SLOTS / tiles;
     L.a_bytes = (uint32_t)images * (cin / 8) * tc_ps(n) * 16;
     L.b_off = (L.a_bytes + 127) / 128 * 128;
     L.tbl_off = L.b_off + (uint32_t)stages * cout * 128;
-    L.pol_off = L.tbl_off + (uint32_t)images * 9 * cout * 4;
-    L.part_off = L.pol_off + 2u * images * 384 * 4;               // [column half][image][position] partial logits
-    L.bar_off = L.part_off + TC_SLOTS * 8 * 2 * 4;                // [tile][warp][value, reward] partial sums
-    L.total = L.bar_off + (4 + 2 * TC_SLOTS + 2 * TC_MAX_STAGES) * 8 + 16;
+    L.tbl_stride = mode_dyn ? (uint32_t)images * 9 * cout * 4 : 0u;                    // per group parity
+    L.pol_off = L.tbl_off + (mode_dyn ? 2 * L.tbl_stride : (uint32_t)cout * 4);
+    L.pol_stride = (uint32_t)images * 384 * 4;                    // [image][position] logits, per group parity
+    L.part_off = L.pol_off + 2 * L.pol_stride;
+    L.bar_off = L.part_off + 2 * TC_SLOTS * 4 * 2 * 4;            // [parity][tile][lane quarter][value, reward]
+    L.total = L.bar_off + TC_NUM_BARS * 8 + 16;
     return L;
 }
 
@@ -189,151 +192,152 @@ __device__ __forceinline__ uint32_t tc_live_mask(const TcArgs& a, int grp, int i
     return __ballot_sync(FULL_MASK, ok);
 }
 
-// ---------------------------------------------------------------------------------------- epilogue pieces
-// One epilogue thread = one output position x COUT/2 channels (column half CHH of the accumulator tile).
-
-// TMEM -> registers, then hand the TMEM slot back to the MMA warp at once.
-template <int COUT, int CHH>
-__device__ __forceinline__ void tc_epi_load(uint32_t taddr, uint64_t* acc_full_bar, uint32_t parity,
-                                            uint64_t* acc_empty_bar, bool live, uint32_t (&rr)[COUT / 2]) {
-    constexpr int CPT = COUT / 2;
-    constexpr int CH0 = CHH * CPT;
-    mbar_wait(acc_full_bar, parity);
-    tc_fence_after();
-    if (live) {
-        TMEM_LD_32X32B_X32(taddr + CH0, rr);
-        if (CPT == 64) TMEM_LD_32X32B_X32(taddr + CH0 + 32, (rr + 32));
-        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-    }
-    tc_fence_before();
-    __syncwarp();
-    if ((threadIdx.x & 31) == 0) mbar_arrive(acc_empty_bar);
-}
-
-// bias + ReLU + heads + bf16 pack + store of one tile held in registers
-template <int COUT, int MODE, int CHH>
-__device__ __forceinline__ void tc_epi_process(const TcArgs& a, const uint32_t (&rr)[COUT / 2], const float* tb, uint4* dst,
-                                               int ps, bool valid, bool store_ok, float& pol, float& val, float& rew) {
-    constexpr int CPT = COUT / 2;
-    constexpr int CH0 = CHH * CPT;
-    pol = 0.f; val = 0.f; rew = 0.f;
-#pragma unroll
-    for (int k = 0; k < CPT / 8; k++) {
-        const float4 b0 = *reinterpret_cast<const float4*>(tb + CH0 + k * 8);
-        const float4 b1 = *reinterpret_cast<const float4*>(tb + CH0 + k * 8 + 4);
-        const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
-        float x[8];
-#pragma unroll
-        for (int e = 0; e < 8; e++) {
-            x[e] = fmaxf(__uint_as_float(rr[k * 8 + e]) + bb[e], 0.f);
-            if (MODE != MODE_PLAIN) {
-                pol = fmaf(x[e], a.hw[CH0 + k * 8 + e], pol);
-                val = fmaf(x[e], a.hw[TC_C + CH0 + k * 8 + e], val);
-            }
-            if (MODE == MODE_DYN) rew = fmaf(x[e], a.hw[2 * TC_C + CH0 + k * 8 + e], rew);
-        }
-        if (store_ok) {
-            uint4 w;
-            w.x = pack_bf16(x[0], x[1]);
-            w.y = pack_bf16(x[2], x[3]);
-            w.z = pack_bf16(x[4], x[5]);
-            w.w = pack_bf16(x[6], x[7]);
-            if (!valid) w = make_uint4(0u, 0u, 0u, 0u);      // padding positions stay zero for the next conv
-            dst[(size_t)(CH0 / 8 + k) * ps] = w;
-        }
-    }
-    if (!valid) { val = 0.f; rew = 0.f; }
-}
-
-struct TcEpiCtx {
-    float* s_tbl;
-    float* s_pol;
-    float* s_part;
-    uint64_t* acc_full;
-    uint64_t* acc_empty;
+struct TcCtx {
+    uint8_t* s_tbl;        // DYN: [parity][images][9][COUT] float; else [COUT] float
+    uint8_t* s_pol;        // [parity][images][384] float
+    float* s_part;         // [parity][tile][lane quarter][value, reward]
+    uint32_t tbl_stride, pol_stride;
+    uint64_t* acc_full;    // [TC_SLOTS]
+    uint64_t* acc_empty;   // [TC_SLOTS]
+    uint64_t* tbl_full;    // [2]
+    uint64_t* fin_full;    // [2] epilogue -> finaliser (and producer: bias table buffer free)
+    uint64_t* fin_empty;   // [2] finaliser -> epilogue
     uint32_t tmem_base;
 };
 
-// The epilogue role: 8 warps, warp (wq, CHH) owns TMEM lane quarter wq and column half CHH.  Tiles are
-// double-buffered in registers: tile j+1 is pulled out of TMEM (and its slot released) before tile j is
-// processed, so with three tiles per group every slot the next group needs is free almost at once.
-template <int COUT, int MODE, int CHH>
-__device__ __forceinline__ void tc_epilogue_role(const TcArgs& a, const TcEpiCtx& cx) {
-    constexpr int CPT = COUT / 2, KC_OUT = COUT / 8;
+// ---------------------------------------------------------------------------------------- epilogue role
+// 8 warps.  Warp (wq, pi): TMEM lane quarter wq = warp % 4, and of the stream of accumulator tiles it
+// takes those whose running index is congruent to pi mod 2 -- the pair (wq,0), (wq,1) pulls two
+// consecutive tiles out of TMEM at once (their slots are released as soon as the registers hold them),
+// and there is ONE copy of the unrolled channel loop in the instruction cache.
+// One thread = one output position x all COUT channels of its tile.
+template <int COUT, int MODE>
+__device__ __forceinline__ void tc_epilogue_role(const TcArgs& a, const TcCtx& cx) {
+    constexpr int KC_OUT = COUT / 8;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int ew = warp - 2, wq = warp & 3;
-    const int et = threadIdx.x - 64;              // 0..255
-    const int n = a.n, ps = a.ps, np = n * n, q0 = n + 2;
+    const int wq = warp & 3, pi = (warp - 2) >> 2;
+    const int n = a.n, ps = a.ps, q0 = n + 2;
     const int tpi = a.tiles_per_image, images = a.images_per_group, NT = images * tpi;
-    uint32_t tile_ctr = 0;
-    uint32_t live = 0;
-    int grp = 0;
-
-    auto load_tile = [&](int j, uint32_t (&rr)[CPT]) {
-        const int img = j / tpi;
-        const uint32_t c = tile_ctr + j, slot = c & (TC_SLOTS - 1);
-        const uint32_t taddr = cx.tmem_base + ((uint32_t)(wq * 32) << 16) + slot * 128;
-        tc_epi_load<COUT, CHH>(taddr, cx.acc_full + slot, (c >> 2) & 1, cx.acc_empty + slot, (live >> img) & 1u, rr);
-    };
-    auto process_tile = [&](int j, const uint32_t (&rr)[CPT]) {
-        const int img = j / tpi, tt = j - img * tpi;
-        if (!((live >> img) & 1u)) return;
-        const int item = grp * images + img;
-        const int o = tt * 128 + wq * 32 + lane;            // flat output row of this thread
+    // geometry of this thread's row in tile tt of an image (tt < 3 for n <= 19): r | c << 5 | cls << 10 | valid << 14
+    uint32_t geo[3];
+#pragma unroll
+    for (int tt = 0; tt < 3; tt++) {
+        const int o = tt * 128 + wq * 32 + lane;
         const int r = o / (n + 1), cc = o - r * (n + 1);
         const bool valid = (r < n) && (cc < n);
-        const int cls = (r == 0 ? 0 : (r == n - 1 ? 2 : 1)) * 3 + (cc == 0 ? 0 : (cc == n - 1 ? 2 : 1));
-        const int q = q0 + o;
-        const float* tb = (MODE == MODE_DYN) ? cx.s_tbl + (img * 9 + (valid ? cls : 4)) * COUT : cx.s_tbl;
-        const int oslot = a.out_slot ? a.out_slot[item] : item;
-        uint4* dst = reinterpret_cast<uint4*>(a.out) + (size_t)oslot * KC_OUT * ps + q;
-        float pol, val, rew;
-        tc_epi_process<COUT, MODE, CHH>(a, rr, tb, dst, ps, valid, q < ps, pol, val, rew);
-        if (MODE != MODE_PLAIN) {
-            if (valid) cx.s_pol[(CHH * images + img) * 384 + r * n + cc] = pol;
-            val = warp_sum_f(val);
-            if (MODE == MODE_DYN) rew = warp_sum_f(rew);
-            if (lane == 0) { cx.s_part[(j * 8 + ew) * 2] = val; cx.s_part[(j * 8 + ew) * 2 + 1] = rew; }
-        }
-    };
-
-    if (MODE != MODE_DYN) {
-        for (int k = et; k < COUT; k += TC_EPI_THREADS) cx.s_tbl[k] = a.tbl[k];
+        const int cls = valid ? (r == 0 ? 0 : (r == n - 1 ? 2 : 1)) * 3 + (cc == 0 ? 0 : (cc == n - 1 ? 2 : 1)) : 4;
+        geo[tt] = (uint32_t)(r & 31) | ((uint32_t)(cc & 31) << 5) | ((uint32_t)cls << 10) | ((valid ? 1u : 0u) << 14);
     }
-    for (grp = blockIdx.x; grp < a.num_groups; grp += gridDim.x) {
-        live = tc_live_mask(a, grp, images, lane);
+    if (MODE != MODE_DYN) {
+        float* sb = reinterpret_cast<float*>(cx.s_tbl);
+        for (int k = threadIdx.x - 64; k < COUT; k += TC_EPI_THREADS) sb[k] = a.tbl[k];
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+    }
+    uint32_t tile_ctr = 0, it = 0;
+    for (int grp = blockIdx.x; grp < a.num_groups; grp += gridDim.x) {
+        const uint32_t live = tc_live_mask(a, grp, images, lane);
         if (!live) continue;
-        epi_bar_sync();                            // previous group's finalisation has read s_pol / s_part / s_tbl
-        if (MODE == MODE_DYN) {
-            for (int i = 0; i < images; i++) {
-                if (!(live & (1u << i))) continue;
-                const float4* src = reinterpret_cast<const float4*>(a.tbl + (size_t)a.action[grp * images + i] * 9 * COUT);
-                float4* dstt = reinterpret_cast<float4*>(cx.s_tbl + i * 9 * COUT);
-                for (int k = et; k < 9 * COUT / 4; k += TC_EPI_THREADS) dstt[k] = src[k];
+        const uint32_t par = it & 1, use = it >> 1;
+        if (MODE == MODE_DYN) mbar_wait(cx.tbl_full + par, use & 1);                 // bias tables of this group have landed
+        if (MODE != MODE_PLAIN) mbar_wait(cx.fin_empty + par, (use & 1) ^ 1);        // finaliser is done with this parity's buffers
+        const float* s_tbl = reinterpret_cast<const float*>(cx.s_tbl + par * cx.tbl_stride);
+        float* s_pol = reinterpret_cast<float*>(cx.s_pol + par * cx.pol_stride);
+        float* s_part = cx.s_part + par * (TC_SLOTS * 4 * 2);
+        for (int j = 0; j < NT; j++) {
+            const uint32_t c = tile_ctr + j;
+            if ((c & 1) != (uint32_t)pi) continue;
+            const uint32_t slot = c & (TC_SLOTS - 1);
+            const int img = j / tpi, tt = j - img * tpi;
+            const bool is_live = (live >> img) & 1u;
+            mbar_wait(cx.acc_full + slot, (c >> 2) & 1);
+            tc_fence_after();
+            uint32_t rr[COUT];
+            if (is_live) {
+                const uint32_t taddr = cx.tmem_base + ((uint32_t)(wq * 32) << 16) + slot * 128;
+                TMEM_LD_32X32B_X32(taddr, rr);
+                TMEM_LD_32X32B_X32(taddr + 32, (rr + 32));
+                if constexpr (COUT == 128) {
+                    TMEM_LD_32X32B_X32(taddr + 64, (rr + 64));
+                    TMEM_LD_32X32B_X32(taddr + 96, (rr + 96));
+                }
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            }
+            // the accumulator now lives in registers: hand the TMEM slot back to the MMA warp at once
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(cx.acc_empty + slot);
+            if (!is_live) continue;
+            const uint32_t g = tt == 0 ? geo[0] : (tt == 1 ? geo[1] : geo[2]);
+            const int r = g & 31, cc = (g >> 5) & 31, cls = (g >> 10) & 15;
+            const bool valid = (g >> 14) & 1u;
+            const int q = q0 + tt * 128 + wq * 32 + lane;
+            const bool store_ok = q < ps;
+            const float* tb = (MODE == MODE_DYN) ? s_tbl + (img * 9 + cls) * COUT : s_tbl;
+            const int item = grp * images + img;
+            const int oslot = a.out_slot ? a.out_slot[item] : item;
+            uint4* dst = reinterpret_cast<uint4*>(a.out) + (size_t)oslot * KC_OUT * ps + q;
+            float pol = 0.f, val = 0.f, rew = 0.f;
+#pragma unroll
+            for (int k = 0; k < KC_OUT; k++) {
+                const float4 b0 = *reinterpret_cast<const float4*>(tb + k * 8);
+                const float4 b1 = *reinterpret_cast<const float4*>(tb + k * 8 + 4);
+                const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+                float x[8];
+#pragma unroll
+                for (int e = 0; e < 8; e++) {
+                    x[e] = fmaxf(__uint_as_float(rr[k * 8 + e]) + bb[e], 0.f);
+                    if (MODE != MODE_PLAIN) {
+                        pol = fmaf(x[e], a.hw[k * 8 + e], pol);
+                        val = fmaf(x[e], a.hw[TC_C + k * 8 + e], val);
+                    }
+                    if (MODE == MODE_DYN) rew = fmaf(x[e], a.hw[2 * TC_C + k * 8 + e], rew);
+                }
+                if (store_ok) {
+                    uint4 w;
+                    w.x = pack_bf16(x[0], x[1]);
+                    w.y = pack_bf16(x[2], x[3]);
+                    w.z = pack_bf16(x[4], x[5]);
+                    w.w = pack_bf16(x[6], x[7]);
+                    if (!valid) w = make_uint4(0u, 0u, 0u, 0u);      // padding positions stay zero for the next conv
+                    dst[(size_t)k * ps] = w;
+                }
+            }
+            if (MODE != MODE_PLAIN) {
+                if (valid) s_pol[img * 384 + r * n + cc] = pol + a.sc.pol_b;
+                val = warp_sum_f(valid ? val : 0.f);
+                if (MODE == MODE_DYN) rew = warp_sum_f(valid ? rew : 0.f);
+                if (lane == 0) { s_part[(j * 4 + wq) * 2] = val; s_part[(j * 4 + wq) * 2 + 1] = rew; }
             }
         }
-        epi_bar_sync();
-        uint32_t ra[CPT], rb[CPT];
-        load_tile(0, ra);
-        for (int j = 0; j < NT; j += 2) {
-            if (j + 1 < NT) load_tile(j + 1, rb);
-            process_tile(j, ra);
-            if (j + 2 < NT) load_tile(j + 2, ra);
-            if (j + 1 < NT) process_tile(j + 1, rb);
-        }
         tile_ctr += NT;
-        if (MODE == MODE_PLAIN) continue;
-        epi_bar_sync();
-        // ---- per-image finalisation: value / reward heads and the policy softmax (one warp per image)
-        for (int img = ew; img < images; img += 8) {
+        it++;
+        if (MODE != MODE_PLAIN) {
+            __syncwarp();
+            if (lane == 0) mbar_arrive(cx.fin_full + par);         // release: s_pol / s_part of this warp are visible
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------- finaliser role
+// One warp: per image the value / reward heads (main.py:101-105, :118-120) and the policy softmax.
+template <int MODE>
+__device__ __forceinline__ void tc_finaliser_role(const TcArgs& a, const TcCtx& cx) {
+    const int lane = threadIdx.x & 31;
+    const int n = a.n, np = n * n;
+    const int tpi = a.tiles_per_image, images = a.images_per_group;
+    uint32_t it = 0;
+    for (int grp = blockIdx.x; grp < a.num_groups; grp += gridDim.x) {
+        const uint32_t live = tc_live_mask(a, grp, images, lane);
+        if (!live) continue;
+        const uint32_t par = it & 1, use = it >> 1;
+        mbar_wait(cx.fin_full + par, use & 1);
+        float* s_pol = reinterpret_cast<float*>(cx.s_pol + par * cx.pol_stride);
+        const float* s_part = cx.s_part + par * (TC_SLOTS * 4 * 2);
+        for (int img = 0; img < images; img++) {
             if (!(live & (1u << img))) continue;
             const int item = grp * images + img;
             float vs = 0.f, rs = 0.f;
-            for (int tt = 0; tt < tpi; tt++)
-                for (int w = 0; w < 8; w++) {
-                    vs += cx.s_part[((img * tpi + tt) * 8 + w) * 2];
-                    rs += cx.s_part[((img * tpi + tt) * 8 + w) * 2 + 1];
-                }
+            for (int k = 0; k < tpi * 4; k++) { vs += s_part[(img * tpi * 4 + k) * 2]; rs += s_part[(img * tpi * 4 + k) * 2 + 1]; }
             if (lane == 0) {
                 const float vm = vs / (float)np + a.sc.val_b;
                 a.value[item] = fmaf(a.sc.vfc_w, vm, a.sc.vfc_b);
@@ -345,24 +349,36 @@ __device__ __forceinline__ void tc_epilogue_role(const TcArgs& a, const TcEpiCtx
                     a.reward[item] = rw;
                 }
             }
-            const float* l0 = cx.s_pol + img * 384;
-            float* l1 = cx.s_pol + (images + img) * 384;             // reused for the summed logits
-            for (int k = lane; k < np; k += 32) l1[k] = l0[k] + l1[k] + a.sc.pol_b;
-            if (lane == 0) l1[np] = a.sc.pass_logit;
-            __syncwarp();
+            const float* lg = s_pol + img * 384;
             float* pol_out = a.policy + (size_t)item * (np + 1);
             if (!a.want_softmax) {
-                for (int k = lane; k <= np; k += 32) pol_out[k] = l1[k];
+                for (int k = lane; k < np; k += 32) pol_out[k] = lg[k];
+                if (lane == 0) pol_out[np] = a.sc.pass_logit;
             } else {
-                float m = -INFINITY;
-                for (int k = lane; k <= np; k += 32) m = fmaxf(m, l1[k]);
+                float m = a.sc.pass_logit;
+                for (int k = lane; k < np; k += 32) m = fmaxf(m, lg[k]);
                 m = warp_max_f(m);
+                float ev[12];                                       // np <= 361 = 11.3 x 32
                 float se = 0.f;
-                for (int k = lane; k <= np; k += 32) { float e = expf(l1[k] - m); l1[k] = e; se += e; }
-                se = warp_sum_f(se);
-                for (int k = lane; k <= np; k += 32) pol_out[k] = l1[k] / se;
+#pragma unroll
+                for (int u = 0; u < 12; u++) {
+                    const int k = u * 32 + lane;
+                    ev[u] = k < np ? expf(lg[k] - m) : 0.f;
+                    se += ev[u];
+                }
+                const float ep = expf(a.sc.pass_logit - m);
+                se = warp_sum_f(se) + ep;
+#pragma unroll
+                for (int u = 0; u < 12; u++) {
+                    const int k = u * 32 + lane;
+                    if (k < np) pol_out[k] = ev[u] / se;
+                }
+                if (lane == 0) pol_out[np] = ep / se;
             }
         }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(cx.fin_empty + par);
+        it++;
     }
 }
 
@@ -374,7 +390,7 @@ k_tc_conv(const __grid_constant__ TcArgs a) {
     constexpr uint32_t STAGE_BYTES = COUT * 128;          // [8 chunks][COUT][8] bf16
     constexpr uint32_t IDESC = tc_idesc(COUT);
     extern __shared__ __align__(128) uint8_t smem[];
-    const TcSmemLayout L = tc_smem_layout(a.n, CIN, COUT, a.stages);
+    const TcSmemLayout L = tc_smem_layout(a.n, CIN, COUT, a.stages, MODE == MODE_DYN);
     uint8_t* sA = smem;
     uint8_t* sB = smem + L.b_off;
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L.bar_off);
@@ -384,7 +400,10 @@ k_tc_conv(const __grid_constant__ TcArgs a) {
     uint64_t* acc_empty = bars + 4 + TC_SLOTS;      // [TC_SLOTS]
     uint64_t* b_full = bars + 4 + 2 * TC_SLOTS;     // [TC_MAX_STAGES]
     uint64_t* b_empty = b_full + TC_MAX_STAGES;     // [TC_MAX_STAGES]
-    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(b_empty + TC_MAX_STAGES);
+    uint64_t* tbl_full = b_empty + TC_MAX_STAGES;   // [2] per-action bias tables of a group (DYN)
+    uint64_t* fin_full = tbl_full + 2;              // [2] epilogue warps -> finaliser / producer
+    uint64_t* fin_empty = fin_full + 2;             // [2] finaliser -> epilogue warps
+    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + TC_NUM_BARS);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n = a.n, ps = a.ps;
@@ -395,8 +414,9 @@ k_tc_conv(const __grid_constant__ TcArgs a) {
 
     if (threadIdx.x == 0) {
         for (int h = 0; h < 2; h++) { mbar_init(a_full + h, 1); mbar_init(a_empty + h, 1); }
-        for (int s = 0; s < TC_SLOTS; s++) { mbar_init(acc_full + s, 1); mbar_init(acc_empty + s, 8); }
+        for (int s = 0; s < TC_SLOTS; s++) { mbar_init(acc_full + s, 1); mbar_init(acc_empty + s, 4); }
         for (int s = 0; s < TC_MAX_STAGES; s++) { mbar_init(b_full + s, 1); mbar_init(b_empty + s, 1); }
+        for (int p = 0; p < 2; p++) { mbar_init(tbl_full + p, 1); mbar_init(fin_full + p, 8); mbar_init(fin_empty + p, 1); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {
@@ -414,6 +434,18 @@ k_tc_conv(const __grid_constant__ TcArgs a) {
         for (int grp = blockIdx.x; grp < a.num_groups; grp += gridDim.x) {
             const uint32_t live = tc_live_mask(a, grp, images, lane);
             if (!live) continue;
+            if (MODE == MODE_DYN) {
+                // per-action bias tables of this group -> s_tbl[parity] (free once the epilogue of group it-2 is through)
+                const uint32_t par = it & 1, use = it >> 1;
+                if (use > 0) mbar_wait(fin_full + par, (use - 1) & 1);
+                if (lane == 0) mbar_expect_tx(tbl_full + par, 9u * COUT * 4 * __popc(live));
+                __syncwarp();
+                if (lane < images && ((live >> lane) & 1u)) {
+                    const int item = grp * images + lane;
+                    bulk_g2s(smem + L.tbl_off + par * L.tbl_stride + (uint32_t)lane * 9 * COUT * 4,
+                             a.tbl + (size_t)a.action[item] * 9 * COUT, 9u * COUT * 4, tbl_full + par);
+                }
+            }
             for (int h = 0; h < NH; h++) {
                 mbar_wait(a_empty + h, (it & 1) ^ 1);
                 if (lane == 0) mbar_expect_tx(a_full + h, half_bytes * __popc(live));
@@ -463,9 +495,7 @@ k_tc_conv(const __grid_constant__ TcArgs a) {
                     mbar_wait(b_full + s, bph);
                     tc_fence_after();
                     const int dy = (tap * 11) >> 5;                       // tap / 3 for tap < 9
-                    int shift = (dy - 1) * (n + 1) + (tap - 3 * dy - 1);
-                    if (a.dbg == 1) shift = 0;
-                    if (a.dbg == 2) shift = ((shift + q0) & ~7) - q0;
+                    const int shift = (dy - 1) * (n + 1) + (tap - 3 * dy - 1);
                     const uint32_t a_off = (uint32_t)(h * 8 * ps + shift);       // 16-byte units
                     const uint32_t b_lo = b_lo0 + s * (STAGE_BYTES >> 4);
                     const bool first = (h | tap) == 0;
@@ -500,16 +530,20 @@ k_tc_conv(const __grid_constant__ TcArgs a) {
             it++;
         }
     } else {
-        // ===================================================== epilogue (8 warps: TMEM lane quarter x column half)
-        TcEpiCtx cx;
-        cx.s_tbl = reinterpret_cast<float*>(smem + L.tbl_off);       // DYN: [images][9][COUT]; else [COUT]
-        cx.s_pol = reinterpret_cast<float*>(smem + L.pol_off);       // [2][images][384]
-        cx.s_part = reinterpret_cast<float*>(smem + L.part_off);     // [tile][warp][2]
+        TcCtx cx;
+        cx.s_tbl = smem + L.tbl_off;
+        cx.s_pol = smem + L.pol_off;
+        cx.s_part = reinterpret_cast<float*>(smem + L.part_off);
+        cx.tbl_stride = L.tbl_stride;
+        cx.pol_stride = L.pol_stride;
         cx.acc_full = acc_full;
         cx.acc_empty = acc_empty;
+        cx.tbl_full = tbl_full;
+        cx.fin_full = fin_full;
+        cx.fin_empty = fin_empty;
         cx.tmem_base = tmem_base;
-        if ((warp - 2) >> 2) tc_epilogue_role<COUT, MODE, 1>(a, cx);
-        else tc_epilogue_role<COUT, MODE, 0>(a, cx);
+        if (warp < 10) tc_epilogue_role<COUT, MODE>(a, cx);              // 8 warps: TMEM lane quarter x tile parity
+        else if (MODE != MODE_PLAIN) tc_finaliser_role<MODE>(a, cx);     // heads + softmax per image
     }
     tc_fence_before();
     __syncthreads();
@@ -722,14 +756,13 @@ int launch_tc_conv(TcArgs& a, int n, int B, cudaStream_t st) {
     a.images_per_group = TC_SLOTS / a.tiles_per_image;
     a.num_groups = ceil_div(B, a.images_per_group);
     const int kblocks = 9 * CIN / 64;
-    const TcSmemLayout L0 = tc_smem_layout(n, CIN, COUT, 0);
+    const TcSmemLayout L0 = tc_smem_layout(n, CIN, COUT, 0, MODE == MODE_DYN);
     int stages = ((int)TC_SMEM_LIMIT - (int)L0.total) / (COUT * 128);
     if (stages > TC_MAX_STAGES) stages = TC_MAX_STAGES;
     if (stages > kblocks) stages = kblocks;
     MZGO_CHECK_ARG(stages >= 2, "shared memory layout of %u B leaves no room for the weight ring", L0.total);
     a.stages = stages;
-    { const char* d = getenv("MZGO_TC_DBG"); a.dbg = d ? atoi(d) : 0; }
-    const TcSmemLayout L = tc_smem_layout(n, CIN, COUT, stages);
+    const TcSmemLayout L = tc_smem_layout(n, CIN, COUT, stages, MODE == MODE_DYN);
     const int grid = a.num_groups < num_sms() ? a.num_groups : num_sms();
     k_tc_conv<CIN, COUT, MODE><<<grid, TC_THREADS, L.total, st>>>(a);
     mzgo_count_launch();
