@@ -382,6 +382,83 @@ __device__ __forceinline__ void tc_finaliser_role(const TcArgs& a, const TcCtx& 
     }
 }
 
+// ---------------------------------------------------------------------------------------- MMA issuer role
+// The whole warp runs the loop so that every value stays warp-uniform (uniform registers, no per-thread
+// serialisation around UTCHMMA); one elected lane issues tcgen05.mma / tcgen05.commit.  NT (tiles per
+// group) is a template parameter so that the 4 x NT MMAs of a k-block are straight-line code.
+struct TcMmaCtx {
+    uint32_t sA, sB;
+    uint64_t *a_full, *a_empty, *b_full, *b_empty, *acc_full, *acc_empty;
+    uint32_t tmem_base;
+};
+
+template <int CIN, int COUT, int NT>
+__device__ __forceinline__ void tc_mma_role(const TcArgs& a, const TcMmaCtx& mx) {
+    constexpr int KC_IN = CIN / 8, NH = CIN / 64;
+    constexpr uint32_t STAGE_BYTES = COUT * 128;
+    constexpr uint32_t IDESC = tc_idesc(COUT);
+    const int lane = threadIdx.x & 31;
+    const int n = a.n, ps = a.ps, q0 = n + 2;
+    const int tpi = a.tiles_per_image, images = a.images_per_group;
+    const uint32_t slab_bytes = (uint32_t)KC_IN * ps * 16;
+    const bool leader = elect_one();
+    uint32_t it = 0, s = 0, bph = 0, tile_ctr = 0;
+    const uint32_t a_hi = desc_hi(128), b_hi = desc_hi(128);
+    const uint32_t b_lo0 = desc_lo(mx.sB, COUT * 16);
+    uint32_t a_lo[NT];
+#pragma unroll
+    for (int j = 0; j < NT; j++) {
+        const int img = j / tpi, tt = j - img * tpi;
+        a_lo[j] = desc_lo(mx.sA + img * slab_bytes + (uint32_t)(q0 + tt * 128) * 16, ps * 16);
+    }
+    const uint32_t ks_step = 2 * ps;
+    for (int grp = blockIdx.x; grp < a.num_groups; grp += gridDim.x) {
+        const uint32_t live = tc_live_mask(a, grp, images, lane);
+        if (!live) continue;
+        uint32_t d_col[NT];
+#pragma unroll
+        for (int j = 0; j < NT; j++) d_col[j] = mx.tmem_base + ((tile_ctr + j) & (TC_SLOTS - 1)) * 128;
+        // first touch of the TMEM slots of this group: the epilogue must have drained them
+#pragma unroll
+        for (int j = 0; j < NT; j++) {
+            const uint32_t c = tile_ctr + j;
+            mbar_wait(mx.acc_empty + (c & (TC_SLOTS - 1)), ((c >> 2) & 1) ^ 1);
+        }
+        for (int h = 0; h < NH; h++) {
+            mbar_wait(mx.a_full + h, it & 1);
+            for (int tap = 0; tap < 9; tap++) {
+                mbar_wait(mx.b_full + s, bph);
+                tc_fence_after();
+                const int dy = (tap * 11) >> 5;                       // tap / 3 for tap < 9
+                const int shift = (dy - 1) * (n + 1) + (tap - 3 * dy - 1);
+                const uint32_t a_off = (uint32_t)(h * 8 * ps + shift);       // 16-byte units
+                const uint32_t b_lo = b_lo0 + s * (STAGE_BYTES >> 4);
+                const uint32_t acc0 = (h | tap) != 0;
+                if (leader) {
+#pragma unroll
+                    for (int ks = 0; ks < 4; ks++) {
+#pragma unroll
+                        for (int j = 0; j < NT; j++)
+                            umma_bf16(d_col[j], a_lo[j] + a_off + ks * ks_step, a_hi, b_lo + ks * (2 * COUT), b_hi, IDESC,
+                                      ks == 0 ? acc0 : 1u);
+                    }
+                    umma_commit(mx.b_empty + s);          // frees the weight stage when these MMAs retire
+                }
+                __syncwarp();
+                if (++s == (uint32_t)a.stages) { s = 0; bph ^= 1; }
+            }
+            if (leader) umma_commit(mx.a_empty + h);      // this half of the input slab may be overwritten
+        }
+        if (leader) {
+#pragma unroll
+            for (int j = 0; j < NT; j++) umma_commit(mx.acc_full + ((tile_ctr + j) & (TC_SLOTS - 1)));
+        }
+        __syncwarp();
+        tile_ctr += NT;
+        it++;
+    }
+}
+
 // ---------------------------------------------------------------------------------------- the fused kernel
 template <int CIN, int COUT, int MODE>
 __global__ void __launch_bounds__(TC_THREADS, 1)
@@ -471,63 +548,16 @@ k_tc_conv(const __grid_constant__ TcArgs a) {
         }
     } else if (warp == 1) {
         // ===================================================== MMA issuer
-        // The whole warp runs the loop so that every value stays warp-uniform (uniform registers, no
-        // per-thread serialisation around UTCHMMA); one elected lane issues tcgen05.mma / tcgen05.commit.
-        const bool leader = elect_one();
-        uint32_t it = 0, s = 0, bph = 0, tile_ctr = 0;
-        const uint32_t a_hi = desc_hi(128), b_hi = desc_hi(128);
-        const uint32_t b_lo0 = desc_lo(smem_u32(sB), COUT * 16);
-        uint32_t a_lo[TC_SLOTS];
-#pragma unroll
-        for (int j = 0; j < TC_SLOTS; j++) {
-            const int img = j / tpi, tt = j - img * tpi;
-            a_lo[j] = desc_lo(smem_u32(sA) + img * slab_bytes + (uint32_t)(q0 + tt * 128) * 16, ps * 16);
-        }
-        for (int grp = blockIdx.x; grp < a.num_groups; grp += gridDim.x) {
-            const uint32_t live = tc_live_mask(a, grp, images, lane);
-            if (!live) continue;
-            uint32_t d_col[TC_SLOTS];
-#pragma unroll
-            for (int j = 0; j < TC_SLOTS; j++) d_col[j] = tmem_base + ((tile_ctr + j) & (TC_SLOTS - 1)) * 128;
-            for (int h = 0; h < NH; h++) {
-                mbar_wait(a_full + h, it & 1);
-                for (int tap = 0; tap < 9; tap++) {
-                    mbar_wait(b_full + s, bph);
-                    tc_fence_after();
-                    const int dy = (tap * 11) >> 5;                       // tap / 3 for tap < 9
-                    const int shift = (dy - 1) * (n + 1) + (tap - 3 * dy - 1);
-                    const uint32_t a_off = (uint32_t)(h * 8 * ps + shift);       // 16-byte units
-                    const uint32_t b_lo = b_lo0 + s * (STAGE_BYTES >> 4);
-                    const bool first = (h | tap) == 0;
-                    if (first) {
-                        // first touch of the TMEM slots of this group: the epilogue must have drained them
-                        for (int j = 0; j < NT; j++) {
-                            const uint32_t c = tile_ctr + j;
-                            mbar_wait(acc_empty + (c & (TC_SLOTS - 1)), ((c >> 2) & 1) ^ 1);
-                        }
-                        tc_fence_after();
-                    }
-#pragma unroll
-                    for (int ks = 0; ks < 4; ks++) {
-#pragma unroll
-                        for (int j = 0; j < TC_SLOTS; j++) {
-                            if (j < NT && leader)
-                                umma_bf16(d_col[j], a_lo[j] + a_off + ks * 2 * ps, a_hi, b_lo + ks * (2 * COUT), b_hi, IDESC,
-                                          (first && ks == 0) ? 0u : 1u);
-                        }
-                    }
-                    if (leader) umma_commit(b_empty + s);     // frees the weight stage when these MMAs retire
-                    __syncwarp();
-                    if (++s == (uint32_t)a.stages) { s = 0; bph ^= 1; }
-                }
-                if (leader) umma_commit(a_empty + h);         // this half of the input slab may be overwritten
-            }
-            if (leader) {
-                for (int j = 0; j < NT; j++) umma_commit(acc_full + ((tile_ctr + j) & (TC_SLOTS - 1)));
-            }
-            __syncwarp();
-            tile_ctr += NT;
-            it++;
+        TcMmaCtx mx;
+        mx.sA = smem_u32(sA); mx.sB = smem_u32(sB);
+        mx.a_full = a_full; mx.a_empty = a_empty; mx.b_full = b_full; mx.b_empty = b_empty;
+        mx.acc_full = acc_full; mx.acc_empty = acc_empty;
+        mx.tmem_base = tmem_base;
+        switch (NT) {
+            case 1: tc_mma_role<CIN, COUT, 1>(a, mx); break;
+            case 2: tc_mma_role<CIN, COUT, 2>(a, mx); break;
+            case 3: tc_mma_role<CIN, COUT, 3>(a, mx); break;
+            default: tc_mma_role<CIN, COUT, 4>(a, mx); break;
         }
     } else {
         TcCtx cx;
