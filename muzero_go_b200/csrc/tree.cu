@@ -325,6 +325,236 @@ k_tree_expand_backup(mzgo_tree_t t, mzgo_search_params_t p, const float* __restr
     }
 }
 
+// ------------------------------------------------------------------------------------------ fused step
+// One launch per simulation: expand + backup of the leaf evaluated by the previous network call
+// (main.py:300-313, :365-368), then the selection of the next leaf (main.py:318-363).  TPG threads
+// work on one game (128 when A > 96, else one warp), so a PUCT level is one coalesced pass over the
+// edge arrays with up to three edges per thread, and the backup updates all edges of the selection
+// path in parallel: the path is written by the selection into the scratch row ([g][0][A] of `prior`).
+// Arithmetic is the same, operation for operation, as in k_tree_select / k_tree_expand_backup.
+constexpr int STEP_THREADS = 128;
+constexpr int STEP_EPT = 3;   // edges per thread: A <= 3 * TPG
+
+template <int TPG>
+__device__ __forceinline__ void step_sync() {
+    if (TPG == 32) __syncwarp(); else __syncthreads();
+}
+
+template <int TPG>
+__global__ void __launch_bounds__(STEP_THREADS)
+k_tree_step(mzgo_tree_t t, mzgo_search_params_t p, const float* __restrict__ soft, const float* __restrict__ reward,
+            const float* __restrict__ value, const uint32_t* __restrict__ choice_stream, int stride, int do_backup,
+            int do_select) {
+    constexpr int GPB = STEP_THREADS / TPG;     // games per block
+    constexpr int WPG = TPG / 32;               // warps per game
+    constexpr int NW = STEP_EPT * WPG;          // ballot words per game (word w covers actions [32w, 32w+32))
+    __shared__ uint32_t s_open[GPB][NW];
+    __shared__ uint32_t s_live[GPB][WPG];
+    __shared__ double s_min[GPB][WPG], s_max[GPB][WPG], s_best[GPB][WPG];
+    __shared__ int s_besta[GPB][WPG], s_bestn[GPB][WPG];
+    const int sub = threadIdx.x / TPG, tid = threadIdx.x % TPG;
+    const int wig = tid >> 5, lane = tid & 31;
+    const int g = blockIdx.x * GPB + sub;
+    if (g >= t.G) return;                        // TPG == 128: the whole block; TPG == 32: whole warps
+    const int A = t.A, M = t.M;
+    int* path = reinterpret_cast<int*>(t.prior + (size_t)g * M * A);   // scratch row of the root (its priors are float64, elsewhere)
+
+    // ---------------------------------------------------------------- expand + backup
+    const int act = do_backup ? t.leaf_action[g] : -1;
+    if (act >= 0) {
+        const int par = t.leaf_parent[g];
+        const int nw = t.leaf_node[g];
+        const int depth = t.leaf_depth[g];
+        const size_t nbase = ((size_t)g * M + nw) * A;
+        const float* mask = t.root_mask + (size_t)g * A;
+#pragma unroll
+        for (int e = 0; e < STEP_EPT; e++) {
+            const int a = e * TPG + tid;
+            if (a < A) {
+                // prior_child = policy_child[a] if valid_mask[a] > 0 else 0   (the ROOT's mask, main.py:303)
+                t.prior[nbase + a] = mask[a] > 0.f ? soft[(size_t)g * A + a] : 0.f;
+                t.edge_visit[nbase + a] = 0;
+                t.edge_vsum[nbase + a] = 0.0;
+                t.child[nbase + a] = (int16_t)-1;
+            }
+        }
+        // backup_value = reward.item() + discount * value.item()   (main.py:311), float64
+        const double bv = __dadd_rn((double)reward[g], __dmul_rn(p.discount, (double)value[g]));
+        if (depth <= A) {
+            for (int d = tid; d < depth; d += TPG) {
+                const int pk = path[d];
+                const size_t e = ((size_t)g * M + (pk >> 9)) * A + (pk & 511);
+                t.edge_visit[e] += 1;
+                t.edge_vsum[e] = __dadd_rn(t.edge_vsum[e], bv);
+            }
+        }
+        if (tid == 0) {
+            t.child[((size_t)g * M + par) * A + act] = (int16_t)nw;
+            t.parent[(size_t)g * M + nw] = par * 512 + act;
+            t.n_nodes[g] = nw + 1;
+            if (depth > A) {                     // path longer than the scratch row: walk the parent links
+                int node = nw;
+                while (node != 0) {
+                    const int pk = t.parent[(size_t)g * M + node];
+                    const int pn = pk >> 9, pa = pk & 511;
+                    const size_t e = ((size_t)g * M + pn) * A + pa;
+                    t.edge_visit[e] += 1;
+                    t.edge_vsum[e] = __dadd_rn(t.edge_vsum[e], bv);
+                    node = pn;
+                }
+            }
+            t.root_visit[g] += 1;
+            t.root_vsum[g] = __dadd_rn(t.root_vsum[g], bv);
+            t.sims_done[g] += 1;
+            t.depth_sum[g] += depth;
+        }
+    }
+    if (!do_select) return;
+    step_sync<TPG>();                            // the statistics written above are read below by other threads
+
+    // ---------------------------------------------------------------- select
+    if (!t.active[g]) {
+        if (tid == 0) { t.leaf_parent[g] = -1; t.leaf_action[g] = -1; }
+        return;
+    }
+    int node = 0, depth = 1;
+    int npar = t.root_visit[g];
+    int sel_parent = -1, sel_action = -1;
+    while (true) {
+        const size_t base = ((size_t)g * M + node) * A;
+        double cp[STEP_EPT];
+        int nv[STEP_EPT];
+        uint32_t live = 0u;
+#pragma unroll
+        for (int e = 0; e < STEP_EPT; e++) {
+            const int a = e * TPG + tid;
+            bool pos = false, opn = false;
+            cp[e] = 0.0; nv[e] = 0;
+            if (a < A) {
+                nv[e] = t.edge_visit[base + a];
+                if (node == 0) {
+                    const double pr = t.root_prior[(size_t)g * A + a];
+                    pos = pr > 0.0;
+                    cp[e] = __dmul_rn(p.c_puct, pr);
+                } else {
+                    const float pr = t.prior[base + a];
+                    pos = pr > 0.f;
+                    cp[e] = (double)__fmul_rn((float)p.c_puct, pr);   // c*P rounds in float32 (NEP 50)
+                }
+                opn = pos && nv[e] == 0;
+            }
+            if (pos) live |= 1u << e;
+            const uint32_t b = __ballot_sync(FULL_MASK, opn);
+            if (lane == 0) s_open[sub][e * WPG + wig] = b;
+        }
+        const uint32_t any_live = __ballot_sync(FULL_MASK, live != 0u);
+        if (lane == 0) s_live[sub][wig] = any_live;
+        step_sync<TPG>();
+        int n_open = 0;
+        uint32_t all_live = 0u;
+#pragma unroll
+        for (int w = 0; w < NW; w++) n_open += __popc(s_open[sub][w]);
+#pragma unroll
+        for (int w = 0; w < WPG; w++) all_live |= s_live[sub][w];
+        if (n_open > 0) {
+            // random.choice(unexpanded), main.py:322-325
+            const uint32_t ctr = t.choice_ctr[g];
+            const uint32_t r = choice_stream ? choice_stream[(size_t)g * stride + ctr]
+                                             : mzgo_rand_u32(p.seed, (uint32_t)g, 0x20000u + (uint32_t)t.move_index, ctr);
+            int k = (int)(r % (uint32_t)n_open);
+            int a_sel = -1;
+#pragma unroll
+            for (int w = 0; w < NW; w++) {
+                const uint32_t b = s_open[sub][w];
+                const int c = __popc(b);
+                if (a_sel < 0) {
+                    if (k < c) a_sel = w * 32 + (int)__fns(b, 0, k + 1);
+                    else k -= c;
+                }
+            }
+            sel_parent = node;
+            sel_action = a_sel;
+            step_sync<TPG>();                    // everyone has read choice_ctr
+            if (tid == 0) t.choice_ctr[g] = ctr + 1u;
+            break;
+        }
+        if (!all_live) break;                    // nothing selectable: simulation dropped
+        // Q of every live edge, min-max normalisation set = prior > 0 (main.py:328-339)
+        double q[STEP_EPT];
+        double qmin = INFINITY, qmax = -INFINITY;
+#pragma unroll
+        for (int e = 0; e < STEP_EPT; e++) {
+            q[e] = 0.0;
+            if (live & (1u << e)) {
+                const int a = e * TPG + tid;
+                if (nv[e] > 0) q[e] = __ddiv_rn(t.edge_vsum[base + a], (double)nv[e]);
+                qmin = fmin(qmin, q[e]);
+                qmax = fmax(qmax, q[e]);
+            }
+        }
+        qmin = warp_min_d(qmin);
+        qmax = warp_max_d(qmax);
+        if (WPG > 1) {
+            if (lane == 0) { s_min[sub][wig] = qmin; s_max[sub][wig] = qmax; }
+            step_sync<TPG>();
+#pragma unroll
+            for (int w = 0; w < WPG; w++) { qmin = fmin(qmin, s_min[sub][w]); qmax = fmax(qmax, s_max[sub][w]); }
+        }
+        const double sq = __dsqrt_rn((double)(npar + 1));
+        const bool norm = qmax > qmin;
+        const double range = __dsub_rn(qmax, qmin);
+        double best = -INFINITY;
+        int best_a = -1, best_n = 0;
+#pragma unroll
+        for (int e = 0; e < STEP_EPT; e++) {
+            if (live & (1u << e)) {
+                const double qn = norm ? __ddiv_rn(__dsub_rn(q[e], qmin), range) : q[e];
+                const double u = __ddiv_rn(__dmul_rn(cp[e], sq), (double)(1 + nv[e]));
+                const double score = __dadd_rn(qn, u);
+                if (score > best) { best = score; best_a = e * TPG + tid; best_n = nv[e]; }   // e ascending = action ascending
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const double ob = __shfl_xor_sync(FULL_MASK, best, o);
+            const int oa = __shfl_xor_sync(FULL_MASK, best_a, o);
+            const int on = __shfl_xor_sync(FULL_MASK, best_n, o);
+            const bool take = (oa >= 0) && (best_a < 0 || ob > best || (ob == best && oa < best_a));
+            if (take) { best = ob; best_a = oa; best_n = on; }
+        }
+        if (WPG > 1) {
+            if (lane == 0) { s_best[sub][wig] = best; s_besta[sub][wig] = best_a; s_bestn[sub][wig] = best_n; }
+            step_sync<TPG>();
+            best = s_best[sub][0]; best_a = s_besta[sub][0]; best_n = s_bestn[sub][0];
+#pragma unroll
+            for (int w = 1; w < WPG; w++) {
+                const double ob = s_best[sub][w];
+                const int oa = s_besta[sub][w], on = s_bestn[sub][w];
+                const bool take = (oa >= 0) && (best_a < 0 || ob > best || (ob == best && oa < best_a));
+                if (take) { best = ob; best_a = oa; best_n = on; }
+            }
+        }
+        if (best_a < 0) break;                   // only NaN / -inf scores: the reference falls out of the loop too
+        if (tid == 0 && depth <= A) path[depth - 1] = node * 512 + best_a;
+        node = (int)t.child[base + best_a];
+        npar = best_n;
+        depth++;
+        step_sync<TPG>();                        // shared scratch is reused by the next level
+    }
+    if (tid == 0) {
+        const int nn = t.n_nodes[g];
+        if (sel_action >= 0 && nn >= M) sel_action = -1;   // arena full: drop (cannot happen when M > simulations)
+        if (sel_action >= 0 && depth <= A) path[depth - 1] = sel_parent * 512 + sel_action;
+        t.leaf_parent[g] = sel_action >= 0 ? sel_parent : -1;
+        t.leaf_action[g] = sel_action;
+        t.leaf_node[g] = nn;
+        t.leaf_depth[g] = depth;
+        t.leaf_in_slot[g] = sel_action >= 0 ? g * M + sel_parent : -1;
+        t.leaf_out_slot[g] = sel_action >= 0 ? g * M + nn : -1;
+        if (sel_action < 0) t.dropped[g] += 1;
+    }
+}
+
 // main.py:666-669
 __global__ void k_tree_visit_counts(mzgo_tree_t t, int32_t* out) {
     const long total = (long)t.G * t.A;
@@ -494,6 +724,24 @@ extern "C" int mzgo_tree_expand_backup(const mzgo_tree_t* tree, const mzgo_searc
     if (tree->G == 0) return MZGO_OK;
     k_tree_expand_backup<<<ceil_div(tree->G, TREE_WARPS), TREE_WARPS * 32, 0, (cudaStream_t)stream>>>(*tree, *p, soft,
                                                                                                       reward, value);
+    mzgo_count_launch();
+    MZGO_LAUNCH_CHECK();
+    return MZGO_OK;
+}
+
+// Fused simulation step (engine path): expand + backup of the previous leaf, then the next selection.
+int mzgo_tree_step(const mzgo_tree_t* tree, const mzgo_search_params_t* p, const float* soft, const float* reward,
+                   const float* value, const uint32_t* choice_stream, int stride, int do_backup, int do_select,
+                   cudaStream_t st) {
+    if (int e = check_tree(tree)) return e;
+    MZGO_CHECK_ARG(p && (!do_backup || (soft && reward && value)), "NULL argument");
+    if (tree->G == 0) return MZGO_OK;
+    if (tree->A <= STEP_EPT * 32)
+        k_tree_step<32><<<ceil_div(tree->G, STEP_THREADS / 32), STEP_THREADS, 0, st>>>(*tree, *p, soft, reward, value,
+                                                                                      choice_stream, stride, do_backup, do_select);
+    else
+        k_tree_step<128><<<tree->G, STEP_THREADS, 0, st>>>(*tree, *p, soft, reward, value, choice_stream, stride,
+                                                          do_backup, do_select);
     mzgo_count_launch();
     MZGO_LAUNCH_CHECK();
     return MZGO_OK;
