@@ -341,7 +341,7 @@ __device__ __forceinline__ void step_sync() {
 }
 
 template <int TPG>
-__global__ void __launch_bounds__(STEP_THREADS)
+__global__ void __launch_bounds__(STEP_THREADS, 10)
 k_tree_step(mzgo_tree_t t, mzgo_search_params_t p, const float* __restrict__ soft, const float* __restrict__ reward,
             const float* __restrict__ value, const uint32_t* __restrict__ choice_stream, int stride, int do_backup,
             int do_select) {
@@ -360,28 +360,48 @@ k_tree_step(mzgo_tree_t t, mzgo_search_params_t p, const float* __restrict__ sof
     int* path = reinterpret_cast<int*>(t.prior + (size_t)g * M * A);   // scratch row of the root (its priors are float64, elsewhere)
 
     // ---------------------------------------------------------------- expand + backup
+    // everything the backup needs is fetched in one round trip (all of it is valid memory in any case)
     const int act = do_backup ? t.leaf_action[g] : -1;
+    const int par = t.leaf_parent[g];
+    const int nw = t.leaf_node[g];
+    const int depth_b = t.leaf_depth[g];
+    const float rew_g = do_backup ? reward[g] : 0.f, val_g = do_backup ? value[g] : 0.f;
+    const int is_active = t.active[g];
     if (act >= 0) {
-        const int par = t.leaf_parent[g];
-        const int nw = t.leaf_node[g];
-        const int depth = t.leaf_depth[g];
+        const int depth = depth_b;
         const size_t nbase = ((size_t)g * M + nw) * A;
         const float* mask = t.root_mask + (size_t)g * A;
+        float mk[STEP_EPT], sf[STEP_EPT];
+        int pk_mine = -1;
+        if (depth <= A && tid < depth) pk_mine = path[tid];
+#pragma unroll
+        for (int e = 0; e < STEP_EPT; e++) {
+            const int a = e * TPG + tid;
+            mk[e] = 0.f; sf[e] = 0.f;
+            if (a < A) { mk[e] = mask[a]; sf[e] = soft[(size_t)g * A + a]; }
+        }
 #pragma unroll
         for (int e = 0; e < STEP_EPT; e++) {
             const int a = e * TPG + tid;
             if (a < A) {
                 // prior_child = policy_child[a] if valid_mask[a] > 0 else 0   (the ROOT's mask, main.py:303)
-                t.prior[nbase + a] = mask[a] > 0.f ? soft[(size_t)g * A + a] : 0.f;
+                t.prior[nbase + a] = mk[e] > 0.f ? sf[e] : 0.f;
                 t.edge_visit[nbase + a] = 0;
                 t.edge_vsum[nbase + a] = 0.0;
                 t.child[nbase + a] = (int16_t)-1;
             }
         }
         // backup_value = reward.item() + discount * value.item()   (main.py:311), float64
-        const double bv = __dadd_rn((double)reward[g], __dmul_rn(p.discount, (double)value[g]));
+        const double bv = __dadd_rn((double)rew_g, __dmul_rn(p.discount, (double)val_g));
         if (depth <= A) {
-            for (int d = tid; d < depth; d += TPG) {
+            if (pk_mine >= 0) {
+                const size_t e = ((size_t)g * M + (pk_mine >> 9)) * A + (pk_mine & 511);
+                const int ev = t.edge_visit[e];
+                const double es = t.edge_vsum[e];
+                t.edge_visit[e] = ev + 1;
+                t.edge_vsum[e] = __dadd_rn(es, bv);
+            }
+            for (int d = tid + TPG; d < depth; d += TPG) {
                 const int pk = path[d];
                 const size_t e = ((size_t)g * M + (pk >> 9)) * A + (pk & 511);
                 t.edge_visit[e] += 1;
@@ -413,33 +433,45 @@ k_tree_step(mzgo_tree_t t, mzgo_search_params_t p, const float* __restrict__ sof
     step_sync<TPG>();                            // the statistics written above are read below by other threads
 
     // ---------------------------------------------------------------- select
-    if (!t.active[g]) {
+    if (!is_active) {
         if (tid == 0) { t.leaf_parent[g] = -1; t.leaf_action[g] = -1; }
         return;
     }
     int node = 0, depth = 1;
     int npar = t.root_visit[g];
+    const uint32_t ctr0 = t.choice_ctr[g];
+    const int nn0 = t.n_nodes[g];
     int sel_parent = -1, sel_action = -1;
     while (true) {
         const size_t base = ((size_t)g * M + node) * A;
         double cp[STEP_EPT];
         int nv[STEP_EPT];
         uint32_t live = 0u;
+        // all loads of the level first, so that they are in flight together
+        double prd[STEP_EPT];
+        float prf[STEP_EPT];
+#pragma unroll
+        for (int e = 0; e < STEP_EPT; e++) {
+            const int a = e * TPG + tid;
+            nv[e] = 0; prd[e] = 0.0; prf[e] = 0.f;
+            if (a < A) {
+                nv[e] = t.edge_visit[base + a];
+                if (node == 0) prd[e] = t.root_prior[(size_t)g * A + a];
+                else prf[e] = t.prior[base + a];
+            }
+        }
 #pragma unroll
         for (int e = 0; e < STEP_EPT; e++) {
             const int a = e * TPG + tid;
             bool pos = false, opn = false;
-            cp[e] = 0.0; nv[e] = 0;
+            cp[e] = 0.0;
             if (a < A) {
-                nv[e] = t.edge_visit[base + a];
                 if (node == 0) {
-                    const double pr = t.root_prior[(size_t)g * A + a];
-                    pos = pr > 0.0;
-                    cp[e] = __dmul_rn(p.c_puct, pr);
+                    pos = prd[e] > 0.0;
+                    cp[e] = __dmul_rn(p.c_puct, prd[e]);
                 } else {
-                    const float pr = t.prior[base + a];
-                    pos = pr > 0.f;
-                    cp[e] = (double)__fmul_rn((float)p.c_puct, pr);   // c*P rounds in float32 (NEP 50)
+                    pos = prf[e] > 0.f;
+                    cp[e] = (double)__fmul_rn((float)p.c_puct, prf[e]);   // c*P rounds in float32 (NEP 50)
                 }
                 opn = pos && nv[e] == 0;
             }
@@ -458,7 +490,7 @@ k_tree_step(mzgo_tree_t t, mzgo_search_params_t p, const float* __restrict__ sof
         for (int w = 0; w < WPG; w++) all_live |= s_live[sub][w];
         if (n_open > 0) {
             // random.choice(unexpanded), main.py:322-325
-            const uint32_t ctr = t.choice_ctr[g];
+            const uint32_t ctr = ctr0;
             const uint32_t r = choice_stream ? choice_stream[(size_t)g * stride + ctr]
                                              : mzgo_rand_u32(p.seed, (uint32_t)g, 0x20000u + (uint32_t)t.move_index, ctr);
             int k = (int)(r % (uint32_t)n_open);
@@ -474,7 +506,6 @@ k_tree_step(mzgo_tree_t t, mzgo_search_params_t p, const float* __restrict__ sof
             }
             sel_parent = node;
             sel_action = a_sel;
-            step_sync<TPG>();                    // everyone has read choice_ctr
             if (tid == 0) t.choice_ctr[g] = ctr + 1u;
             break;
         }
@@ -485,9 +516,12 @@ k_tree_step(mzgo_tree_t t, mzgo_search_params_t p, const float* __restrict__ sof
 #pragma unroll
         for (int e = 0; e < STEP_EPT; e++) {
             q[e] = 0.0;
+            if ((live & (1u << e)) && nv[e] > 0) q[e] = t.edge_vsum[base + e * TPG + tid];
+        }
+#pragma unroll
+        for (int e = 0; e < STEP_EPT; e++) {
             if (live & (1u << e)) {
-                const int a = e * TPG + tid;
-                if (nv[e] > 0) q[e] = __ddiv_rn(t.edge_vsum[base + a], (double)nv[e]);
+                if (nv[e] > 0) q[e] = __ddiv_rn(q[e], (double)nv[e]);
                 qmin = fmin(qmin, q[e]);
                 qmax = fmax(qmax, q[e]);
             }
@@ -542,7 +576,7 @@ k_tree_step(mzgo_tree_t t, mzgo_search_params_t p, const float* __restrict__ sof
         step_sync<TPG>();                        // shared scratch is reused by the next level
     }
     if (tid == 0) {
-        const int nn = t.n_nodes[g];
+        const int nn = act >= 0 ? nw + 1 : nn0;
         if (sel_action >= 0 && nn >= M) sel_action = -1;   // arena full: drop (cannot happen when M > simulations)
         if (sel_action >= 0 && depth <= A) path[depth - 1] = sel_parent * 512 + sel_action;
         t.leaf_parent[g] = sel_action >= 0 ? sel_parent : -1;
