@@ -152,6 +152,120 @@ def run_mcts(obs, initial_fn, recurrent_fn, num_simulations, noise, choice_strea
     return tree, mask
 
 
+# ---------------------------------------------------------------------------------------------
+# self_play.py variant (/root/reference/self_play.py:142-343).  Differences from main.py, all on the hot path:
+#   * root priors re-masked and renormalised in float64 after the noise mix (:166-178);
+#   * child priors = float32 softmax * float64 mask -> float32, float32 pairwise sum, float32 divide (:210-216);
+#   * exploration term uses sqrt(max(1, N_parent)) (:297-300);
+#   * a node without any prior > 0 is terminal: the simulation backs 0 up along the path (:188-190, :245-247, :268-270);
+#   * backup alternates sign per level starting with +value at the new leaf (:340-343).
+# At PUCT time every live child is expanded (the unexpanded branch is taken first, :283-287), so the
+# "expanded children only" min/max set (:262-277) equals the set of all edges with prior > 0.
+def _uniform_over(mask, like):
+    """self_play.py:163, :178, :216: the rare fallback when a masked policy sums to zero."""
+    ms = mask.sum()
+    return np.ones_like(like) * mask / ms if ms > 0 else np.ones_like(like) / len(like)
+
+
+def root_priors_selfplay(softmax_f32, valid_mask, noise, epsilon):
+    """self_play.py:158-178 -> float64 [A]."""
+    policy = np.array(softmax_f32, dtype=np.float32, copy=True)
+    policy *= valid_mask
+    total = policy.sum()
+    if total > 0:
+        policy /= total
+    else:
+        policy = _uniform_over(valid_mask, policy)
+    policy = (1 - epsilon) * policy + epsilon * np.asarray(noise, dtype=np.float64)
+    policy *= valid_mask
+    total = policy.sum()
+    if total > 0:
+        policy /= total
+    else:
+        policy = _uniform_over(valid_mask, policy)
+    return np.where(valid_mask > 0, policy, 0.0)
+
+
+def child_priors_selfplay(softmax_f32, valid_mask):
+    """self_play.py:210-222 -> [A] (float32 unless the zero-sum fallback promoted it to float64)."""
+    policy = np.array(softmax_f32, dtype=np.float32, copy=True)
+    policy *= valid_mask
+    total = policy.sum()
+    if total > 0:
+        policy /= total
+    else:
+        policy = _uniform_over(valid_mask, policy)
+    return np.where(valid_mask > 0, policy, policy.dtype.type(0))
+
+
+class TreeRefSelfPlay(TreeRef):
+    def select(self, choose):
+        """self_play.py:239-331.  Returns (path, action); action None = terminal leaf."""
+        node = 0
+        path = [0]
+        while True:
+            pri, ch = self.prior[node], self.child[node]
+            live = [a for a in range(self.A) if pri[a] > 0]
+            if not live:                        # :245-247 / :268-270
+                return path, None
+            open_edges = [a for a in live if ch[a] < 0]
+            if open_edges:                      # :283-287
+                return path, choose(open_edges)
+            qs = [self.q(int(ch[a])) for a in live]
+            lo, hi = min(qs), max(qs)
+            best, best_a = -float('inf'), None
+            for a, qa in zip(live, qs):
+                qn = (qa - lo) / (hi - lo) if hi > lo else qa
+                n = self.visit[int(ch[a])]
+                u = self.c_puct * pri[a] * np.sqrt(max(1, self.visit[node])) / (1 + n)
+                score = qn + u
+                if score > best:
+                    best, best_a = score, a
+            if best_a is None:                  # :315-320
+                return path, None
+            node = int(ch[best_a])
+            path.append(node)
+
+    def backup(self, path, value):
+        """self_play.py:337-343."""
+        for i, node in enumerate(reversed(path)):
+            self.visit[node] += 1
+            self.value_sum[node] += value * ((-1) ** i)
+
+    def expand_and_backup(self, path, action, child_prior, root_mask, reward, value, latent):
+        """self_play.py:218-230."""
+        new = self.add_node(child_prior, latent)
+        self.child[path[-1]][action] = new
+        self.backup(path + [new], float(reward) + self.discount * float(value))
+        self.depths.append(len(path))
+
+
+def run_mcts_selfplay(obs, initial_fn, recurrent_fn, num_simulations, noise, choice_stream,
+                      c_puct=2.5, discount=0.99, dirichlet_epsilon=0.02, pass_epsilon=0.01):
+    """self_play.py:148-237 with injected randomness and network callbacks (same callbacks as run_mcts)."""
+    latent, _value, soft = initial_fn(obs)
+    A = len(soft)
+    mask = valid_mask_from_obs(obs, pass_epsilon)
+    tree = TreeRefSelfPlay(A, c_puct=c_puct, discount=discount)
+    tree.add_node(root_priors_selfplay(soft, mask, noise, dirichlet_epsilon), latent)
+    calls = [0]
+
+    def choose(seq):
+        k = int(choice_stream[calls[0]]) % len(seq)
+        calls[0] += 1
+        return seq[k]
+
+    for _ in range(num_simulations):
+        path, action = tree.select(choose)
+        if action is None:
+            tree.dropped += 1
+            tree.backup(path, 0)                # :188-195
+            continue
+        nxt, reward, value, soft_c = recurrent_fn(tree.latent[path[-1]], action)
+        tree.expand_and_backup(path, action, child_priors_selfplay(soft_c, mask), mask, reward, value, nxt)
+    return tree, mask
+
+
 def choose_action(visit_counts, root_mask, fallback_u32=0):
     """main.py:670-677 -> (action, policy_target float64[A])."""
     vc = np.asarray(visit_counts)

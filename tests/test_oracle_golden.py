@@ -52,14 +52,14 @@ def run_oracle_on_fixture(g):
 
     c = float(g["c_puct"])
     c_puct = int(c) if bool(g["c_puct_is_int"]) else c
-    tree, mask = mcts_ref.run_mcts(g["obs"], initial, recurrent, int(g["sims"]), g["noise"], g["stream"],
-                                   c_puct=c_puct, discount=float(g["discount"]),
-                                   dirichlet_epsilon=float(g["dirichlet_epsilon"]),
-                                   pass_epsilon=float(g["pass_epsilon"]))
+    run = mcts_ref.run_mcts_selfplay if str(g["variant"]) == "self_play" else mcts_ref.run_mcts
+    tree, mask = run(g["obs"], initial, recurrent, int(g["sims"]), g["noise"], g["stream"],
+                     c_puct=c_puct, discount=float(g["discount"]), dirichlet_epsilon=float(g["dirichlet_epsilon"]),
+                     pass_epsilon=float(g["pass_epsilon"]))
     return tree, mask
 
 
-MAIN_LIKE = sorted(glob.glob(os.path.join(GOLDEN, "mcts_main_*.npz")) + glob.glob(os.path.join(GOLDEN, "mcts_play_*.npz")))
+MAIN_LIKE = sorted(glob.glob(os.path.join(GOLDEN, "mcts_*.npz")))
 
 
 @pytest.mark.parametrize("path", MAIN_LIKE, ids=os.path.basename)
@@ -74,6 +74,7 @@ def test_mcts_oracle_bit_exact_vs_reference(path):
     assert float(tree.value_sum[0]) == float(g["root_value_sum"])
     assert np.array_equal(tree.root_child_value_sums(), g["child_value_sum"])
     assert np.array_equal(np.array(tree.depths), g["sel_depth"][g["sel_action"] >= 0])
+    assert tree.dropped == int((g["sel_action"] < 0).sum())
 
 
 def test_choose_action_matches_main():
