@@ -188,7 +188,8 @@ def run_ours(args, wl):
     free_b, _ = torch.cuda.mem_get_info()
     per_game = (S + 1) * (net.slot_bytes() + A * 18 + 8) + 64 * 1024
     if G * per_game > 0.92 * free_b:
-        G = int(0.92 * free_b / per_game) // 64 * 64
+        # whole rounds of the persistent network kernel: one leaf per SM and round (148 SMs)
+        G = int(0.92 * free_b / per_game) // 148 * 148
     T = 2
     eng = mz.SelfPlayEngine(net, n, G, S, search=mz.SearchConfig(seed=1000 + rank), traj_capacity=T,
                             restart_finished=True)
@@ -269,6 +270,53 @@ def run_ours(args, wl):
     achieved = live * flops_recurrent(n) / (kern_ms * 1e-3) / 1e12
     peak_tf = peaks["bf16_sustained"]
 
+    # ---- tree step (HBM bound): expand + backup + next selection of all G trees, late in a search
+    def bytes_tree(depth_mean):
+        return 20 * A * depth_mean + 8 * A + 24 * (depth_mean + 1)
+
+    tree_reps = min(16, max(1, S // 4))
+    d_part = eng.descriptor()
+    d_part.num_simulations = S - tree_reps - 1
+    p_struct = eng.search.to_struct()
+    eng.tree.reset_roots(eng.search, eng.root_policy, eng.boards, n, noise=None, move_index=0)
+    _lib.check(lib.mzgo_search_run(d_part, None, 0, _lib.stream_ptr()))
+    step_args = (eng.tree.desc, p_struct, _lib.ptr(eng.leaf_policy), _lib.ptr(eng.leaf_reward), _lib.ptr(eng.leaf_value),
+                 None, 0)
+    _lib.check(lib.mzgo_tree_step(*step_args, 0, 1, _lib.stream_ptr()))
+    torch.cuda.synchronize()
+    dsum0, sims0 = int(eng.tree.depth_sum.sum()), int(eng.tree.sims_done.sum())
+    k0.record()
+    for _ in range(tree_reps):
+        _lib.check(lib.mzgo_tree_step(*step_args, 1, 1, _lib.stream_ptr()))
+    k1.record()
+    torch.cuda.synchronize()
+    tree_ms = k0.elapsed_time(k1) / tree_reps
+    tree_sims = int(eng.tree.sims_done.sum()) - sims0
+    tree_depth = (int(eng.tree.depth_sum.sum()) - dsum0) / max(1, tree_sims)
+    tree_bytes = tree_sims / tree_reps * bytes_tree(tree_depth)
+    tree_gbs = tree_bytes / (tree_ms * 1e-3) / 1e9
+
+    # ---- rules step (HBM bound nominally, 324 B per ply at 19x19 / 108 B at 9x9): 2^20 mid-game boards, one
+    # random legal move each per launch (the configs[2] playout kernel with T = 1)
+    NB = 1 << 20
+    rb = mz.GoBoards(NB, n).reset()
+    Rnd = torch.randint(0, 2 ** 31 - 1, (NB, n * n // 2), dtype=torch.int32, device=dev)
+    rb.playout(Rnd, want_actions=False)
+    rules_reps = 6
+    acts = [torch.randint(0, 2 ** 31 - 1, (NB, 1), dtype=torch.int32, device=dev) for _ in range(rules_reps + 2)]
+    for i in range(2):
+        rb.playout(acts[i], want_actions=False)
+    torch.cuda.synchronize()
+    k0.record()
+    for i in range(rules_reps):
+        rb.playout(acts[2 + i], want_actions=False)
+    k1.record()
+    torch.cuda.synchronize()
+    rules_ms = k0.elapsed_time(k1) / rules_reps
+    rules_bytes = NB * (2 * (3 * 4 * ((n * n + 31) // 32) + 16) + 4)
+    rules_gbs = rules_bytes / (rules_ms * 1e-3) / 1e9
+    del rb, Rnd, acts
+
     t = torch.tensor([ms, e2e_s * 1000.0], dtype=torch.float64, device=dev)
     tot = torch.tensor([sims_done, moves_done, e2e_sims, launches, G], dtype=torch.float64, device=dev)
     if world > 1:
@@ -301,6 +349,16 @@ def run_ours(args, wl):
                              "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved / peak_tf,
                              "traffic": None, "peak_source": peaks["source"] + " bf16 sustained",
                              "launch_ms": kern_ms, "leaves_per_launch": live},
+                "roofline_tree": {"bound": "hbm", "kernel": "k_tree_step (expand + backup + select, all trees)",
+                                  "achieved": tree_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                                  "frac": tree_gbs / peaks["hbm_gbs"], "traffic": None, "launch_ms": tree_ms,
+                                  "bytes_per_sim": bytes_tree(tree_depth), "mean_leaf_depth": tree_depth,
+                                  "sims_per_launch": tree_sims / tree_reps,
+                                  "state": f"simulations {S - tree_reps}..{S} of a search"},
+                "roofline_rules": {"bound": "hbm", "kernel": "k_rules_playout, T=1 (one random legal move on each of 2^20 mid-game boards)",
+                                   "achieved": rules_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                                   "frac": rules_gbs / peaks["hbm_gbs"], "traffic": None, "launch_ms": rules_ms,
+                                   "bytes_per_ply": rules_bytes / NB, "plies_per_sec": NB / (rules_ms * 1e-3)},
                 "cpu_baseline": cpu, "clocks": clocks,
                 "weight_broadcast_bytes": bytes_bcast}
         print(json.dumps(line), flush=True)

@@ -123,6 +123,12 @@ typedef struct mzgo_tree {
     uint8_t* active;      /* device [G] 0 = tree idle (game finished) */
 } mzgo_tree_t;
 
+/* Search variants.  MAIN: main.py:247-368 and play.py:104-216.  SELFPLAY: self_play.py:142-343
+ * (root priors re-masked and renormalised after the noise, child priors masked and renormalised,
+ * sqrt(max(1, N_parent)), sign-alternating backup, terminal leaves back 0 up along the path). */
+#define MZGO_VARIANT_MAIN 0
+#define MZGO_VARIANT_SELFPLAY 1
+
 typedef struct mzgo_search_params {
     double c_puct;             /* main.py:248 (2), play.py:116 (10.0), self_play.py:143 (2.5) */
     double discount;           /* main.py:37, used at :311 */
@@ -131,7 +137,7 @@ typedef struct mzgo_search_params {
     float dirichlet_alpha;     /* main.py:45 (device sampler only) */
     int32_t c_puct_is_int;     /* 1: c*P exact in P's dtype (main.py); 0: float c, rounds in float32 below the root */
     uint64_t seed;             /* device RNG key (Philox) when no stream / noise is injected */
-    int32_t variant;           /* 0 = main.py / play.py semantics */
+    int32_t variant;           /* MZGO_VARIANT_* */
     int32_t reserved;
 } mzgo_search_params_t;
 
@@ -156,6 +162,15 @@ int mzgo_tree_select(const mzgo_tree_t* tree, const mzgo_search_params_t* p,
 int mzgo_tree_expand_backup(const mzgo_tree_t* tree, const mzgo_search_params_t* p,
                             const float* soft /*device*/, const float* reward /*device*/,
                             const float* value /*device*/, void* stream);
+
+/* Fused simulation step (what mzgo_search_run launches once per simulation): expansion + backup of the
+ * leaf picked by the previous step (do_backup != 0; arguments as mzgo_tree_expand_backup), then the
+ * selection of the next leaf (do_select != 0; arguments as mzgo_tree_select).  Same arithmetic as the
+ * two separate entry points. */
+int mzgo_tree_step(const mzgo_tree_t* tree, const mzgo_search_params_t* p, const float* soft /*device*/,
+                   const float* reward /*device*/, const float* value /*device*/,
+                   const uint32_t* choice_stream /*device, optional*/, int stride, int do_backup, int do_select,
+                   void* stream);
 
 /* Visit-count extraction, main.py:666-669: out[g][a] = child visit count where root_mask > 0. */
 int mzgo_tree_visit_counts(const mzgo_tree_t* tree, int32_t* out /*device [G][A]*/, void* stream);

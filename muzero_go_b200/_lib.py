@@ -76,6 +76,7 @@ _PROTOS = {
     "mzgo_tree_reset_roots": (i32, [C.POINTER(TreeDesc), C.POINTER(SearchParams), vp, vp, i32, vp, u32, vp]),
     "mzgo_tree_select": (i32, [C.POINTER(TreeDesc), C.POINTER(SearchParams), vp, i32, vp]),
     "mzgo_tree_expand_backup": (i32, [C.POINTER(TreeDesc), C.POINTER(SearchParams), vp, vp, vp, vp]),
+    "mzgo_tree_step": (i32, [C.POINTER(TreeDesc), C.POINTER(SearchParams), vp, vp, vp, vp, i32, i32, i32, vp]),
     "mzgo_tree_visit_counts": (i32, [C.POINTER(TreeDesc), vp, vp]),
     "mzgo_tree_choose_action": (i32, [C.POINTER(TreeDesc), C.POINTER(SearchParams), f32, vp, u32, vp, vp, vp, vp]),
     "mzgo_net_workspace_bytes": (i64, [i32, i32, i32, i32]),

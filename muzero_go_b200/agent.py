@@ -20,7 +20,7 @@ from .tree import SearchConfig
 
 class MuZeroAgent:
     def __init__(self, board_size, latent_dim, env_action_size, num_simulations, max_action_size=None,
-                 precision="fp32", config=None, c_puct=2, device="cuda"):
+                 precision="fp32", config=None, c_puct=None, device="cuda", variant="main"):
         self.board_size = board_size
         self.action_size = env_action_size
         if max_action_size is None:
@@ -28,15 +28,17 @@ class MuZeroAgent:
         self.net = MuZeroNet(latent_dim, max_action_size, board_size=board_size, precision=precision).to(device)
         self.net.eval()
         self.mcts_simulations = num_simulations
-        self.config = config if config is not None else SearchConfig()
+        self.variant = variant
+        self.config = config if config is not None else SearchConfig.for_variant(variant)
         self.c_puct = c_puct
         self._mcts = None
 
     def _search(self, observation):
         if self._mcts is None:
             self._mcts = MCTS(self.net, self.action_size, self.mcts_simulations, c_puct=self.c_puct,
-                              config=self.config)
-        root = self._mcts.run(observation)
+                              config=self.config, variant=self.variant)
+        out = self._mcts.run(observation)
+        root = out[0] if isinstance(out, tuple) else out
         valid_mask = valid_mask_from_observation(observation, self.config.pass_epsilon)
         visit_counts = np.array([child["node"].visit_count if (child["node"] is not None and valid_mask[a] > 0) else 0
                                  for a, child in root.children.items()])

@@ -42,7 +42,3 @@ int mzgo_tc_recurrent(const mzgo_net_t* net, void* arena, const int32_t* in_slot
                       const int32_t* out_slot, float* reward, float* value, float* policy, int want_softmax, int B,
                       cudaStream_t st);
 
-// fused tree step of the engine path (tree.cu)
-int mzgo_tree_step(const mzgo_tree_t* tree, const mzgo_search_params_t* p, const float* soft, const float* reward,
-                   const float* value, const uint32_t* choice_stream, int stride, int do_backup, int do_select,
-                   cudaStream_t st);

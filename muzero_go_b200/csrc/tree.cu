@@ -25,30 +25,34 @@ __device__ __forceinline__ double warp_max_d(double v) {
 
 // numpy's float32 pairwise summation (np.add.reduce on a contiguous array, numpy 2.x):
 // blocks of <= 128 use 8 strided accumulators, longer inputs split in halves (multiple of 8).
-__device__ float np_pairwise_sum_f32(const float* a, int n) {
+__device__ __forceinline__ float add_rn(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ double add_rn(double a, double b) { return __dadd_rn(a, b); }
+
+template <typename T>
+__device__ T np_pairwise_sum(const T* a, int n) {
     if (n < 8) {
-        float r = 0.f;
-        for (int i = 0; i < n; i++) r = __fadd_rn(r, a[i]);
+        T r = (T)0;
+        for (int i = 0; i < n; i++) r = add_rn(r, a[i]);
         return r;
     }
     if (n <= 128) {
-        float r[8];
+        T r[8];
 #pragma unroll
         for (int k = 0; k < 8; k++) r[k] = a[k];
         int i = 8;
         for (; i < n - (n % 8); i += 8) {
 #pragma unroll
-            for (int k = 0; k < 8; k++) r[k] = __fadd_rn(r[k], a[i + k]);
+            for (int k = 0; k < 8; k++) r[k] = add_rn(r[k], a[i + k]);
         }
-        float res = __fadd_rn(__fadd_rn(__fadd_rn(r[0], r[1]), __fadd_rn(r[2], r[3])),
-                              __fadd_rn(__fadd_rn(r[4], r[5]), __fadd_rn(r[6], r[7])));
-        for (; i < n; i++) res = __fadd_rn(res, a[i]);
+        T res = add_rn(add_rn(add_rn(r[0], r[1]), add_rn(r[2], r[3])), add_rn(add_rn(r[4], r[5]), add_rn(r[6], r[7])));
+        for (; i < n; i++) res = add_rn(res, a[i]);
         return res;
     }
     int n2 = n / 2;
     n2 -= n2 % 8;
-    return __fadd_rn(np_pairwise_sum_f32(a, n2), np_pairwise_sum_f32(a + n2, n - n2));
+    return add_rn(np_pairwise_sum(a, n2), np_pairwise_sum(a + n2, n - n2));
 }
+__device__ float np_pairwise_sum_f32(const float* a, int n) { return np_pairwise_sum<float>(a, n); }
 
 // ---- device Dirichlet sampler (production path; distribution parity only) ----
 __device__ __forceinline__ float u01(uint32_t x) { return ((float)(x >> 8) + 0.5f) * (1.0f / 16777216.0f); }
@@ -72,6 +76,24 @@ __device__ float sample_gamma(float alpha, uint64_t seed, uint32_t game, uint32_
     uint32_t r[4] = {ctr, stream, game, 0x626f6f73u};
     philox4x32_10(r, (uint32_t)seed, (uint32_t)(seed >> 32));
     return out * __powf(u01(r[0]), 1.0f / alpha);
+}
+
+// self_play.py:210: policy_child *= valid_mask -- float32 * float64 in float64, rounded back to float32.
+// The float64 mask is 0 / 1 on the board and pass_epsilon (or 1.0 when no board move is legal) for the pass.
+__device__ __forceinline__ float masked_child_prior(float soft, float mask_f32, bool is_pass, double pass_epsilon) {
+    const double m = is_pass ? (mask_f32 == 1.0f ? 1.0 : pass_epsilon) : (double)mask_f32;
+    return (float)__dmul_rn((double)soft, m);
+}
+// self_play.py:211-222.  tot > 0: float32 divide.  tot == 0 (every legal move underflowed): the reference
+// switches to a float64 uniform distribution over the mask; it is stored rounded to float32 here (the only
+// place this variant departs from the reference's dtypes; unreachable with finite logits).
+__device__ __forceinline__ float renorm_child_prior(float pr, float tot, float mask_f32, bool is_pass, double pass_epsilon,
+                                                    const float* mask, int A) {
+    if (tot > 0.f) return __fdiv_rn(pr, tot);
+    double ms = 0.0;
+    for (int a = 0; a < A; a++) ms += a == A - 1 ? (mask[a] == 1.0f ? 1.0 : pass_epsilon) : (double)mask[a];
+    const double m = is_pass ? (mask_f32 == 1.0f ? 1.0 : pass_epsilon) : (double)mask_f32;
+    return (float)(m / ms);
 }
 
 // ------------------------------------------------------------------------------------------ root prep
@@ -131,16 +153,49 @@ k_tree_reset_roots(mzgo_tree_t t, mzgo_search_params_t p, const float* __restric
         gsum = warp_sum_f(gsum);
     }
     double* rp = t.root_prior + (size_t)g * A;
+    // self_play.py:163: a masked policy that sums to zero becomes uniform over the mask, in float64
+    double msum = 0.0;
+    if (p.variant == MZGO_VARIANT_SELFPLAY) {
+        // sum of the float64 mask, numpy pairwise order (edge_vsum row 0 is free until the root is cleared below)
+        double* dscr = t.edge_vsum + (size_t)g * t.M * A;
+        for (int a = lane; a < A; a += 32) dscr[a] = a < np ? (double)mask[a] : pass_prior;
+        __syncwarp();
+        if (lane == 0) msum = np_pairwise_sum<double>(dscr, A);
+        msum = __shfl_sync(FULL_MASK, msum, 0);
+        __syncwarp();
+    }
 #pragma unroll
     for (int j = 0; j < MAX_EPL; j++) {
         int a = j * 32 + lane;
         if (a >= A) continue;
         float pol = scratch[a];
-        if (total > 0.f) pol = __fdiv_rn(pol, total);                      // main.py:272-273
+        const double m = a < np ? (double)mask[a] : pass_prior;
         double nz = noise ? noise[(size_t)g * A + a] : (double)(gam[j] / gsum);
-        // (1 - eps) * policy stays float32; + eps * dirichlet promotes to float64 (main.py:63-64)
-        double mixed = __dadd_rn((double)__fmul_rn(one_minus_eps, pol), __dmul_rn(p.dirichlet_epsilon, nz));
+        double scaled;
+        if (total > 0.f) {
+            pol = __fdiv_rn(pol, total);                                   // main.py:272-273
+            // (1 - eps) * policy stays float32; + eps * dirichlet promotes to float64 (main.py:63-64)
+            scaled = (double)__fmul_rn(one_minus_eps, pol);
+        } else if (p.variant == MZGO_VARIANT_SELFPLAY) {
+            scaled = __dmul_rn(1.0 - p.dirichlet_epsilon, __ddiv_rn(m, msum));   // float64 uniform over the mask
+        } else {
+            scaled = (double)__fmul_rn(one_minus_eps, pol);
+        }
+        double mixed = __dadd_rn(scaled, __dmul_rn(p.dirichlet_epsilon, nz));
+        if (p.variant == MZGO_VARIANT_SELFPLAY) mixed = __dmul_rn(mixed, m);   // policy *= valid_mask, self_play.py:172
         rp[a] = mask[a] > 0.f ? mixed : 0.0;                               // main.py:281
+    }
+    if (p.variant == MZGO_VARIANT_SELFPLAY) {
+        // renormalise after the noise, float64 pairwise sum (self_play.py:173-178)
+        __syncwarp();
+        double tot2 = 0.0;
+        if (lane == 0) tot2 = np_pairwise_sum<double>(rp, A);
+        tot2 = __shfl_sync(FULL_MASK, tot2, 0);
+        for (int a = lane; a < A; a += 32) {
+            const double m = a < np ? (double)mask[a] : pass_prior;
+            rp[a] = tot2 > 0.0 ? __ddiv_rn(rp[a], tot2) : __ddiv_rn(m, msum);
+        }
+        __syncwarp();
     }
     // fresh root: no children, no visits
     size_t base = (size_t)g * t.M * A;
@@ -241,7 +296,8 @@ k_tree_select(mzgo_tree_t t, mzgo_search_params_t p, const uint32_t* __restrict_
         }
         qmin = warp_min_d(qmin);
         qmax = warp_max_d(qmax);
-        const double sq = __dsqrt_rn((double)(npar + 1));
+        // main.py:354 sqrt(N+1); self_play.py:297-300 sqrt(max(1, N))
+        const double sq = __dsqrt_rn((double)(p.variant == MZGO_VARIANT_SELFPLAY ? max(1, npar) : npar + 1));
         const bool norm = qmax > qmin;
         const double range = __dsub_rn(qmax, qmin);
         double best = -INFINITY;
@@ -270,6 +326,16 @@ k_tree_select(mzgo_tree_t t, mzgo_search_params_t p, const uint32_t* __restrict_
     }
     if (lane == 0) {
         int nn = t.n_nodes[g];
+        if (sel_action < 0 && p.variant == MZGO_VARIANT_SELFPLAY) {
+            // terminal leaf: backpropagate(path, 0) -- a visit for every node on the path (self_play.py:188-190)
+            int nd = node;
+            while (nd != 0) {
+                const int pk = t.parent[(size_t)g * M + nd];
+                t.edge_visit[((size_t)g * M + (pk >> 9)) * A + (pk & 511)] += 1;
+                nd = pk >> 9;
+            }
+            t.root_visit[g] += 1;
+        }
         if (sel_action >= 0 && nn >= M) sel_action = -1;   // arena full: drop (cannot happen when M > simulations)
         t.leaf_parent[g] = sel_action >= 0 ? sel_parent : -1;
         t.leaf_action[g] = sel_action;
@@ -296,12 +362,25 @@ k_tree_expand_backup(mzgo_tree_t t, mzgo_search_params_t p, const float* __restr
     const int nw = t.leaf_node[g];
     const size_t nbase = ((size_t)g * M + nw) * A;
     const float* mask = t.root_mask + (size_t)g * A;
+    const bool v1 = p.variant == MZGO_VARIANT_SELFPLAY;
     for (int a = lane; a < A; a += 32) {
         // prior_child = policy_child[a] if valid_mask[a] > 0 else 0   (the ROOT's mask, main.py:303)
-        t.prior[nbase + a] = mask[a] > 0.f ? soft[(size_t)g * A + a] : 0.f;
+        float pr = mask[a] > 0.f ? soft[(size_t)g * A + a] : 0.f;
+        if (v1) pr = masked_child_prior(soft[(size_t)g * A + a], mask[a], a == A - 1, p.pass_epsilon);
+        t.prior[nbase + a] = pr;
         t.edge_visit[nbase + a] = 0;
         t.edge_vsum[nbase + a] = 0.0;
         t.child[nbase + a] = (int16_t)-1;
+    }
+    if (v1) {
+        // policy_child /= policy_child.sum(): float32 pairwise sum, float32 divide (self_play.py:211-214)
+        __syncwarp();
+        float tot = 0.f;
+        if (lane == 0) tot = np_pairwise_sum<float>(t.prior + nbase, A);
+        tot = __shfl_sync(FULL_MASK, tot, 0);
+        __syncwarp();
+        for (int a = lane; a < A; a += 32)
+            t.prior[nbase + a] = renorm_child_prior(t.prior[nbase + a], tot, mask[a], a == A - 1, p.pass_epsilon, mask, A);
     }
     if (lane == 0) {
         t.child[((size_t)g * M + par) * A + act] = (int16_t)nw;
@@ -309,17 +388,19 @@ k_tree_expand_backup(mzgo_tree_t t, mzgo_search_params_t p, const float* __restr
         t.n_nodes[g] = nw + 1;
         // backup_value = reward.item() + discount * value.item()   (main.py:311), float64
         const double bv = __dadd_rn((double)reward[g], __dmul_rn(p.discount, (double)value[g]));
+        double sv = bv;                                      // self_play.py:340-343: +value at the new leaf, then alternating
         int node = nw;
         while (node != 0) {
             int pk = t.parent[(size_t)g * M + node];
             int pn = pk >> 9, pa = pk & 511;
             size_t e = ((size_t)g * M + pn) * A + pa;
             t.edge_visit[e] += 1;
-            t.edge_vsum[e] = __dadd_rn(t.edge_vsum[e], bv);
+            t.edge_vsum[e] = __dadd_rn(t.edge_vsum[e], sv);
+            if (v1) sv = -sv;
             node = pn;
         }
         t.root_visit[g] += 1;
-        t.root_vsum[g] = __dadd_rn(t.root_vsum[g], bv);
+        t.root_vsum[g] = __dadd_rn(t.root_vsum[g], sv);
         t.sims_done[g] += 1;
         t.depth_sum[g] += t.leaf_depth[g];
     }
@@ -352,6 +433,9 @@ k_tree_step(mzgo_tree_t t, mzgo_search_params_t p, const float* __restrict__ sof
     __shared__ uint32_t s_live[GPB][WPG];
     __shared__ double s_min[GPB][WPG], s_max[GPB][WPG], s_best[GPB][WPG];
     __shared__ int s_besta[GPB][WPG], s_bestn[GPB][WPG];
+    __shared__ float s_pri[GPB][STEP_EPT * TPG];  // self_play.py variant: masked child priors before the renormalisation
+    __shared__ float s_tot[GPB];
+    const bool v1 = p.variant == MZGO_VARIANT_SELFPLAY;
     const int sub = threadIdx.x / TPG, tid = threadIdx.x % TPG;
     const int wig = tid >> 5, lane = tid & 31;
     const int g = blockIdx.x * GPB + sub;
@@ -367,12 +451,11 @@ k_tree_step(mzgo_tree_t t, mzgo_search_params_t p, const float* __restrict__ sof
     const int depth_b = t.leaf_depth[g];
     const float rew_g = do_backup ? reward[g] : 0.f, val_g = do_backup ? value[g] : 0.f;
     const int is_active = t.active[g];
+    float mk[STEP_EPT], sf[STEP_EPT];
+    int pk_mine = -1;
     if (act >= 0) {
         const int depth = depth_b;
-        const size_t nbase = ((size_t)g * M + nw) * A;
         const float* mask = t.root_mask + (size_t)g * A;
-        float mk[STEP_EPT], sf[STEP_EPT];
-        int pk_mine = -1;
         if (depth <= A && tid < depth) pk_mine = path[tid];
 #pragma unroll
         for (int e = 0; e < STEP_EPT; e++) {
@@ -380,12 +463,32 @@ k_tree_step(mzgo_tree_t t, mzgo_search_params_t p, const float* __restrict__ sof
             mk[e] = 0.f; sf[e] = 0.f;
             if (a < A) { mk[e] = mask[a]; sf[e] = soft[(size_t)g * A + a]; }
         }
+        if (v1) {
+            // policy_child *= valid_mask; /= sum (float32 pairwise)   self_play.py:210-214
+#pragma unroll
+            for (int e = 0; e < STEP_EPT; e++) {
+                const int a = e * TPG + tid;
+                if (a < A) s_pri[sub][a] = masked_child_prior(sf[e], mk[e], a == A - 1, p.pass_epsilon);
+            }
+        }
+    }
+    if (v1) {                                    // uniform for the block: p is a kernel parameter
+        step_sync<TPG>();
+        if (tid == 0 && act >= 0) s_tot[sub] = np_pairwise_sum<float>(s_pri[sub], A);
+        step_sync<TPG>();
+    }
+    if (act >= 0) {
+        const int depth = depth_b;
+        const size_t nbase = ((size_t)g * M + nw) * A;
+        const float* mask = t.root_mask + (size_t)g * A;
 #pragma unroll
         for (int e = 0; e < STEP_EPT; e++) {
             const int a = e * TPG + tid;
             if (a < A) {
                 // prior_child = policy_child[a] if valid_mask[a] > 0 else 0   (the ROOT's mask, main.py:303)
-                t.prior[nbase + a] = mk[e] > 0.f ? sf[e] : 0.f;
+                float pr = mk[e] > 0.f ? sf[e] : 0.f;
+                if (v1) pr = renorm_child_prior(s_pri[sub][a], s_tot[sub], mk[e], a == A - 1, p.pass_epsilon, mask, A);
+                t.prior[nbase + a] = pr;
                 t.edge_visit[nbase + a] = 0;
                 t.edge_vsum[nbase + a] = 0.0;
                 t.child[nbase + a] = (int16_t)-1;
@@ -393,19 +496,21 @@ k_tree_step(mzgo_tree_t t, mzgo_search_params_t p, const float* __restrict__ sof
         }
         // backup_value = reward.item() + discount * value.item()   (main.py:311), float64
         const double bv = __dadd_rn((double)rew_g, __dmul_rn(p.discount, (double)val_g));
+        // self_play.py:340-343: node i levels above the new leaf gets value * (-1)^i; edge d of the path holds the
+        // statistics of the node at depth d + 1, i.e. i = depth - 1 - d, and the root has i = depth
         if (depth <= A) {
             if (pk_mine >= 0) {
                 const size_t e = ((size_t)g * M + (pk_mine >> 9)) * A + (pk_mine & 511);
                 const int ev = t.edge_visit[e];
                 const double es = t.edge_vsum[e];
                 t.edge_visit[e] = ev + 1;
-                t.edge_vsum[e] = __dadd_rn(es, bv);
+                t.edge_vsum[e] = __dadd_rn(es, (v1 && ((depth - 1 - tid) & 1)) ? -bv : bv);
             }
             for (int d = tid + TPG; d < depth; d += TPG) {
                 const int pk = path[d];
                 const size_t e = ((size_t)g * M + (pk >> 9)) * A + (pk & 511);
                 t.edge_visit[e] += 1;
-                t.edge_vsum[e] = __dadd_rn(t.edge_vsum[e], bv);
+                t.edge_vsum[e] = __dadd_rn(t.edge_vsum[e], (v1 && ((depth - 1 - d) & 1)) ? -bv : bv);
             }
         }
         if (tid == 0) {
@@ -414,17 +519,19 @@ k_tree_step(mzgo_tree_t t, mzgo_search_params_t p, const float* __restrict__ sof
             t.n_nodes[g] = nw + 1;
             if (depth > A) {                     // path longer than the scratch row: walk the parent links
                 int node = nw;
+                double sv = bv;
                 while (node != 0) {
                     const int pk = t.parent[(size_t)g * M + node];
                     const int pn = pk >> 9, pa = pk & 511;
                     const size_t e = ((size_t)g * M + pn) * A + pa;
                     t.edge_visit[e] += 1;
-                    t.edge_vsum[e] = __dadd_rn(t.edge_vsum[e], bv);
+                    t.edge_vsum[e] = __dadd_rn(t.edge_vsum[e], sv);
+                    if (v1) sv = -sv;
                     node = pn;
                 }
             }
             t.root_visit[g] += 1;
-            t.root_vsum[g] = __dadd_rn(t.root_vsum[g], bv);
+            t.root_vsum[g] = __dadd_rn(t.root_vsum[g], (v1 && (depth & 1)) ? -bv : bv);
             t.sims_done[g] += 1;
             t.depth_sum[g] += depth;
         }
@@ -534,7 +641,7 @@ k_tree_step(mzgo_tree_t t, mzgo_search_params_t p, const float* __restrict__ sof
 #pragma unroll
             for (int w = 0; w < WPG; w++) { qmin = fmin(qmin, s_min[sub][w]); qmax = fmax(qmax, s_max[sub][w]); }
         }
-        const double sq = __dsqrt_rn((double)(npar + 1));
+        const double sq = __dsqrt_rn((double)(v1 ? max(1, npar) : npar + 1));   // main.py:354 / self_play.py:297-300
         const bool norm = qmax > qmin;
         const double range = __dsub_rn(qmax, qmin);
         double best = -INFINITY;
@@ -577,6 +684,16 @@ k_tree_step(mzgo_tree_t t, mzgo_search_params_t p, const float* __restrict__ sof
     }
     if (tid == 0) {
         const int nn = act >= 0 ? nw + 1 : nn0;
+        if (sel_action < 0 && v1) {
+            // terminal leaf: backpropagate(path, 0) -- a visit for every node on the path (self_play.py:188-190)
+            int nd = node;
+            while (nd != 0) {
+                const int pk = t.parent[(size_t)g * M + nd];
+                t.edge_visit[((size_t)g * M + (pk >> 9)) * A + (pk & 511)] += 1;
+                nd = pk >> 9;
+            }
+            t.root_visit[g] += 1;
+        }
         if (sel_action >= 0 && nn >= M) sel_action = -1;   // arena full: drop (cannot happen when M > simulations)
         if (sel_action >= 0 && depth <= A) path[depth - 1] = sel_parent * 512 + sel_action;
         t.leaf_parent[g] = sel_action >= 0 ? sel_parent : -1;
@@ -764,9 +881,10 @@ extern "C" int mzgo_tree_expand_backup(const mzgo_tree_t* tree, const mzgo_searc
 }
 
 // Fused simulation step (engine path): expand + backup of the previous leaf, then the next selection.
-int mzgo_tree_step(const mzgo_tree_t* tree, const mzgo_search_params_t* p, const float* soft, const float* reward,
-                   const float* value, const uint32_t* choice_stream, int stride, int do_backup, int do_select,
-                   cudaStream_t st) {
+extern "C" int mzgo_tree_step(const mzgo_tree_t* tree, const mzgo_search_params_t* p, const float* soft,
+                              const float* reward, const float* value, const uint32_t* choice_stream, int stride,
+                              int do_backup, int do_select, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
     if (int e = check_tree(tree)) return e;
     MZGO_CHECK_ARG(p && (!do_backup || (soft && reward && value)), "NULL argument");
     if (tree->G == 0) return MZGO_OK;

@@ -1,5 +1,5 @@
 """Drop-in for the reference's per-move search: MCTS(net, action_size, num_simulations, c_puct).run(obs)
-(/root/reference/main.py:247-368, play.py:104-216).  The tree lives on the GPU (csrc/tree.cu); run()
+(/root/reference/main.py:247-368, play.py:104-216; variant="self_play": self_play.py:142-343).  The tree lives on the GPU (csrc/tree.cu); run()
 returns a read-only MCTSNode view exposing what the callers walk (main.py:666-669, play.py:234-239):
 root.visit_count, root.value(), root.children[a]['node'].visit_count, root.children[a]['prior'].
 """
@@ -62,13 +62,16 @@ class MCTS:
     """main.py:247-316.  `config` supplies discount / dirichlet_epsilon / dirichlet_alpha / pass_epsilon
     (the reference reads them from its module-global config, main.py:264,276,311)."""
 
-    def __init__(self, muzero_net, action_size, num_simulations, c_puct=2, config=None, seed=0):
+    def __init__(self, muzero_net, action_size, num_simulations, c_puct=None, config=None, seed=0, variant="main"):
         self.net = muzero_net
         self.net.eval()
         self.action_size = int(action_size)
         self.num_simulations = int(num_simulations)
+        self.variant = variant
+        if c_puct is None:                  # main.py:248 (2), play.py:116 (10.0), self_play.py:143 (2.5)
+            c_puct = SearchConfig.for_variant(variant).c_puct
         self.c_puct = c_puct
-        cfg = SearchConfig(c_puct=c_puct, seed=seed)
+        cfg = SearchConfig.for_variant(variant, c_puct=c_puct, seed=seed)
         for k in ("discount", "dirichlet_epsilon", "dirichlet_alpha", "pass_epsilon"):
             if config is not None and hasattr(config, k):
                 setattr(cfg, k, getattr(config, k))
@@ -110,7 +113,15 @@ class MCTS:
             stride = stream_t.shape[1]
         _lib.check(L.mzgo_search_run(d, _lib.ptr(stream_t), stride, s))
         self._calls += 1
-        return MCTSNode(self._snapshot(eng), 0)
+        root = MCTSNode(self._snapshot(eng), 0)
+        if self.variant == "self_play":
+            # self_play.py:233-237 returns (root, visit_counts, root_value).  The reference's vector reads the
+            # edge dicts' dead 'visit_count' field and is always zero (defect 1); the counts
+            # returned here are the children's, i.e. what the agent was meant to receive.
+            visit_counts = np.array([c["node"].visit_count if c["node"] is not None else 0
+                                     for c in root.children.values()])
+            return root, visit_counts, root.value()
+        return root
 
     def _snapshot(self, eng):
         t = eng.tree

@@ -21,6 +21,18 @@ class SearchConfig:
     dirichlet_alpha: float = 0.03
     pass_epsilon: float = 0.05
     seed: int = 0
+    variant: str = "main"     # "main" (main.py / play.py) or "self_play" (self_play.py:142-343), SURVEY 2.2
+
+    VARIANTS = {"main": 0, "play": 0, "self_play": 1}
+
+    @classmethod
+    def for_variant(cls, variant, **kw):
+        """The reference's per-file defaults."""
+        defaults = {"main": dict(c_puct=2, dirichlet_alpha=0.03, dirichlet_epsilon=0.25, pass_epsilon=0.05),
+                    "play": dict(c_puct=10.0, dirichlet_alpha=0.01, dirichlet_epsilon=0.02, pass_epsilon=0.01),
+                    "self_play": dict(c_puct=2.5, dirichlet_alpha=0.15, dirichlet_epsilon=0.02, pass_epsilon=0.01)}[variant]
+        defaults.update(kw)
+        return cls(variant=variant, **defaults)
 
     def to_struct(self):
         p = _lib.SearchParams()
@@ -31,7 +43,9 @@ class SearchConfig:
         p.dirichlet_alpha = float(self.dirichlet_alpha)
         p.c_puct_is_int = int(isinstance(self.c_puct, int))
         p.seed = int(self.seed) & (2 ** 64 - 1)
-        p.variant = 0
+        if self.variant not in self.VARIANTS:
+            raise ValueError(f"unknown search variant {self.variant!r}")
+        p.variant = self.VARIANTS[self.variant]
         return p
 
 

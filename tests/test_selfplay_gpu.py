@@ -21,10 +21,12 @@ def make_net(n, c, seed, precision="fp32"):
     return ref, net.cuda().eval()
 
 
-def test_mcts_run_drop_in_matches_oracle_search_with_same_network_outputs():
+@pytest.mark.parametrize("variant", ["main", "self_play"])
+def test_mcts_run_drop_in_matches_oracle_search_with_same_network_outputs(variant):
     """MCTS(net, A, sims).run(obs) on the GPU vs the oracle search driven by the SAME float32 network
     outputs: the oracle's callbacks evaluate our CUDA fp32 network (so both sides consume identical
-    numbers, as north_star specifies) and apply the same softmax kernel."""
+    numbers, as north_star specifies) and apply the same softmax kernel.  This path runs the fused
+    tree-step kernel (mzgo_search_run)."""
     import muzero_go_b200 as mz
     from oracle.make_golden import midgame_obs
     n, c, sims = 6, 32, 150
@@ -34,8 +36,10 @@ def test_mcts_run_drop_in_matches_oracle_search_with_same_network_outputs():
     rng = np.random.default_rng(0)
     noise = rng.dirichlet([0.3] * A)
     stream = rng.integers(0, 2 ** 32, size=sims + 8, dtype=np.uint64).astype(np.uint32)
-    mcts = mz.MCTS(net, A, sims)
+    mcts = mz.MCTS(net, A, sims, variant=variant)
     root = mcts.run(obs, noise=noise, choice_stream=stream)
+    if variant == "self_play":                      # self_play.py:233-237 returns a triple
+        root, vc_ret, rv_ret = root
 
     def initial(o):
         lat, v, p = net._run_initial(torch.from_numpy(np.asarray(o, dtype=np.float32))[None].cuda(), want_softmax=True)
@@ -45,7 +49,14 @@ def test_mcts_run_drop_in_matches_oracle_search_with_same_network_outputs():
         nxt, r, v, p = net._run_recurrent(lat, torch.tensor([a]).cuda(), want_softmax=True)
         return nxt, r.cpu().numpy().reshape(-1)[0], v.cpu().numpy().reshape(-1)[0], p.cpu().numpy()[0]
 
-    tree, mask = mcts_ref.run_mcts(obs, initial, recurrent, sims, noise, stream)
+    if variant == "self_play":
+        sc = mz.SearchConfig.for_variant("self_play")
+        tree, mask = mcts_ref.run_mcts_selfplay(obs, initial, recurrent, sims, noise, stream, c_puct=sc.c_puct,
+                                                dirichlet_epsilon=sc.dirichlet_epsilon, pass_epsilon=sc.pass_epsilon)
+        assert np.array_equal(vc_ret, [tree.visit[int(c_)] if c_ >= 0 else 0 for c_ in tree.child[0]])
+        assert rv_ret == pytest.approx(tree.q(0), rel=1e-12)
+    else:
+        tree, mask = mcts_ref.run_mcts(obs, initial, recurrent, sims, noise, stream)
     got = np.array([ch["node"].visit_count if ch["node"] is not None else 0 for ch in root.children.values()])
     assert np.array_equal(got, tree.root_visit_counts(mask))
     assert root.visit_count == tree.visit[0] == sims

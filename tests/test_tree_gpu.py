@@ -12,7 +12,7 @@ from oracle import mcts_ref
 
 pytestmark = pytest.mark.gpu
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
-MAIN_LIKE = sorted(glob.glob(os.path.join(GOLDEN, "mcts_main_*.npz")) + glob.glob(os.path.join(GOLDEN, "mcts_play_*.npz")))
+MAIN_LIKE = sorted(glob.glob(os.path.join(GOLDEN, "mcts_*.npz")))   # main.py, play.py and self_play.py fixtures
 
 
 def run_gpu_search(n, obs_list, init_soft, soft, rewards, values, noise, streams, sims, cfg):
@@ -47,7 +47,8 @@ def cfg_from_fixture(g):
     import muzero_go_b200 as mz
     c = float(g["c_puct"])
     return mz.SearchConfig(c_puct=int(c) if bool(g["c_puct_is_int"]) else c, discount=float(g["discount"]),
-                           dirichlet_epsilon=float(g["dirichlet_epsilon"]), pass_epsilon=float(g["pass_epsilon"]))
+                           dirichlet_epsilon=float(g["dirichlet_epsilon"]), pass_epsilon=float(g["pass_epsilon"]),
+                           variant="self_play" if str(g["variant"]) == "self_play" else "main")
 
 
 @pytest.mark.parametrize("path", MAIN_LIKE, ids=os.path.basename)
@@ -69,14 +70,18 @@ def test_visit_counts_bit_exact_vs_reference_fixture(path):
         assert int(tree.dropped[k]) == int((g["sel_action"] < 0).sum())
 
 
-@pytest.mark.parametrize("n,sims,G,c_puct", [(5, 120, 6, 2), (9, 260, 4, 2), (9, 150, 3, 10.0), (19, 500, 2, 2)])
-def test_batched_search_matches_oracle_on_random_tables(n, sims, G, c_puct):
-    """Different positions / tables per game; also exercises games whose simulations get dropped."""
+@pytest.mark.parametrize("n,sims,G,c_puct,variant", [(5, 120, 6, 2, "main"), (9, 260, 4, 2, "main"), (9, 150, 3, 10.0, "main"),
+                                                     (19, 500, 2, 2, "main"), (5, 150, 6, 2.5, "self_play"),
+                                                     (9, 260, 4, 2.5, "self_play"), (19, 450, 2, 2.5, "self_play")])
+def test_batched_search_matches_oracle_on_random_tables(n, sims, G, c_puct, variant):
+    """Different positions / tables per game; also exercises games whose simulations get dropped
+    (main.py) or end in a terminal leaf (self_play.py)."""
     import muzero_go_b200 as mz
     from oracle.make_golden import midgame_obs
     A = n * n + 1
     rng = np.random.default_rng(1000 + n + sims)
-    cfg = mz.SearchConfig(c_puct=c_puct, discount=0.99, dirichlet_epsilon=0.25, pass_epsilon=0.05)
+    cfg = mz.SearchConfig(c_puct=c_puct, discount=0.99, dirichlet_epsilon=0.25, pass_epsilon=0.05, variant=variant)
+    run_ref = mcts_ref.run_mcts_selfplay if variant == "self_play" else mcts_ref.run_mcts
     obs, init_soft, soft, rew, val, noise, streams, trees = [], [], [], [], [], [], [], []
     for k in range(G):
         o = midgame_obs(n, plies=int(rng.integers(0, n * n)), seed=int(rng.integers(1 << 30)))
@@ -99,8 +104,8 @@ def test_batched_search_matches_oracle_on_random_tables(n, sims, G, c_puct):
             i = calls[0]
             calls[0] += 1
             return None, rew[k][i], val[k][i], soft[k][i]
-        t, mask = mcts_ref.run_mcts(o, lambda ob, k=k: (None, np.float32(0), init_soft[k]), recurrent, sims, noise[k],
-                                    streams[k], c_puct=c_puct, discount=0.99, dirichlet_epsilon=0.25, pass_epsilon=0.05)
+        t, mask = run_ref(o, lambda ob, k=k: (None, np.float32(0), init_soft[k]), recurrent, sims, noise[k],
+                          streams[k], c_puct=c_puct, discount=0.99, dirichlet_epsilon=0.25, pass_epsilon=0.05)
         trees.append((t, mask))
     tree, depths = run_gpu_search(n, obs, init_soft, soft, rew, val, noise, streams, sims, cfg)
     vc = tree.visit_counts().cpu().numpy()
