@@ -38,9 +38,18 @@ constexpr int TC_SLOTS = 4;             // 4 x 128 TMEM columns
 constexpr int TC_SMEM_LIMIT = 232448;   // 227 KB
 
 enum { MODE_PLAIN = 0, MODE_HEADS = 1, MODE_DYN = 2 };
+unsigned long long* g_tc_trace = nullptr;
 
 __host__ __device__ inline int tc_ps(int n) { return (n + 2) * (n + 1) + 2; }
 __host__ __device__ inline int tc_tiles_per_image(int n) { return (n * (n + 1) + 127) / 128; }
+// A group (the images that share one pass over the weights) fills at most three of the four TMEM
+// accumulator slots: with a spare slot the MMAs of the next group start while the epilogue still holds
+// the last tiles of the previous one (a full ring stalled the tensor pipe for 3.3 us per group at 9x9).
+constexpr int TC_GROUP_TILES = 3;
+__host__ __device__ inline int tc_images_per_group(int n) {
+    const int k = TC_GROUP_TILES / tc_tiles_per_image(n);
+    return k < 1 ? 1 : k;
+}
 
 // ---------------------------------------------------------------------------------------- PTX helpers
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -137,7 +146,8 @@ struct TcArgs {
     float* policy;
     int want_softmax;
     int B;                       // items
-    int n, ps, tiles_per_image, images_per_group, num_groups, stages;
+    int n, ps, tiles_per_image, images_per_group, stages;
+    unsigned long long* trace;   // optional (tools/tc_trace.py): [grid][32] globaltimer stamps of the roles
     TcScalars sc;
     float hw[3 * TC_C];          // policy / value / reward 1x1 conv weights: read as constant-bank operands
 };
@@ -149,7 +159,7 @@ struct TcSmemLayout {
 // mode_dyn: per-action bias tables (double buffered, loaded by TMA per group); otherwise one [cout] bias vector
 __host__ __device__ inline TcSmemLayout tc_smem_layout(int n, int cin, int cout, int stages, bool mode_dyn) {
     TcSmemLayout L;
-    const int tiles = tc_tiles_per_image(n), images = TC_SLOTS / tiles;
+    const int images = tc_images_per_group(n);
     L.a_bytes = (uint32_t)images * (cin / 8) * tc_ps(n) * 16;
     L.b_off = (L.a_bytes + 127) / 128 * 128;
     L.tbl_off = L.b_off + (uint32_t)stages * cout * 128;
@@ -163,6 +173,14 @@ __host__ __device__ inline TcSmemLayout tc_smem_layout(int n, int cin, int cout,
 }
 
 __device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+
+__device__ __forceinline__ void tc_stamp(const TcArgs& a, int slot) {
+    if (a.trace) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+        a.trace[(size_t)blockIdx.x * 32 + slot] = t;
+    }
+}
 
 __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
     __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
@@ -182,11 +200,16 @@ __device__ __forceinline__ bool elect_one() {
     return pred != 0;
 }
 
+// CTA b owns the contiguous items [b*B/grid, (b+1)*B/grid) (balanced to within one item) and walks them in
+// groups of up to images_per_group: the group at `base` holds cnt = min(images_per_group, hi - base) items.
+__device__ __forceinline__ int tc_items_lo(const TcArgs& a) { return (int)((long long)blockIdx.x * a.B / gridDim.x); }
+__device__ __forceinline__ int tc_items_hi(const TcArgs& a) { return (int)((long long)(blockIdx.x + 1) * a.B / gridDim.x); }
+
 // Which images of a group are live (bit i = image i).  Lane i looks at image i and the result is a
 // ballot, so every role of the kernel sees the same warp-uniform mask.
-__device__ __forceinline__ uint32_t tc_live_mask(const TcArgs& a, int grp, int images, int lane) {
-    const int item = grp * images + lane;
-    bool ok = lane < images && item < a.B;
+__device__ __forceinline__ uint32_t tc_live_mask(const TcArgs& a, int base, int cnt, int lane) {
+    const int item = base + lane;
+    bool ok = lane < cnt;
     if (ok) ok = (!a.action || a.action[item] >= 0) && (!a.in_slot || a.in_slot[item] >= 0) &&
                  (!a.out_slot || a.out_slot[item] >= 0);
     return __ballot_sync(FULL_MASK, ok);
@@ -217,7 +240,8 @@ __device__ __forceinline__ void tc_epilogue_role(const TcArgs& a, const TcCtx& c
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int wq = warp & 3, pi = (warp - 2) >> 2;
     const int n = a.n, ps = a.ps, q0 = n + 2;
-    const int tpi = a.tiles_per_image, images = a.images_per_group, NT = images * tpi;
+    const int tpi = a.tiles_per_image, images = a.images_per_group;
+    const int items_hi = tc_items_hi(a);
     // geometry of this thread's row in tile tt of an image (tt < 3 for n <= 19): r | c << 5 | cls << 10 | valid << 14
     uint32_t geo[3];
 #pragma unroll
@@ -234,8 +258,9 @@ __device__ __forceinline__ void tc_epilogue_role(const TcArgs& a, const TcCtx& c
         asm volatile("bar.sync 1, 256;" ::: "memory");
     }
     uint32_t tile_ctr = 0, it = 0;
-    for (int grp = blockIdx.x; grp < a.num_groups; grp += gridDim.x) {
-        const uint32_t live = tc_live_mask(a, grp, images, lane);
+    for (int base = tc_items_lo(a); base < items_hi; base += images) {
+        const int cnt = min(images, items_hi - base), NT = cnt * tpi;
+        const uint32_t live = tc_live_mask(a, base, cnt, lane);
         if (!live) continue;
         const uint32_t par = it & 1, use = it >> 1;
         if (MODE == MODE_DYN) mbar_wait(cx.tbl_full + par, use & 1);                 // bias tables of this group have landed
@@ -251,6 +276,7 @@ __device__ __forceinline__ void tc_epilogue_role(const TcArgs& a, const TcCtx& c
             const bool is_live = (live >> img) & 1u;
             mbar_wait(cx.acc_full + slot, (c >> 2) & 1);
             tc_fence_after();
+            if (j == 0 && warp == 2 && lane == 0 && it < 4) tc_stamp(a, 10 + 2 * it);
             uint32_t rr[COUT];
             if (is_live) {
                 const uint32_t taddr = cx.tmem_base + ((uint32_t)(wq * 32) << 16) + slot * 128;
@@ -273,7 +299,7 @@ __device__ __forceinline__ void tc_epilogue_role(const TcArgs& a, const TcCtx& c
             const int q = q0 + tt * 128 + wq * 32 + lane;
             const bool store_ok = q < ps;
             const float* tb = (MODE == MODE_DYN) ? s_tbl + (img * 9 + cls) * COUT : s_tbl;
-            const int item = grp * images + img;
+            const int item = base + img;
             const int oslot = a.out_slot ? a.out_slot[item] : item;
             uint4* dst = reinterpret_cast<uint4*>(a.out) + (size_t)oslot * KC_OUT * ps + q;
             float pol = 0.f, val = 0.f, rew = 0.f;
@@ -310,6 +336,7 @@ __device__ __forceinline__ void tc_epilogue_role(const TcArgs& a, const TcCtx& c
             }
         }
         tile_ctr += NT;
+        if (warp == 2 && lane == 0 && it < 4) tc_stamp(a, 11 + 2 * it);
         it++;
         if (MODE != MODE_PLAIN) {
             __syncwarp();
@@ -325,17 +352,19 @@ __device__ __forceinline__ void tc_finaliser_role(const TcArgs& a, const TcCtx& 
     const int lane = threadIdx.x & 31;
     const int n = a.n, np = n * n;
     const int tpi = a.tiles_per_image, images = a.images_per_group;
+    const int items_hi = tc_items_hi(a);
     uint32_t it = 0;
-    for (int grp = blockIdx.x; grp < a.num_groups; grp += gridDim.x) {
-        const uint32_t live = tc_live_mask(a, grp, images, lane);
+    for (int base = tc_items_lo(a); base < items_hi; base += images) {
+        const int cnt = min(images, items_hi - base);
+        const uint32_t live = tc_live_mask(a, base, cnt, lane);
         if (!live) continue;
         const uint32_t par = it & 1, use = it >> 1;
         mbar_wait(cx.fin_full + par, use & 1);
         float* s_pol = reinterpret_cast<float*>(cx.s_pol + par * cx.pol_stride);
         const float* s_part = cx.s_part + par * (TC_SLOTS * 4 * 2);
-        for (int img = 0; img < images; img++) {
+        for (int img = 0; img < cnt; img++) {
             if (!(live & (1u << img))) continue;
-            const int item = grp * images + img;
+            const int item = base + img;
             float vs = 0.f, rs = 0.f;
             for (int k = 0; k < tpi * 4; k++) { vs += s_part[(img * tpi * 4 + k) * 2]; rs += s_part[(img * tpi * 4 + k) * 2 + 1]; }
             if (lane == 0) {
@@ -355,29 +384,28 @@ __device__ __forceinline__ void tc_finaliser_role(const TcArgs& a, const TcCtx& 
                 for (int k = lane; k < np; k += 32) pol_out[k] = lg[k];
                 if (lane == 0) pol_out[np] = a.sc.pass_logit;
             } else {
+                // softmax over np board logits + the pass logit (main.py:298); the exponentials are staged in
+                // place in shared memory so that the loops run np/32 times, not a fixed 12
+                float* ex = s_pol + img * 384;
                 float m = a.sc.pass_logit;
                 for (int k = lane; k < np; k += 32) m = fmaxf(m, lg[k]);
                 m = warp_max_f(m);
-                float ev[12];                                       // np <= 361 = 11.3 x 32
                 float se = 0.f;
-#pragma unroll
-                for (int u = 0; u < 12; u++) {
-                    const int k = u * 32 + lane;
-                    ev[u] = k < np ? expf(lg[k] - m) : 0.f;
-                    se += ev[u];
+                for (int k = lane; k < np; k += 32) {
+                    const float e = __expf(lg[k] - m);
+                    ex[k] = e;
+                    se += e;
                 }
-                const float ep = expf(a.sc.pass_logit - m);
+                const float ep = __expf(a.sc.pass_logit - m);
                 se = warp_sum_f(se) + ep;
-#pragma unroll
-                for (int u = 0; u < 12; u++) {
-                    const int k = u * 32 + lane;
-                    if (k < np) pol_out[k] = ev[u] / se;
-                }
-                if (lane == 0) pol_out[np] = ep / se;
+                const float inv = 1.0f / se;
+                for (int k = lane; k < np; k += 32) pol_out[k] = ex[k] * inv;
+                if (lane == 0) pol_out[np] = ep * inv;
             }
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(cx.fin_empty + par);
+        if (lane == 0 && it < 4) tc_stamp(a, 20 + it);
         it++;
     }
 }
@@ -392,70 +420,98 @@ struct TcMmaCtx {
     uint32_t tmem_base;
 };
 
+struct TcMmaState {
+    uint32_t it, s, bph, tile_ctr;
+    bool leader;
+    uint32_t a_lo[TC_SLOTS];     // descriptor of tile j of a group (image j / tpi, tile j % tpi), tap (0,0), chunk 0
+};
+
+// All MMAs of one group of NT tiles (NT = live images of the group x tiles per image).
 template <int CIN, int COUT, int NT>
-__device__ __forceinline__ void tc_mma_role(const TcArgs& a, const TcMmaCtx& mx) {
-    constexpr int KC_IN = CIN / 8, NH = CIN / 64;
+__device__ __forceinline__ void tc_mma_group(const TcArgs& a, const TcMmaCtx& mx, TcMmaState& st) {
+    constexpr int NH = CIN / 64;
     constexpr uint32_t STAGE_BYTES = COUT * 128;
     constexpr uint32_t IDESC = tc_idesc(COUT);
     const int lane = threadIdx.x & 31;
-    const int n = a.n, ps = a.ps, q0 = n + 2;
-    const int tpi = a.tiles_per_image, images = a.images_per_group;
-    const uint32_t slab_bytes = (uint32_t)KC_IN * ps * 16;
-    const bool leader = elect_one();
-    uint32_t it = 0, s = 0, bph = 0, tile_ctr = 0;
+    const int n = a.n, ps = a.ps;
     const uint32_t a_hi = desc_hi(128), b_hi = desc_hi(128);
     const uint32_t b_lo0 = desc_lo(mx.sB, COUT * 16);
-    uint32_t a_lo[NT];
+    const uint32_t ks_step = 2 * ps;
+    const uint32_t tile_ctr = st.tile_ctr, it = st.it;
+    uint32_t s = st.s, bph = st.bph;
+    const bool leader = st.leader;
+    uint32_t d_col[NT];
+#pragma unroll
+    for (int j = 0; j < NT; j++) d_col[j] = mx.tmem_base + ((tile_ctr + j) & (TC_SLOTS - 1)) * 128;
+    // first touch of the TMEM slots of this group: the epilogue must have drained them
 #pragma unroll
     for (int j = 0; j < NT; j++) {
-        const int img = j / tpi, tt = j - img * tpi;
-        a_lo[j] = desc_lo(mx.sA + img * slab_bytes + (uint32_t)(q0 + tt * 128) * 16, ps * 16);
+        const uint32_t c = tile_ctr + j;
+        mbar_wait(mx.acc_empty + (c & (TC_SLOTS - 1)), ((c >> 2) & 1) ^ 1);
     }
-    const uint32_t ks_step = 2 * ps;
-    for (int grp = blockIdx.x; grp < a.num_groups; grp += gridDim.x) {
-        const uint32_t live = tc_live_mask(a, grp, images, lane);
-        if (!live) continue;
-        uint32_t d_col[NT];
+    for (int h = 0; h < NH; h++) {
+        mbar_wait(mx.a_full + h, it & 1);
+        if (h == 0 && it < 4 && lane == 0) tc_stamp(a, 2 + 2 * it);
+        for (int tap = 0; tap < 9; tap++) {
+            mbar_wait(mx.b_full + s, bph);
+            tc_fence_after();
+            const int dy = (tap * 11) >> 5;                       // tap / 3 for tap < 9
+            const int shift = (dy - 1) * (n + 1) + (tap - 3 * dy - 1);
+            const uint32_t a_off = (uint32_t)(h * 8 * ps + shift);       // 16-byte units
+            const uint32_t b_lo = b_lo0 + s * (STAGE_BYTES >> 4);
+            const uint32_t acc0 = (h | tap) != 0;
+            if (leader) {
 #pragma unroll
-        for (int j = 0; j < NT; j++) d_col[j] = mx.tmem_base + ((tile_ctr + j) & (TC_SLOTS - 1)) * 128;
-        // first touch of the TMEM slots of this group: the epilogue must have drained them
+                for (int ks = 0; ks < 4; ks++) {
 #pragma unroll
-        for (int j = 0; j < NT; j++) {
-            const uint32_t c = tile_ctr + j;
-            mbar_wait(mx.acc_empty + (c & (TC_SLOTS - 1)), ((c >> 2) & 1) ^ 1);
-        }
-        for (int h = 0; h < NH; h++) {
-            mbar_wait(mx.a_full + h, it & 1);
-            for (int tap = 0; tap < 9; tap++) {
-                mbar_wait(mx.b_full + s, bph);
-                tc_fence_after();
-                const int dy = (tap * 11) >> 5;                       // tap / 3 for tap < 9
-                const int shift = (dy - 1) * (n + 1) + (tap - 3 * dy - 1);
-                const uint32_t a_off = (uint32_t)(h * 8 * ps + shift);       // 16-byte units
-                const uint32_t b_lo = b_lo0 + s * (STAGE_BYTES >> 4);
-                const uint32_t acc0 = (h | tap) != 0;
-                if (leader) {
-#pragma unroll
-                    for (int ks = 0; ks < 4; ks++) {
-#pragma unroll
-                        for (int j = 0; j < NT; j++)
-                            umma_bf16(d_col[j], a_lo[j] + a_off + ks * ks_step, a_hi, b_lo + ks * (2 * COUT), b_hi, IDESC,
-                                      ks == 0 ? acc0 : 1u);
-                    }
-                    umma_commit(mx.b_empty + s);          // frees the weight stage when these MMAs retire
+                    for (int j = 0; j < NT; j++)
+                        umma_bf16(d_col[j], st.a_lo[j] + a_off + ks * ks_step, a_hi, b_lo + ks * (2 * COUT), b_hi, IDESC,
+                                  ks == 0 ? acc0 : 1u);
                 }
-                __syncwarp();
-                if (++s == (uint32_t)a.stages) { s = 0; bph ^= 1; }
+                umma_commit(mx.b_empty + s);          // frees the weight stage when these MMAs retire
             }
-            if (leader) umma_commit(mx.a_empty + h);      // this half of the input slab may be overwritten
+            __syncwarp();
+            if (++s == (uint32_t)a.stages) { s = 0; bph ^= 1; }
         }
-        if (leader) {
+        if (leader) umma_commit(mx.a_empty + h);      // this half of the input slab may be overwritten
+    }
+    if (leader) {
 #pragma unroll
-            for (int j = 0; j < NT; j++) umma_commit(mx.acc_full + ((tile_ctr + j) & (TC_SLOTS - 1)));
+        for (int j = 0; j < NT; j++) umma_commit(mx.acc_full + ((tile_ctr + j) & (TC_SLOTS - 1)));
+    }
+    if (it < 4 && lane == 0) tc_stamp(a, 3 + 2 * it);
+    __syncwarp();
+    st.s = s;
+    st.bph = bph;
+    st.tile_ctr = tile_ctr + NT;
+    st.it = it + 1;
+}
+
+template <int CIN, int COUT>
+__device__ __forceinline__ void tc_mma_role(const TcArgs& a, const TcMmaCtx& mx) {
+    constexpr int KC_IN = CIN / 8;
+    const int lane = threadIdx.x & 31;
+    const int ps = a.ps, q0 = a.n + 2;
+    const int tpi = a.tiles_per_image, images = a.images_per_group;
+    const uint32_t slab_bytes = (uint32_t)KC_IN * ps * 16;
+    TcMmaState st;
+    st.it = st.s = st.bph = st.tile_ctr = 0;
+    st.leader = elect_one();
+#pragma unroll
+    for (int j = 0; j < TC_SLOTS; j++) {
+        const int img = j / tpi, tt = j - img * tpi;
+        st.a_lo[j] = desc_lo(mx.sA + img * slab_bytes + (uint32_t)(q0 + tt * 128) * 16, ps * 16);
+    }
+    const int items_hi = tc_items_hi(a);
+    for (int base = tc_items_lo(a); base < items_hi; base += images) {
+        const int cnt = min(images, items_hi - base);
+        const uint32_t live = tc_live_mask(a, base, cnt, lane);
+        if (!live) continue;
+        switch (cnt * tpi) {
+            case 1: tc_mma_group<CIN, COUT, 1>(a, mx, st); break;
+            case 2: tc_mma_group<CIN, COUT, 2>(a, mx, st); break;
+            default: tc_mma_group<CIN, COUT, 3>(a, mx, st); break;
         }
-        __syncwarp();
-        tile_ctr += NT;
-        it++;
     }
 }
 
@@ -484,7 +540,8 @@ k_tc_conv(const __grid_constant__ TcArgs a) {
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n = a.n, ps = a.ps;
-    const int tpi = a.tiles_per_image, images = a.images_per_group, NT = images * tpi;
+    const int images = a.images_per_group;
+    if (threadIdx.x == 0) tc_stamp(a, 0);
     const uint32_t slab_bytes = (uint32_t)KC_IN * ps * 16;
     const uint32_t half_bytes = slab_bytes / NH;
     const int q0 = n + 2;                           // flat position of pixel (0,0)
@@ -504,12 +561,15 @@ k_tc_conv(const __grid_constant__ TcArgs a) {
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *s_tmem;
+    if (threadIdx.x == 0) tc_stamp(a, 1);
 
     if (warp == 0) {
         // ===================================================== TMA producer (lane 0 issues, the warp stays converged)
         uint32_t it = 0, s = 0, bph = 0;
-        for (int grp = blockIdx.x; grp < a.num_groups; grp += gridDim.x) {
-            const uint32_t live = tc_live_mask(a, grp, images, lane);
+        const int items_hi = tc_items_hi(a);
+        for (int base = tc_items_lo(a); base < items_hi; base += images) {
+            const int cnt = min(images, items_hi - base);
+            const uint32_t live = tc_live_mask(a, base, cnt, lane);
             if (!live) continue;
             if (MODE == MODE_DYN) {
                 // per-action bias tables of this group -> s_tbl[parity] (free once the epilogue of group it-2 is through)
@@ -517,8 +577,8 @@ k_tc_conv(const __grid_constant__ TcArgs a) {
                 if (use > 0) mbar_wait(fin_full + par, (use - 1) & 1);
                 if (lane == 0) mbar_expect_tx(tbl_full + par, 9u * COUT * 4 * __popc(live));
                 __syncwarp();
-                if (lane < images && ((live >> lane) & 1u)) {
-                    const int item = grp * images + lane;
+                if ((live >> lane) & 1u) {
+                    const int item = base + lane;
                     bulk_g2s(smem + L.tbl_off + par * L.tbl_stride + (uint32_t)lane * 9 * COUT * 4,
                              a.tbl + (size_t)a.action[item] * 9 * COUT, 9u * COUT * 4, tbl_full + par);
                 }
@@ -527,8 +587,8 @@ k_tc_conv(const __grid_constant__ TcArgs a) {
                 mbar_wait(a_empty + h, (it & 1) ^ 1);
                 if (lane == 0) mbar_expect_tx(a_full + h, half_bytes * __popc(live));
                 __syncwarp();
-                if (lane < images && ((live >> lane) & 1u)) {
-                    const int item = grp * images + lane;
+                if ((live >> lane) & 1u) {
+                    const int item = base + lane;
                     const int slot = a.in_slot ? a.in_slot[item] : item;
                     const uint8_t* src = reinterpret_cast<const uint8_t*>(a.in) + (size_t)slot * slab_bytes + (size_t)h * half_bytes;
                     bulk_g2s(sA + (size_t)lane * slab_bytes + (size_t)h * half_bytes, src, half_bytes, a_full + h);
@@ -553,12 +613,7 @@ k_tc_conv(const __grid_constant__ TcArgs a) {
         mx.a_full = a_full; mx.a_empty = a_empty; mx.b_full = b_full; mx.b_empty = b_empty;
         mx.acc_full = acc_full; mx.acc_empty = acc_empty;
         mx.tmem_base = tmem_base;
-        switch (NT) {
-            case 1: tc_mma_role<CIN, COUT, 1>(a, mx); break;
-            case 2: tc_mma_role<CIN, COUT, 2>(a, mx); break;
-            case 3: tc_mma_role<CIN, COUT, 3>(a, mx); break;
-            default: tc_mma_role<CIN, COUT, 4>(a, mx); break;
-        }
+        tc_mma_role<CIN, COUT>(a, mx);
     } else {
         TcCtx cx;
         cx.s_tbl = smem + L.tbl_off;
@@ -577,6 +632,7 @@ k_tc_conv(const __grid_constant__ TcArgs a) {
     }
     tc_fence_before();
     __syncthreads();
+    if (threadIdx.x == 0) tc_stamp(a, 30);
     if (warp == 1) {
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem_base) : "memory");
@@ -781,10 +837,10 @@ int launch_tc_conv(TcArgs& a, int n, int B, cudaStream_t st) {
     }
     a.B = B;
     a.n = n;
+    a.trace = g_tc_trace;
     a.ps = tc_ps(n);
     a.tiles_per_image = tc_tiles_per_image(n);
-    a.images_per_group = TC_SLOTS / a.tiles_per_image;
-    a.num_groups = ceil_div(B, a.images_per_group);
+    a.images_per_group = tc_images_per_group(n);
     const int kblocks = 9 * CIN / 64;
     const TcSmemLayout L0 = tc_smem_layout(n, CIN, COUT, 0, MODE == MODE_DYN);
     int stages = ((int)TC_SMEM_LIMIT - (int)L0.total) / (COUT * 128);
@@ -793,12 +849,20 @@ int launch_tc_conv(TcArgs& a, int n, int B, cudaStream_t st) {
     MZGO_CHECK_ARG(stages >= 2, "shared memory layout of %u B leaves no room for the weight ring", L0.total);
     a.stages = stages;
     const TcSmemLayout L = tc_smem_layout(n, CIN, COUT, stages, MODE == MODE_DYN);
-    const int grid = a.num_groups < num_sms() ? a.num_groups : num_sms();
+    const int grid = B < num_sms() ? B : num_sms();
     k_tc_conv<CIN, COUT, MODE><<<grid, TC_THREADS, L.total, st>>>(a);
     mzgo_count_launch();
     MZGO_LAUNCH_CHECK();
     return MZGO_OK;
 }
+
+}  // namespace
+// Debug aid (tools/tc_trace.py): when set, every k_tc_conv launch stamps its role timeline into buf[grid][32].
+extern "C" int mzgo_debug_tc_trace(void* buf) {
+    g_tc_trace = (unsigned long long*)buf;
+    return MZGO_OK;
+}
+namespace {
 
 int fill_heads(const mzgo_net_t* net, TcArgs& a) {
     std::lock_guard<std::mutex> lk(g_heads_mu);
