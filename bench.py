@@ -184,15 +184,19 @@ def run_ours(args, wl):
     torch.manual_seed(0)                                    # random-init weights of the reference architecture
     net = mz.MuZeroNet(LATENT, A, precision=args.precision).to(dev).eval()
     bytes_bcast = mzdist.broadcast_weights(net, src=0)       # weight version 0 from the learner rank
-    # fit the latent arena into HBM (19x19 / 800 sims / 2048 games needs ~152 GB in bf16)
+    # The latent arena of one search is G * (S + 1) slots.  When the named game count does not fit the HBM at
+    # once (19x19 / 800 sims / 2048 games: 177 GB of bf16 latents) the games run as `waves` equal groups that
+    # take turns on one set of search buffers (muzero_go_b200.WaveGroup): still G games, one move each per step.
     free_b, _ = torch.cuda.mem_get_info()
     per_game = (S + 1) * (net.slot_bytes() + A * 18 + 8) + 64 * 1024
-    if G * per_game > 0.92 * free_b:
-        # whole rounds of the persistent network kernel: one leaf per SM and round (148 SMs)
-        G = int(0.92 * free_b / per_game) // 148 * 148
+    waves = 1
+    while (G // waves) * per_game > 0.90 * free_b or G % waves:
+        waves += 1
     T = 2
-    eng = mz.SelfPlayEngine(net, n, G, S, search=mz.SearchConfig(seed=1000 + rank), traj_capacity=T,
-                            restart_finished=True)
+    group = mz.WaveGroup(net, n, G, S, waves=waves, search=mz.SearchConfig(seed=1000 + rank), traj_capacity=T,
+                         restart_finished=True)
+    eng = group.engines[0]          # the single-kernel timings below run on one wave's buffers
+    GW = G // waves
     lib = _lib.load()
 
     def barrier():
@@ -201,8 +205,8 @@ def run_ours(args, wl):
         torch.cuda.synchronize()
 
     def step(row=0):
-        eng.run(1, traj_offset=row)
-        rows = eng.trajectory_rows(row, row + 1)
+        group.run(1, traj_offset=row)
+        rows = group.trajectory_rows(row, row + 1)
         if world > 1:                                        # trajectory gather to the replay side, outside the search
             mzdist.gather_trajectories(rows, A)
         return rows
@@ -211,7 +215,7 @@ def run_ours(args, wl):
         step()
     barrier()
     lib.mzgo_launch_count(1)
-    c0 = eng.read_counters()
+    c0 = group.read_counters()
     sampler = ClockSampler(local)
     sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -224,27 +228,37 @@ def run_ours(args, wl):
     ms = e0.elapsed_time(e1)
     clocks = sampler.stop()
     launches = int(lib.mzgo_launch_count(0))
-    c1 = eng.read_counters()
+    c1 = group.read_counters()
     sims_done = c1["simulations"] - c0["simulations"]
     moves_done = c1["moves"] - c0["moves"]
     depth = (c1["leaf_depth_sum"] - c0["leaf_depth_sum"]) / max(1, sims_done)
 
     # ---- end to end through the public API with HOST buffers: positions up, trajectory row down, every step
     host_boards = torch.empty((G, 64), dtype=torch.int32).pin_memory()
-    host_boards.copy_(eng.boards.records)
-    row_bytes = mzdist.pack_rows(eng.trajectory_rows(0, 1))
+    dev_boards = [e.boards.records for e in group.engines]
+
+    def boards_up():
+        for w, rec in enumerate(dev_boards):
+            rec.copy_(host_boards[w * GW:(w + 1) * GW], non_blocking=True)
+
+    def boards_down():
+        for w, rec in enumerate(dev_boards):
+            host_boards[w * GW:(w + 1) * GW].copy_(rec)
+
+    boards_down()
+    row_bytes = mzdist.pack_rows(group.trajectory_rows(0, 1))
     host_row = torch.empty(row_bytes.shape, dtype=torch.uint8).pin_memory()
     barrier()
     t0 = time.perf_counter()
     for _ in range(K):
-        eng.boards.records.copy_(host_boards, non_blocking=True)
+        boards_up()
         rows = step()
         host_row.copy_(mzdist.pack_rows(rows), non_blocking=True)
         torch.cuda.synchronize()
-        host_boards.copy_(eng.boards.records)                # next step's input comes from the host again
+        boards_down()                                        # next step's input comes from the host again
     barrier()
     e2e_s = time.perf_counter() - t0
-    c2 = eng.read_counters()
+    c2 = group.read_counters()
     e2e_sims = c2["simulations"] - c1["simulations"]
 
     # ---- dominant kernel (recurrent inference of one leaf batch), timed alone with CUDA events
@@ -255,7 +269,7 @@ def run_ours(args, wl):
     k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     args_rec = (d.net, _lib.ptr(eng.arena), _lib.ptr(eng.tree.leaf_in_slot), _lib.ptr(eng.tree.leaf_action),
                 _lib.ptr(eng.tree.leaf_out_slot), _lib.ptr(eng.leaf_reward), _lib.ptr(eng.leaf_value),
-                _lib.ptr(eng.leaf_policy), 1, G, _lib.stream_ptr())
+                _lib.ptr(eng.leaf_policy), 1, GW, _lib.stream_ptr())
     for _ in range(3):
         _lib.check(lib.mzgo_net_recurrent(*args_rec))
     torch.cuda.synchronize()
@@ -337,14 +351,15 @@ def run_ours(args, wl):
         line = {"metric": "mcts_simulations_per_sec", "value": sims_all / (ms * 1e-3), "unit": "sims/s", "n_gpus": world,
                 "steps": K, "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "bf16" if args.precision == "bf16" else "f32", "data": "synthetic",
-                "config": {"workload": wl["name"], "board": n, "games_per_gpu": G, "games_total": int(G_all),
+                "config": {"workload": wl["name"], "board": n, "games_per_gpu": G, "games_total": int(G_all), "waves": waves,
+                           "games_per_wave": GW,
                            "sims_per_move": S, "latent_dim": LATENT, "weights": "random-init (torch.manual_seed(0))",
                            "cache": "inputs larger than L2 (latent arena %.1f GB per GPU)" % (eng.arena.numel() / 1e9),
                            "parallelism": f"games sharded over {world} GPU(s), no collective inside the search"},
                 "moves_per_sec": moves_all / (ms * 1e-3), "mean_leaf_depth": depth,
                 "e2e": {"value": e2e_sims_all / (e2e_ms * 1e-3), "unit": "sims/s", "h2d_bytes_per_step": G * 256,
                         "d2h_bytes_per_step": row_b + G * 256},
-                "gpu_launches": int(launches_all),
+                "gpu_launches": int(launches_all), "search_graph_replays": int(lib.mzgo_graph_replays()),
                 "roofline": {"bound": "tensor", "kernel": "mzgo_net_recurrent (dynamics conv3x3 + heads, one leaf batch)",
                              "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved / peak_tf,
                              "traffic": None, "peak_source": peaks["source"] + " bf16 sustained",

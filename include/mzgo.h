@@ -121,6 +121,9 @@ typedef struct mzgo_tree {
     int32_t* sims_done;   /* device [G] completed simulations */
     int32_t* dropped;     /* device [G] simulations dropped because nothing was selectable (main.py:359-363) */
     uint8_t* active;      /* device [G] 0 = tree idle (game finished) */
+    int32_t* move_index_dev; /* device [1]: mzgo_tree_reset_roots stores its move_index here and the tree-step
+                                kernel keys its RNG with it, so a captured CUDA graph of the search loop can be
+                                replayed for every move (mzgo_selfplay_run) */
 } mzgo_tree_t;
 
 /* Search variants.  MAIN: main.py:247-368 and play.py:104-216.  SELFPLAY: self_play.py:142-343
@@ -303,6 +306,10 @@ int mzgo_selfplay_run(const mzgo_selfplay_t* sp, int num_moves, int traj_offset,
 /* One search only (the body of MCTS.run after the root is prepared): `num_simulations` rounds of
  * select -> recurrent inference -> expand/backup on sp->tree.  choice_stream as in mzgo_tree_select. */
 int mzgo_search_run(const mzgo_selfplay_t* sp, const uint32_t* choice_stream, int stride, void* stream);
+
+/* Number of searches mzgo_selfplay_run served by replaying its captured CUDA graph of the search loop
+ * (the graph is captured on the second move of an engine; MZGO_NO_GRAPH=1 in the environment disables it). */
+long long mzgo_graph_replays(void);
 
 /* Number of kernels launched by this library in the calling thread since the last reset
  * (bench.py's gpu_launches). */

@@ -10,7 +10,7 @@ from .tree import SearchConfig, Tree
 from .networks import MuZeroNet
 from .mcts import MCTS, MCTSNode
 from .agent import MuZeroAgent
-from .selfplay import SelfPlayEngine
+from .selfplay import SelfPlayEngine, WaveGroup
 
-__all__ = ["MzgoError", "GoBoards", "GoEnv", "govars", "make", "SearchConfig", "Tree", "MuZeroNet", "MCTS",
+__all__ = ["MzgoError", "GoBoards", "GoEnv", "govars", "make", "SearchConfig", "Tree", "MuZeroNet", "MCTS", "WaveGroup",
            "MCTSNode", "MuZeroAgent", "SelfPlayEngine"]

@@ -24,7 +24,7 @@ class TreeDesc(C.Structure):
                 ("child", vp), ("parent", vp), ("root_visit", vp), ("root_vsum", vp), ("n_nodes", vp),
                 ("leaf_parent", vp), ("leaf_action", vp), ("leaf_node", vp), ("leaf_depth", vp),
                 ("leaf_in_slot", vp), ("leaf_out_slot", vp), ("choice_ctr", vp), ("depth_sum", vp),
-                ("sims_done", vp), ("dropped", vp), ("active", vp)]
+                ("sims_done", vp), ("dropped", vp), ("active", vp), ("move_index_dev", vp)]
 
 
 class SearchParams(C.Structure):
@@ -66,6 +66,7 @@ _PROTOS = {
     "mzgo_abi_version": (i32, []),
     "mzgo_device_ok": (i32, []),
     "mzgo_launch_count": (i64, [i32]),
+    "mzgo_graph_replays": (C.c_longlong, []),
     "mzgo_sizeof": (i64, [i32]),
     "mzgo_rules_reset": (i32, [vp, i32, i32, vp]),
     "mzgo_rules_step": (i32, [vp, vp, vp, i32, i32, vp]),

@@ -13,6 +13,11 @@ void mzgo_set_error(const char* fmt, ...) {
 
 void mzgo_count_launch() { g_launches++; }
 void mzgo_count_launches(int k) { g_launches += k; }
+int64_t mzgo_launch_count_peek() { return g_launches; }
+
+static unsigned long long g_net_generation = 0;
+unsigned long long mzgo_net_generation() { return g_net_generation; }
+void mzgo_net_bump_generation() { g_net_generation++; }
 
 extern "C" const char* mzgo_last_error(void) { return g_err; }
 

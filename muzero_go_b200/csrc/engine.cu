@@ -4,9 +4,33 @@
 // choice, env.step, trajectory append, two-pass / move-cap termination) and the game epilogue
 // main.py:703-711.  The host loop below only enqueues kernels; per simulation it enqueues
 // select -> recurrent inference -> expand/backup for the whole batch of games.
+#include <string.h>
+
+#include <mutex>
+#include <vector>
+
 #include "nets.cuh"
 
 namespace {
+
+// ---- CUDA graph of the search loop.  One move enqueues 2 * simulations + 1 dependent launches; at 9x9 the
+// gaps between them cost 8 % of the step (tools/graph_probe.py), so mzgo_selfplay_run replays a captured
+// graph of mzgo_search_run instead.  Everything the loop reads per move comes from device memory (the move
+// index through tree.move_index_dev), so one graph serves every move of an engine.  Key: the descriptor bytes
+// (with the by-value move index cleared) and the weight generation (head parameters are kernel-argument
+// constants, nets_tc.cu).  The first move of a new key runs un-captured (it may set function attributes).
+struct SearchGraph {
+    mzgo_selfplay_t key;
+    unsigned long long generation;
+    int device;
+    int uses;
+    int launches;
+    cudaGraphExec_t exec;
+};
+std::mutex g_graph_mu;
+std::vector<SearchGraph> g_graphs;
+long long g_graph_replays = 0;
+constexpr size_t MAX_GRAPHS = 8;
 
 constexpr int SP_THREADS = 128;
 
@@ -106,6 +130,70 @@ extern "C" int mzgo_search_run(const mzgo_selfplay_t* sp, const uint32_t* choice
     return MZGO_OK;
 }
 
+// The search of one move through the graph cache (falls back to plain launches when capture is not possible).
+static int search_run_cached(const mzgo_selfplay_t* sp, cudaStream_t st) {
+    static const bool disabled = getenv("MZGO_NO_GRAPH") != nullptr;      // A/B switch for measurements
+    if (disabled || sp->num_simulations == 0) return mzgo_search_run(sp, nullptr, 0, st);
+    mzgo_selfplay_t key;
+    memcpy(&key, sp, sizeof(key));
+    key.tree.move_index = 0;
+    int device = 0;
+    MZGO_CUDA(cudaGetDevice(&device));
+    const unsigned long long gen = mzgo_net_generation();
+    std::lock_guard<std::mutex> lk(g_graph_mu);
+    SearchGraph* e = nullptr;
+    for (auto& c : g_graphs)
+        if (c.device == device && c.generation == gen && memcmp(&c.key, &key, sizeof(key)) == 0) e = &c;
+    if (!e) {
+        if (g_graphs.size() >= MAX_GRAPHS) {
+            if (g_graphs.front().exec) cudaGraphExecDestroy(g_graphs.front().exec);
+            g_graphs.erase(g_graphs.begin());
+        }
+        SearchGraph c;
+        memcpy(&c.key, &key, sizeof(key));
+        c.generation = gen; c.device = device; c.uses = 0; c.launches = 0; c.exec = nullptr;
+        g_graphs.push_back(c);
+        e = &g_graphs.back();
+    }
+    e->uses++;
+    if (e->uses == 1) return mzgo_search_run(sp, nullptr, 0, st);
+    if (!e->exec && e->launches >= 0) {
+        // captured on a private stream (the caller's may be the legacy default stream, which cannot capture);
+        // the instantiated graph is then launched into the caller's stream like any other work
+        static thread_local cudaStream_t cap = nullptr;
+        cudaGraph_t graph = nullptr;
+        const int64_t before = mzgo_launch_count_peek();
+        if ((!cap && cudaStreamCreateWithFlags(&cap, cudaStreamNonBlocking) != cudaSuccess) ||
+            cudaStreamBeginCapture(cap, cudaStreamCaptureModeThreadLocal) != cudaSuccess) {
+            cudaGetLastError();
+            e->launches = -1;                                   // do not try again
+            return mzgo_search_run(sp, nullptr, 0, st);
+        }
+        const int rc = mzgo_search_run(sp, nullptr, 0, cap);
+        const cudaError_t ce = cudaStreamEndCapture(cap, &graph);
+        const int captured = (int)(mzgo_launch_count_peek() - before);
+        mzgo_count_launches(-captured);                         // nothing ran yet
+        if (rc != MZGO_OK || ce != cudaSuccess || !graph ||
+            cudaGraphInstantiate(&e->exec, graph, 0) != cudaSuccess) {
+            cudaGetLastError();
+            if (graph) cudaGraphDestroy(graph);
+            e->exec = nullptr;
+            e->launches = -1;
+            return mzgo_search_run(sp, nullptr, 0, st);
+        }
+        cudaGraphDestroy(graph);
+        e->launches = captured;
+    }
+    if (!e->exec) return mzgo_search_run(sp, nullptr, 0, st);
+    MZGO_CUDA(cudaGraphLaunch(e->exec, st));
+    g_graph_replays++;
+    mzgo_count_launches(e->launches);
+    return MZGO_OK;
+}
+
+// Searches served by a replayed graph so far (bench.py reports it next to gpu_launches).
+extern "C" long long mzgo_graph_replays(void) { return g_graph_replays; }
+
 extern "C" int mzgo_selfplay_run(const mzgo_selfplay_t* sp_in, int num_moves, int traj_offset,
                                  uint32_t first_move_index, void* stream) {
     if (int e = check_sp(sp_in)) return e;
@@ -138,7 +226,7 @@ extern "C" int mzgo_selfplay_run(const mzgo_selfplay_t* sp_in, int num_moves, in
                                           stream))
             return e;
         // the simulations (main.py:291-314)
-        if (int e = mzgo_search_run(&sp, nullptr, 0, stream)) return e;
+        if (int e = search_run_cached(&sp, st)) return e;
         // action + policy target (main.py:659-677), then env.step (main.py:681)
         if (int e = mzgo_tree_choose_action(&sp.tree, &sp.params, 0.f, sp.game_temperature, move_index, sp.action,
                                             sp.traj_policy + (size_t)t * G * A, sp.traj_root_value + (size_t)t * G,

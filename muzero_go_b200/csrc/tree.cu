@@ -108,6 +108,7 @@ k_tree_reset_roots(mzgo_tree_t t, mzgo_search_params_t p, const float* __restric
     if (lane == 0) {
         t.leaf_parent[g] = -1;
         t.leaf_action[g] = -1;
+        if (g == 0) *t.move_index_dev = (int32_t)move_index;
     }
     if (!t.active[g]) return;
     const int A = t.A, np = n * n;
@@ -413,8 +414,18 @@ k_tree_expand_backup(mzgo_tree_t t, mzgo_search_params_t p, const float* __restr
 // edge arrays with up to three edges per thread, and the backup updates all edges of the selection
 // path in parallel: the path is written by the selection into the scratch row ([g][0][A] of `prior`).
 // Arithmetic is the same, operation for operation, as in k_tree_select / k_tree_expand_backup.
+//
+// Memory round trips (the kernel is latency bound: a few KB per game, dependent levels):
+//   1. everything that does not depend on another load is fetched at the top in one batch: the leaf record,
+//      the network outputs, the mask, the stored path AND the root level of the next selection (visits,
+//      priors, value sums, child links).  The root statistics this very step changes (one edge of the
+//      backup path, the child link when the leaf hangs off the root) are patched in registers;
+//   2. the backup read-modify-write of the path edges;
+//   3. one batch per level below the root (visits, priors, value sums and child links together).
 constexpr int STEP_THREADS = 128;
 constexpr int STEP_EPT = 3;   // edges per thread: A <= 3 * TPG
+
+__device__ __forceinline__ int npar_root_after(int root_visit0, int act) { return root_visit0 + (act >= 0 ? 1 : 0); }
 
 template <int TPG>
 __device__ __forceinline__ void step_sync() {
@@ -422,80 +433,204 @@ __device__ __forceinline__ void step_sync() {
 }
 
 template <int TPG>
-__global__ void __launch_bounds__(STEP_THREADS, 10)
+struct StepShared {
+    static constexpr int GPB = STEP_THREADS / TPG, WPG = TPG / 32, NW = STEP_EPT * WPG;
+    uint32_t open[GPB][NW];      // ballot words per game (word w covers actions [32w, 32w+32))
+    uint32_t live[GPB][WPG];
+    double qmin[GPB][WPG], qmax[GPB][WPG], best[GPB][WPG];
+    int besta[GPB][WPG], bestn[GPB][WPG], bestc[GPB][WPG];
+    float pri[GPB][STEP_EPT * TPG];   // self_play.py variant: masked child priors before the renormalisation
+    float tot[GPB];
+};
+
+// One PUCT level (main.py:318-358) on register-resident edge data.  Returns 0: an unexpanded edge was drawn
+// (*out_a), 1: descend through *out_a into child *out_c (which has *out_n visits), 2: nothing selectable.
+template <int TPG>
+__device__ __forceinline__ int step_level(StepShared<TPG>& sh, int sub, int tid, const int (&nv)[STEP_EPT],
+                                          const double (&cp)[STEP_EPT], const double (&vs)[STEP_EPT],
+                                          const int (&ch)[STEP_EPT], uint32_t pos, int npar, bool v1, uint32_t rnd_or_ctr,
+                                          const uint32_t* choice_stream, size_t stream_off, const mzgo_search_params_t& p,
+                                          uint32_t g, uint32_t move_index, int* out_a, int* out_n, int* out_c) {
+    constexpr int WPG = TPG / 32, NW = STEP_EPT * WPG;
+    const int wig = tid >> 5, lane = tid & 31;
+#pragma unroll
+    for (int e = 0; e < STEP_EPT; e++) {
+        const bool opn = ((pos >> e) & 1u) && nv[e] == 0;
+        const uint32_t b = __ballot_sync(FULL_MASK, opn);
+        if (lane == 0) sh.open[sub][e * WPG + wig] = b;
+    }
+    const uint32_t any_live = __ballot_sync(FULL_MASK, pos != 0u);
+    if (lane == 0) sh.live[sub][wig] = any_live;
+    step_sync<TPG>();
+    int n_open = 0;
+    uint32_t all_live = 0u;
+#pragma unroll
+    for (int w = 0; w < NW; w++) n_open += __popc(sh.open[sub][w]);
+#pragma unroll
+    for (int w = 0; w < WPG; w++) all_live |= sh.live[sub][w];
+    if (n_open > 0) {
+        // random.choice(unexpanded), main.py:322-325
+        const uint32_t r = choice_stream ? choice_stream[stream_off + rnd_or_ctr]
+                                         : mzgo_rand_u32(p.seed, g, 0x20000u + move_index, rnd_or_ctr);
+        int k = (int)(r % (uint32_t)n_open);
+        int a_sel = -1;
+#pragma unroll
+        for (int w = 0; w < NW; w++) {
+            const uint32_t b = sh.open[sub][w];
+            const int c = __popc(b);
+            if (a_sel < 0) {
+                if (k < c) a_sel = w * 32 + (int)__fns(b, 0, k + 1);
+                else k -= c;
+            }
+        }
+        // word w = e * WPG + wig covers the edges e * TPG + wig * 32 + [0, 32): the same numbering as the action index
+        *out_a = a_sel;
+        return 0;
+    }
+    if (!all_live) return 2;                     // nothing selectable: simulation dropped / terminal leaf
+    // Q of every live edge, min-max normalisation set = prior > 0 (main.py:328-339)
+    double q[STEP_EPT];
+    double qmin = INFINITY, qmax = -INFINITY;
+#pragma unroll
+    for (int e = 0; e < STEP_EPT; e++) {
+        q[e] = 0.0;
+        if ((pos >> e) & 1u) {
+            if (nv[e] > 0) q[e] = __ddiv_rn(vs[e], (double)nv[e]);
+            qmin = fmin(qmin, q[e]);
+            qmax = fmax(qmax, q[e]);
+        }
+    }
+    qmin = warp_min_d(qmin);
+    qmax = warp_max_d(qmax);
+    if (WPG > 1) {
+        if (lane == 0) { sh.qmin[sub][wig] = qmin; sh.qmax[sub][wig] = qmax; }
+        step_sync<TPG>();
+#pragma unroll
+        for (int w = 0; w < WPG; w++) { qmin = fmin(qmin, sh.qmin[sub][w]); qmax = fmax(qmax, sh.qmax[sub][w]); }
+    }
+    const double sq = __dsqrt_rn((double)(v1 ? max(1, npar) : npar + 1));   // main.py:354 / self_play.py:297-300
+    const bool norm = qmax > qmin;
+    const double range = __dsub_rn(qmax, qmin);
+    double best = -INFINITY;
+    int best_a = -1, best_n = 0, best_c = -1;
+#pragma unroll
+    for (int e = 0; e < STEP_EPT; e++) {
+        if ((pos >> e) & 1u) {
+            const double qn = norm ? __ddiv_rn(__dsub_rn(q[e], qmin), range) : q[e];
+            const double u = __ddiv_rn(__dmul_rn(cp[e], sq), (double)(1 + nv[e]));
+            const double score = __dadd_rn(qn, u);
+            if (score > best) { best = score; best_a = e * TPG + tid; best_n = nv[e]; best_c = ch[e]; }   // e ascending = action ascending
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const double ob = __shfl_xor_sync(FULL_MASK, best, o);
+        const int oa = __shfl_xor_sync(FULL_MASK, best_a, o);
+        const int on = __shfl_xor_sync(FULL_MASK, best_n, o);
+        const int oc = __shfl_xor_sync(FULL_MASK, best_c, o);
+        const bool take = (oa >= 0) && (best_a < 0 || ob > best || (ob == best && oa < best_a));
+        if (take) { best = ob; best_a = oa; best_n = on; best_c = oc; }
+    }
+    if (WPG > 1) {
+        if (lane == 0) { sh.best[sub][wig] = best; sh.besta[sub][wig] = best_a; sh.bestn[sub][wig] = best_n; sh.bestc[sub][wig] = best_c; }
+        step_sync<TPG>();
+        best = sh.best[sub][0]; best_a = sh.besta[sub][0]; best_n = sh.bestn[sub][0]; best_c = sh.bestc[sub][0];
+#pragma unroll
+        for (int w = 1; w < WPG; w++) {
+            const double ob = sh.best[sub][w];
+            const int oa = sh.besta[sub][w], on = sh.bestn[sub][w], oc = sh.bestc[sub][w];
+            const bool take = (oa >= 0) && (best_a < 0 || ob > best || (ob == best && oa < best_a));
+            if (take) { best = ob; best_a = oa; best_n = on; best_c = oc; }
+        }
+    }
+    if (best_a < 0) return 2;                    // only NaN / -inf scores: the reference falls out of the loop too
+    *out_a = best_a;
+    *out_n = best_n;
+    *out_c = best_c;
+    return 1;
+}
+
+template <int TPG>
+__global__ void __launch_bounds__(STEP_THREADS, 6)
 k_tree_step(mzgo_tree_t t, mzgo_search_params_t p, const float* __restrict__ soft, const float* __restrict__ reward,
             const float* __restrict__ value, const uint32_t* __restrict__ choice_stream, int stride, int do_backup,
             int do_select) {
     constexpr int GPB = STEP_THREADS / TPG;     // games per block
-    constexpr int WPG = TPG / 32;               // warps per game
-    constexpr int NW = STEP_EPT * WPG;          // ballot words per game (word w covers actions [32w, 32w+32))
-    __shared__ uint32_t s_open[GPB][NW];
-    __shared__ uint32_t s_live[GPB][WPG];
-    __shared__ double s_min[GPB][WPG], s_max[GPB][WPG], s_best[GPB][WPG];
-    __shared__ int s_besta[GPB][WPG], s_bestn[GPB][WPG];
-    __shared__ float s_pri[GPB][STEP_EPT * TPG];  // self_play.py variant: masked child priors before the renormalisation
-    __shared__ float s_tot[GPB];
+    __shared__ StepShared<TPG> sh;
     const bool v1 = p.variant == MZGO_VARIANT_SELFPLAY;
     const int sub = threadIdx.x / TPG, tid = threadIdx.x % TPG;
-    const int wig = tid >> 5, lane = tid & 31;
     const int g = blockIdx.x * GPB + sub;
     if (g >= t.G) return;                        // TPG == 128: the whole block; TPG == 32: whole warps
     const int A = t.A, M = t.M;
     int* path = reinterpret_cast<int*>(t.prior + (size_t)g * M * A);   // scratch row of the root (its priors are float64, elsewhere)
+    const size_t rbase = (size_t)g * M * A;      // edges of the root
 
-    // ---------------------------------------------------------------- expand + backup
-    // everything the backup needs is fetched in one round trip (all of it is valid memory in any case)
+    // ---------------------------------------------------------------- round trip 1: every independent load
     const int act = do_backup ? t.leaf_action[g] : -1;
     const int par = t.leaf_parent[g];
     const int nw = t.leaf_node[g];
     const int depth_b = t.leaf_depth[g];
     const float rew_g = do_backup ? reward[g] : 0.f, val_g = do_backup ? value[g] : 0.f;
     const int is_active = t.active[g];
+    const uint32_t move_index = (uint32_t)*t.move_index_dev;   // written by the root preparation of this move
+    const int pk0 = path[0];                     // first edge of the stored path (an edge of the root)
+    const int pk_raw = tid < A ? path[tid] : -1;
+    const int root_visit0 = t.root_visit[g];
+    const uint32_t ctr0 = t.choice_ctr[g];
+    const int nn0 = t.n_nodes[g];
+    const float* mask = t.root_mask + (size_t)g * A;
     float mk[STEP_EPT], sf[STEP_EPT];
-    int pk_mine = -1;
-    if (act >= 0) {
-        const int depth = depth_b;
-        const float* mask = t.root_mask + (size_t)g * A;
-        if (depth <= A && tid < depth) pk_mine = path[tid];
+    int nv_r[STEP_EPT], ch_r[STEP_EPT];
+    double pr_r[STEP_EPT], vs_r[STEP_EPT];
+#pragma unroll
+    for (int e = 0; e < STEP_EPT; e++) {
+        const int a = e * TPG + tid;
+        mk[e] = 0.f; sf[e] = 0.f; nv_r[e] = 0; ch_r[e] = -1; pr_r[e] = 0.0; vs_r[e] = 0.0;
+        if (a < A) {
+            mk[e] = mask[a];
+            if (do_backup) sf[e] = soft[(size_t)g * A + a];
+            if (do_select) {
+                nv_r[e] = t.edge_visit[rbase + a];
+                pr_r[e] = t.root_prior[(size_t)g * A + a];
+                vs_r[e] = t.edge_vsum[rbase + a];
+                ch_r[e] = (int)t.child[rbase + a];
+            }
+        }
+    }
+
+    // ---------------------------------------------------------------- expand + backup
+    // backup_value = reward.item() + discount * value.item()   (main.py:311), float64
+    const double bv = __dadd_rn((double)rew_g, __dmul_rn(p.discount, (double)val_g));
+    if (act >= 0 && v1) {
+        // policy_child *= valid_mask; /= sum (float32 pairwise)   self_play.py:210-214
 #pragma unroll
         for (int e = 0; e < STEP_EPT; e++) {
             const int a = e * TPG + tid;
-            mk[e] = 0.f; sf[e] = 0.f;
-            if (a < A) { mk[e] = mask[a]; sf[e] = soft[(size_t)g * A + a]; }
-        }
-        if (v1) {
-            // policy_child *= valid_mask; /= sum (float32 pairwise)   self_play.py:210-214
-#pragma unroll
-            for (int e = 0; e < STEP_EPT; e++) {
-                const int a = e * TPG + tid;
-                if (a < A) s_pri[sub][a] = masked_child_prior(sf[e], mk[e], a == A - 1, p.pass_epsilon);
-            }
+            if (a < A) sh.pri[sub][a] = masked_child_prior(sf[e], mk[e], a == A - 1, p.pass_epsilon);
         }
     }
     if (v1) {                                    // uniform for the block: p is a kernel parameter
         step_sync<TPG>();
-        if (tid == 0 && act >= 0) s_tot[sub] = np_pairwise_sum<float>(s_pri[sub], A);
+        if (tid == 0 && act >= 0) sh.tot[sub] = np_pairwise_sum<float>(sh.pri[sub], A);
         step_sync<TPG>();
     }
     if (act >= 0) {
         const int depth = depth_b;
         const size_t nbase = ((size_t)g * M + nw) * A;
-        const float* mask = t.root_mask + (size_t)g * A;
+        const int pk_mine = (depth <= A && tid < depth) ? pk_raw : -1;
 #pragma unroll
         for (int e = 0; e < STEP_EPT; e++) {
             const int a = e * TPG + tid;
             if (a < A) {
                 // prior_child = policy_child[a] if valid_mask[a] > 0 else 0   (the ROOT's mask, main.py:303)
                 float pr = mk[e] > 0.f ? sf[e] : 0.f;
-                if (v1) pr = renorm_child_prior(s_pri[sub][a], s_tot[sub], mk[e], a == A - 1, p.pass_epsilon, mask, A);
+                if (v1) pr = renorm_child_prior(sh.pri[sub][a], sh.tot[sub], mk[e], a == A - 1, p.pass_epsilon, mask, A);
                 t.prior[nbase + a] = pr;
                 t.edge_visit[nbase + a] = 0;
                 t.edge_vsum[nbase + a] = 0.0;
                 t.child[nbase + a] = (int16_t)-1;
             }
         }
-        // backup_value = reward.item() + discount * value.item()   (main.py:311), float64
-        const double bv = __dadd_rn((double)rew_g, __dmul_rn(p.discount, (double)val_g));
         // self_play.py:340-343: node i levels above the new leaf gets value * (-1)^i; edge d of the path holds the
         // statistics of the node at depth d + 1, i.e. i = depth - 1 - d, and the root has i = depth
         if (depth <= A) {
@@ -530,10 +665,20 @@ k_tree_step(mzgo_tree_t t, mzgo_search_params_t p, const float* __restrict__ sof
                     node = pn;
                 }
             }
-            t.root_visit[g] += 1;
+            t.root_visit[g] = root_visit0 + 1;
             t.root_vsum[g] = __dadd_rn(t.root_vsum[g], (v1 && (depth & 1)) ? -bv : bv);
             t.sims_done[g] += 1;
             t.depth_sum[g] += depth;
+        }
+        // the root level fetched above predates this backup: patch the one root edge on the path (the same
+        // float64 addition the backup thread performs on the same operands) and the new child link
+        const int a_first = pk0 & 511;           // stored paths always start with an edge of the root
+        const double sv0 = (v1 && ((depth - 1) & 1)) ? -bv : bv;
+#pragma unroll
+        for (int e = 0; e < STEP_EPT; e++) {
+            const int a = e * TPG + tid;
+            if (a == a_first) { nv_r[e] += 1; vs_r[e] = __dadd_rn(vs_r[e], sv0); }
+            if (par == 0 && a == act) ch_r[e] = nw;
         }
     }
     if (!do_select) return;
@@ -545,155 +690,73 @@ k_tree_step(mzgo_tree_t t, mzgo_search_params_t p, const float* __restrict__ sof
         return;
     }
     int node = 0, depth = 1;
-    int npar = t.root_visit[g];
-    const uint32_t ctr0 = t.choice_ctr[g];
-    const int nn0 = t.n_nodes[g];
+    int npar = root_visit0 + (act >= 0 ? 1 : 0);
     int sel_parent = -1, sel_action = -1;
-    while (true) {
-        const size_t base = ((size_t)g * M + node) * A;
+    const size_t stream_off = (size_t)g * stride;
+    {
+        // root level: float64 priors (main.py:276-282)
         double cp[STEP_EPT];
-        int nv[STEP_EPT];
-        uint32_t live = 0u;
-        // all loads of the level first, so that they are in flight together
-        double prd[STEP_EPT];
+        uint32_t pos = 0u;
+#pragma unroll
+        for (int e = 0; e < STEP_EPT; e++) {
+            cp[e] = __dmul_rn(p.c_puct, pr_r[e]);
+            if (e * TPG + tid < A && pr_r[e] > 0.0) pos |= 1u << e;
+        }
+        int oa = -1, on = 0, oc = -1;
+        const int rc = step_level<TPG>(sh, sub, tid, nv_r, cp, vs_r, ch_r, pos, npar, v1, ctr0, choice_stream, stream_off, p,
+                                       (uint32_t)g, move_index, &oa, &on, &oc);
+        if (rc == 0) { sel_parent = 0; sel_action = oa; }
+        else if (rc == 1) {
+            if (tid == 0) path[0] = oa;          // node 0 * 512 + action
+            node = oc; npar = on; depth = 2;
+        } else node = -1 - node;                 // terminal at the root
+    }
+    while (sel_action < 0 && node > 0) {
+        step_sync<TPG>();                        // shared scratch is reused by the next level
+        const size_t base = ((size_t)g * M + node) * A;
+        int nv[STEP_EPT], ch[STEP_EPT];
         float prf[STEP_EPT];
+        double vs[STEP_EPT], cp[STEP_EPT];
+        uint32_t pos = 0u;
+        // all loads of the level first, so that they are in flight together
 #pragma unroll
         for (int e = 0; e < STEP_EPT; e++) {
             const int a = e * TPG + tid;
-            nv[e] = 0; prd[e] = 0.0; prf[e] = 0.f;
+            nv[e] = 0; prf[e] = 0.f; vs[e] = 0.0; ch[e] = -1;
             if (a < A) {
                 nv[e] = t.edge_visit[base + a];
-                if (node == 0) prd[e] = t.root_prior[(size_t)g * A + a];
-                else prf[e] = t.prior[base + a];
+                prf[e] = t.prior[base + a];
+                vs[e] = t.edge_vsum[base + a];
+                ch[e] = (int)t.child[base + a];
             }
         }
 #pragma unroll
         for (int e = 0; e < STEP_EPT; e++) {
-            const int a = e * TPG + tid;
-            bool pos = false, opn = false;
-            cp[e] = 0.0;
-            if (a < A) {
-                if (node == 0) {
-                    pos = prd[e] > 0.0;
-                    cp[e] = __dmul_rn(p.c_puct, prd[e]);
-                } else {
-                    pos = prf[e] > 0.f;
-                    cp[e] = (double)__fmul_rn((float)p.c_puct, prf[e]);   // c*P rounds in float32 (NEP 50)
-                }
-                opn = pos && nv[e] == 0;
-            }
-            if (pos) live |= 1u << e;
-            const uint32_t b = __ballot_sync(FULL_MASK, opn);
-            if (lane == 0) s_open[sub][e * WPG + wig] = b;
+            cp[e] = (double)__fmul_rn((float)p.c_puct, prf[e]);   // c*P rounds in float32 (NEP 50)
+            if (prf[e] > 0.f) pos |= 1u << e;
         }
-        const uint32_t any_live = __ballot_sync(FULL_MASK, live != 0u);
-        if (lane == 0) s_live[sub][wig] = any_live;
-        step_sync<TPG>();
-        int n_open = 0;
-        uint32_t all_live = 0u;
-#pragma unroll
-        for (int w = 0; w < NW; w++) n_open += __popc(s_open[sub][w]);
-#pragma unroll
-        for (int w = 0; w < WPG; w++) all_live |= s_live[sub][w];
-        if (n_open > 0) {
-            // random.choice(unexpanded), main.py:322-325
-            const uint32_t ctr = ctr0;
-            const uint32_t r = choice_stream ? choice_stream[(size_t)g * stride + ctr]
-                                             : mzgo_rand_u32(p.seed, (uint32_t)g, 0x20000u + (uint32_t)t.move_index, ctr);
-            int k = (int)(r % (uint32_t)n_open);
-            int a_sel = -1;
-#pragma unroll
-            for (int w = 0; w < NW; w++) {
-                const uint32_t b = s_open[sub][w];
-                const int c = __popc(b);
-                if (a_sel < 0) {
-                    if (k < c) a_sel = w * 32 + (int)__fns(b, 0, k + 1);
-                    else k -= c;
-                }
-            }
-            sel_parent = node;
-            sel_action = a_sel;
-            if (tid == 0) t.choice_ctr[g] = ctr + 1u;
-            break;
-        }
-        if (!all_live) break;                    // nothing selectable: simulation dropped
-        // Q of every live edge, min-max normalisation set = prior > 0 (main.py:328-339)
-        double q[STEP_EPT];
-        double qmin = INFINITY, qmax = -INFINITY;
-#pragma unroll
-        for (int e = 0; e < STEP_EPT; e++) {
-            q[e] = 0.0;
-            if ((live & (1u << e)) && nv[e] > 0) q[e] = t.edge_vsum[base + e * TPG + tid];
-        }
-#pragma unroll
-        for (int e = 0; e < STEP_EPT; e++) {
-            if (live & (1u << e)) {
-                if (nv[e] > 0) q[e] = __ddiv_rn(q[e], (double)nv[e]);
-                qmin = fmin(qmin, q[e]);
-                qmax = fmax(qmax, q[e]);
-            }
-        }
-        qmin = warp_min_d(qmin);
-        qmax = warp_max_d(qmax);
-        if (WPG > 1) {
-            if (lane == 0) { s_min[sub][wig] = qmin; s_max[sub][wig] = qmax; }
-            step_sync<TPG>();
-#pragma unroll
-            for (int w = 0; w < WPG; w++) { qmin = fmin(qmin, s_min[sub][w]); qmax = fmax(qmax, s_max[sub][w]); }
-        }
-        const double sq = __dsqrt_rn((double)(v1 ? max(1, npar) : npar + 1));   // main.py:354 / self_play.py:297-300
-        const bool norm = qmax > qmin;
-        const double range = __dsub_rn(qmax, qmin);
-        double best = -INFINITY;
-        int best_a = -1, best_n = 0;
-#pragma unroll
-        for (int e = 0; e < STEP_EPT; e++) {
-            if (live & (1u << e)) {
-                const double qn = norm ? __ddiv_rn(__dsub_rn(q[e], qmin), range) : q[e];
-                const double u = __ddiv_rn(__dmul_rn(cp[e], sq), (double)(1 + nv[e]));
-                const double score = __dadd_rn(qn, u);
-                if (score > best) { best = score; best_a = e * TPG + tid; best_n = nv[e]; }   // e ascending = action ascending
-            }
-        }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            const double ob = __shfl_xor_sync(FULL_MASK, best, o);
-            const int oa = __shfl_xor_sync(FULL_MASK, best_a, o);
-            const int on = __shfl_xor_sync(FULL_MASK, best_n, o);
-            const bool take = (oa >= 0) && (best_a < 0 || ob > best || (ob == best && oa < best_a));
-            if (take) { best = ob; best_a = oa; best_n = on; }
-        }
-        if (WPG > 1) {
-            if (lane == 0) { s_best[sub][wig] = best; s_besta[sub][wig] = best_a; s_bestn[sub][wig] = best_n; }
-            step_sync<TPG>();
-            best = s_best[sub][0]; best_a = s_besta[sub][0]; best_n = s_bestn[sub][0];
-#pragma unroll
-            for (int w = 1; w < WPG; w++) {
-                const double ob = s_best[sub][w];
-                const int oa = s_besta[sub][w], on = s_bestn[sub][w];
-                const bool take = (oa >= 0) && (best_a < 0 || ob > best || (ob == best && oa < best_a));
-                if (take) { best = ob; best_a = oa; best_n = on; }
-            }
-        }
-        if (best_a < 0) break;                   // only NaN / -inf scores: the reference falls out of the loop too
-        if (tid == 0 && depth <= A) path[depth - 1] = node * 512 + best_a;
-        node = (int)t.child[base + best_a];
-        npar = best_n;
-        depth++;
-        step_sync<TPG>();                        // shared scratch is reused by the next level
+        int oa = -1, on = 0, oc = -1;
+        const int rc = step_level<TPG>(sh, sub, tid, nv, cp, vs, ch, pos, npar, v1, ctr0, choice_stream, stream_off, p,
+                                       (uint32_t)g, move_index, &oa, &on, &oc);
+        if (rc == 0) { sel_parent = node; sel_action = oa; }
+        else if (rc == 1) {
+            if (tid == 0 && depth <= A) path[depth - 1] = node * 512 + oa;
+            node = oc; npar = on; depth++;
+        } else node = -1 - node;                 // terminal below the root
     }
     if (tid == 0) {
         const int nn = act >= 0 ? nw + 1 : nn0;
         if (sel_action < 0 && v1) {
             // terminal leaf: backpropagate(path, 0) -- a visit for every node on the path (self_play.py:188-190)
-            int nd = node;
+            int nd = node < 0 ? -1 - node : node;
             while (nd != 0) {
                 const int pk = t.parent[(size_t)g * M + nd];
                 t.edge_visit[((size_t)g * M + (pk >> 9)) * A + (pk & 511)] += 1;
                 nd = pk >> 9;
             }
-            t.root_visit[g] += 1;
+            t.root_visit[g] = npar_root_after(root_visit0, act) + 1;
         }
+        if (sel_action >= 0) t.choice_ctr[g] = ctr0 + 1u;
         if (sel_action >= 0 && nn >= M) sel_action = -1;   // arena full: drop (cannot happen when M > simulations)
         if (sel_action >= 0 && depth <= A) path[depth - 1] = sel_parent * 512 + sel_action;
         t.leaf_parent[g] = sel_action >= 0 ? sel_parent : -1;
@@ -837,7 +900,7 @@ static int check_tree(const mzgo_tree_t* t) {
     MZGO_CHECK_ARG(t->root_prior && t->root_mask && t->prior && t->edge_visit && t->edge_vsum && t->child &&
                        t->parent && t->root_visit && t->root_vsum && t->n_nodes && t->leaf_parent &&
                        t->leaf_action && t->leaf_node && t->leaf_depth && t->leaf_in_slot && t->leaf_out_slot && t->choice_ctr && t->depth_sum &&
-                       t->sims_done && t->dropped && t->active,
+                       t->sims_done && t->dropped && t->active && t->move_index_dev,
                    "tree has a NULL array");
     return 0;
 }

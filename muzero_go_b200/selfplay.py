@@ -6,6 +6,8 @@ MCTS.run + visit-count action + env.step + trajectory append, i.e. the loop body
 move cap (main.py:696-706) and immediate restart of finished games.  Nothing synchronises with the host
 until results are read.
 """
+import dataclasses
+
 import numpy as np
 import torch
 
@@ -20,7 +22,7 @@ COUNTER_NAMES = ["moves", "simulations", "games_finished", "dropped_simulations"
 class SelfPlayEngine:
     def __init__(self, net, board_size, num_games, num_simulations, search=None, max_game_moves=None,
                  temperature=0.0, temperature_moves=0, komi=0.0, restart_finished=True, traj_capacity=8,
-                 device=None):
+                 device=None, share_search_buffers_with=None):
         _lib.require_device()
         self.net = net
         self.n = int(board_size)
@@ -38,18 +40,28 @@ class SelfPlayEngine:
         G, A, T = self.G, self.A, self.T
 
         self.boards = GoBoards(G, self.n, dev).reset()
-        self.tree = Tree(G, A, self.M, dev)
-        self.arena = net.new_arena(G * self.M)
 
         def z(shape, dtype):
             return torch.zeros(shape, dtype=dtype, device=dev)
-        self.root_policy = z((G, A), torch.float32)
-        self.root_value_net = z((G,), torch.float32)
-        self.leaf_policy = z((G, A), torch.float32)
-        self.leaf_reward = z((G,), torch.float32)
-        self.leaf_value = z((G,), torch.float32)
-        self.in_slot = z((G,), torch.int32)
-        self.out_slot = z((G,), torch.int32)
+        other = share_search_buffers_with
+        if other is None:
+            self.tree = Tree(G, A, self.M, dev)
+            self.arena = net.new_arena(G * self.M)
+            self.root_policy = z((G, A), torch.float32)
+            self.root_value_net = z((G,), torch.float32)
+            self.leaf_policy = z((G, A), torch.float32)
+            self.leaf_reward = z((G,), torch.float32)
+            self.leaf_value = z((G,), torch.float32)
+            self.in_slot = z((G,), torch.int32)
+            self.out_slot = z((G,), torch.int32)
+        else:
+            # A search only lives for one move: engines that run their moves one after the other on one stream
+            # (the waves of a WaveGroup) can share the trees, the latent arena and the per-simulation scratch.
+            if (other.G, other.S, other.n, other.net) != (self.G, self.S, self.n, net) or other.device != dev:
+                raise ValueError("engines sharing search buffers must have the same shape, network and device")
+            for name in ("tree", "arena", "root_policy", "root_value_net", "leaf_policy", "leaf_reward", "leaf_value",
+                         "in_slot", "out_slot"):
+                setattr(self, name, getattr(other, name))
         self.action = z((G,), torch.int32)
         self.move_count = z((G,), torch.int32)
         self.pass_streak = z((G,), torch.int32)
@@ -103,3 +115,42 @@ class SelfPlayEngine:
         return {"boards": self.traj_boards[lo:hi], "action": self.traj_action[lo:hi],
                 "policy": self.traj_policy[lo:hi], "root_value": self.traj_root_value[lo:hi],
                 "reward": self.traj_reward[lo:hi], "done": self.traj_done[lo:hi], "winner": self.traj_winner[lo:hi]}
+
+
+class WaveGroup:
+    """`waves` engines of num_games / waves games each that take turns on ONE set of search buffers: every
+    call of run(k) plays k moves of every game, wave after wave.  This is how a game count whose latent arena
+    would not fit the HBM runs on one GPU (19x19, 800 simulations: 2048 games need 177 GB of latents at once,
+    two waves of 1024 need 89 GB); throughput is unchanged because the games are independent and a wave of
+    1024 leaves already fills the persistent network kernel (6.9 leaves per SM)."""
+
+    def __init__(self, net, board_size, num_games, num_simulations, waves=1, search=None, **kw):
+        if num_games % waves:
+            raise ValueError("num_games must be a multiple of waves")
+        per = num_games // waves
+        self.engines = []
+        for w in range(waves):
+            cfg = search
+            if search is not None and w > 0:       # independent RNG streams per wave (games are keyed by local index)
+                cfg = dataclasses.replace(search, seed=search.seed + 7919 * w)
+            self.engines.append(SelfPlayEngine(net, board_size, per, num_simulations, search=cfg,
+                                               share_search_buffers_with=self.engines[0] if w else None, **kw))
+        e0 = self.engines[0]
+        self.G, self.S, self.A, self.n, self.M = num_games, e0.S, e0.A, e0.n, e0.M
+        self.arena, self.tree, self.device = e0.arena, e0.tree, e0.device
+
+    def run(self, num_moves, traj_offset=0):
+        for m in range(int(num_moves)):
+            for e in self.engines:
+                e.run(1, traj_offset=traj_offset + m)
+
+    def read_counters(self):
+        tot = dict.fromkeys(COUNTER_NAMES, 0)
+        for e in self.engines:
+            for k, v in e.read_counters().items():
+                tot[k] += v
+        return tot
+
+    def trajectory_rows(self, lo, hi):
+        rows = [e.trajectory_rows(lo, hi) for e in self.engines]
+        return {k: torch.cat([r[k] for r in rows], dim=1) for k in rows[0]}

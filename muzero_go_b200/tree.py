@@ -85,6 +85,7 @@ class Tree:
         self.sims_done = z((G,), torch.int32)
         self.dropped = z((G,), torch.int32)
         self.active = torch.ones((G,), dtype=torch.uint8, device=dev)
+        self.move_index_dev = z((1,), torch.int32)
         self.desc = self._make_desc()
 
     def _make_desc(self):

@@ -168,3 +168,28 @@ def test_engine_equals_stepwise_api():
         assert torch.equal(action, eng.traj_action[t]), t
         assert torch.equal(policy, eng.traj_policy[t])
         boards.step(action)
+
+
+def test_wave_group_equals_separate_engines():
+    """Waves share the trees, the latent arena and the scratch; because a search only lives for one move each
+    wave must play exactly what a stand-alone engine with the same seed plays (and the replayed search-loop
+    graph must give what plain launches give: the stand-alone engines below run with the same code path)."""
+    import dataclasses
+    import muzero_go_b200 as mz
+    n, c, G, S, T = 5, 16, 12, 12, 5
+    _, net = make_net(n, c, 3)
+    cfg = mz.SearchConfig(seed=77)
+    group = mz.WaveGroup(net, n, G, S, waves=3, search=cfg, traj_capacity=T)
+    group.run(T)
+    torch.cuda.synchronize()
+    rows = group.trajectory_rows(0, T)
+    assert tuple(rows["action"].shape) == (T, G) and group.read_counters()["moves"] == G * T
+    assert group.engines[1].arena.data_ptr() == group.engines[0].arena.data_ptr()
+    for w in range(3):
+        solo = mz.SelfPlayEngine(net, n, G // 3, S, search=dataclasses.replace(cfg, seed=77 + 7919 * w), traj_capacity=T)
+        solo.run(T)
+        torch.cuda.synchronize()
+        lo, hi = w * (G // 3), (w + 1) * (G // 3)
+        assert torch.equal(rows["action"][:, lo:hi], solo.traj_action)
+        assert torch.equal(rows["policy"][:, lo:hi], solo.traj_policy)
+        assert torch.equal(rows["boards"][:, lo:hi], solo.traj_boards)
