@@ -270,15 +270,28 @@ def run_ours(args, wl):
     args_rec = (d.net, _lib.ptr(eng.arena), _lib.ptr(eng.tree.leaf_in_slot), _lib.ptr(eng.tree.leaf_action),
                 _lib.ptr(eng.tree.leaf_out_slot), _lib.ptr(eng.leaf_reward), _lib.ptr(eng.leaf_value),
                 _lib.ptr(eng.leaf_policy), 1, GW, _lib.stream_ptr())
-    for _ in range(3):
-        _lib.check(lib.mzgo_net_recurrent(*args_rec))
-    torch.cuda.synchronize()
-    k0.record()
-    for _ in range(reps):
-        _lib.check(lib.mzgo_net_recurrent(*args_rec))
-    k1.record()
-    torch.cuda.synchronize()
-    kern_ms = k0.elapsed_time(k1) / reps
+    # single kernels are timed as CUDA-graph replays of `reps` launches, so that no host launch overhead sits
+    # between the events (a Python-driven loop of 10 us kernels measures the host, not the GPU)
+    side = torch.cuda.Stream()
+
+    def graph_time(fn, count, replays=3):
+        fn(_lib.stream_ptr())                                # warm (function attributes, tables)
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.stream(side):
+            with torch.cuda.graph(g, stream=side):
+                for _ in range(count):
+                    fn(_lib.stream_ptr())
+        g.replay()
+        torch.cuda.synchronize()
+        k0.record()
+        for _ in range(replays):
+            g.replay()
+        k1.record()
+        torch.cuda.synchronize()
+        return k0.elapsed_time(k1) / (replays * count)
+
+    kern_ms = graph_time(lambda st: _lib.check(lib.mzgo_net_recurrent(*args_rec[:-1], st)), reps)
     live = int((eng.tree.leaf_action >= 0).sum())
     peaks = measured_peaks()
     achieved = live * flops_recurrent(n) / (kern_ms * 1e-3) / 1e12
@@ -290,18 +303,23 @@ def run_ours(args, wl):
 
     tree_reps = min(16, max(1, S // 4))
     d_part = eng.descriptor()
-    d_part.num_simulations = S - tree_reps - 1
+    d_part.num_simulations = S - tree_reps - 2
     p_struct = eng.search.to_struct()
     eng.tree.reset_roots(eng.search, eng.root_policy, eng.boards, n, noise=None, move_index=0)
     _lib.check(lib.mzgo_search_run(d_part, None, 0, _lib.stream_ptr()))
     step_args = (eng.tree.desc, p_struct, _lib.ptr(eng.leaf_policy), _lib.ptr(eng.leaf_reward), _lib.ptr(eng.leaf_value),
                  None, 0)
-    _lib.check(lib.mzgo_tree_step(*step_args, 0, 1, _lib.stream_ptr()))
+    _lib.check(lib.mzgo_tree_step(*step_args, 1, 1, _lib.stream_ptr()))    # warm
+    torch.cuda.synchronize()
+    g_tree = torch.cuda.CUDAGraph()
+    with torch.cuda.stream(side):
+        with torch.cuda.graph(g_tree, stream=side):
+            for _ in range(tree_reps):
+                _lib.check(lib.mzgo_tree_step(*step_args, 1, 1, _lib.stream_ptr()))
     torch.cuda.synchronize()
     dsum0, sims0 = int(eng.tree.depth_sum.sum()), int(eng.tree.sims_done.sum())
     k0.record()
-    for _ in range(tree_reps):
-        _lib.check(lib.mzgo_tree_step(*step_args, 1, 1, _lib.stream_ptr()))
+    g_tree.replay()                                          # one replay: every launch expands a node
     k1.record()
     torch.cuda.synchronize()
     tree_ms = k0.elapsed_time(k1) / tree_reps
@@ -321,9 +339,14 @@ def run_ours(args, wl):
     for i in range(2):
         rb.playout(acts[i], want_actions=False)
     torch.cuda.synchronize()
+    g_rules = torch.cuda.CUDAGraph()
+    with torch.cuda.stream(side):
+        with torch.cuda.graph(g_rules, stream=side):
+            for i in range(rules_reps):
+                rb.playout(acts[2 + i], want_actions=False)
+    torch.cuda.synchronize()
     k0.record()
-    for i in range(rules_reps):
-        rb.playout(acts[2 + i], want_actions=False)
+    g_rules.replay()
     k1.record()
     torch.cuda.synchronize()
     rules_ms = k0.elapsed_time(k1) / rules_reps

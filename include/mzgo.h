@@ -307,6 +307,13 @@ int mzgo_selfplay_run(const mzgo_selfplay_t* sp, int num_moves, int traj_offset,
  * select -> recurrent inference -> expand/backup on sp->tree.  choice_stream as in mzgo_tree_select. */
 int mzgo_search_run(const mzgo_selfplay_t* sp, const uint32_t* choice_stream, int stride, void* stream);
 
+/* Test / profiling hooks.  mzgo_debug_fastdiv_check: operand pairs on which the tree kernels' 5-operation
+ * correctly rounded division differs from the generic IEEE division (must be 0; synchronous).
+ * mzgo_debug_tc_trace: when buf != NULL every tensor-core conv launch stamps its role timeline into
+ * buf[grid][32] (uint64 globaltimer values, tools/tc_trace.py). */
+long long mzgo_debug_fastdiv_check(unsigned long long seed, int blocks, long long per_thread);
+int mzgo_debug_tc_trace(void* buf /*device*/);
+
 /* Number of searches mzgo_selfplay_run served by replaying its captured CUDA graph of the search loop
  * (the graph is captured on the second move of an engine; MZGO_NO_GRAPH=1 in the environment disables it). */
 long long mzgo_graph_replays(void);

@@ -67,6 +67,8 @@ _PROTOS = {
     "mzgo_device_ok": (i32, []),
     "mzgo_launch_count": (i64, [i32]),
     "mzgo_graph_replays": (C.c_longlong, []),
+    "mzgo_debug_fastdiv_check": (C.c_longlong, [C.c_ulonglong, i32, C.c_longlong]),
+    "mzgo_debug_tc_trace": (i32, [vp]),
     "mzgo_sizeof": (i64, [i32]),
     "mzgo_rules_reset": (i32, [vp, i32, i32, vp]),
     "mzgo_rules_step": (i32, [vp, vp, vp, i32, i32, vp]),

@@ -84,6 +84,29 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
                      smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
+// L2 eviction priorities.  A simulation streams 2 x 108 KB of latents per leaf through the L2 exactly once
+// (the next reader of a child latent is a later simulation, after > 200 MB of other traffic), while the tree
+// kernels re-read the same root rows every simulation: latents go through with evict_first so that the
+// trees' working set (about 20 MB per 1024 games) and the weights stay resident in the 126 MB L2.
+__device__ __forceinline__ uint64_t l2_policy_evict_first() {
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+__device__ __forceinline__ uint64_t l2_policy_evict_last() {
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+__device__ __forceinline__ void bulk_g2s_hint(void* dst, const void* src, uint32_t bytes, uint64_t* bar, uint64_t policy) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(
+            smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)), "l"(policy) : "memory");
+}
+__device__ __forceinline__ void st_global_v4_hint(void* ptr, uint4 v, uint64_t policy) {
+    asm volatile("st.global.L2::cache_hint.v4.b32 [%0], {%1, %2, %3, %4}, %5;" ::"l"(ptr), "r"(v.x), "r"(v.y), "r"(v.z),
+                 "r"(v.w), "l"(policy) : "memory");
+}
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
@@ -258,6 +281,7 @@ __device__ __forceinline__ void tc_epilogue_role(const TcArgs& a, const TcCtx& c
         asm volatile("bar.sync 1, 256;" ::: "memory");
     }
     uint32_t tile_ctr = 0, it = 0;
+    const uint64_t pol_stream = l2_policy_evict_first();
     for (int base = tc_items_lo(a); base < items_hi; base += images) {
         const int cnt = min(images, items_hi - base), NT = cnt * tpi;
         const uint32_t live = tc_live_mask(a, base, cnt, lane);
@@ -325,7 +349,8 @@ __device__ __forceinline__ void tc_epilogue_role(const TcArgs& a, const TcCtx& c
                     w.z = pack_bf16(x[4], x[5]);
                     w.w = pack_bf16(x[6], x[7]);
                     if (!valid) w = make_uint4(0u, 0u, 0u, 0u);      // padding positions stay zero for the next conv
-                    dst[(size_t)k * ps] = w;
+                    if (MODE == MODE_PLAIN) dst[(size_t)k * ps] = w;          // read again by the next layer
+                    else st_global_v4_hint(dst + (size_t)k * ps, w, pol_stream);
                 }
             }
             if (MODE != MODE_PLAIN) {
@@ -566,6 +591,7 @@ k_tc_conv(const __grid_constant__ TcArgs a) {
     if (warp == 0) {
         // ===================================================== TMA producer (lane 0 issues, the warp stays converged)
         uint32_t it = 0, s = 0, bph = 0;
+        const uint64_t pol_stream = l2_policy_evict_first(), pol_keep = l2_policy_evict_last();
         const int items_hi = tc_items_hi(a);
         for (int base = tc_items_lo(a); base < items_hi; base += images) {
             const int cnt = min(images, items_hi - base);
@@ -591,15 +617,16 @@ k_tc_conv(const __grid_constant__ TcArgs a) {
                     const int item = base + lane;
                     const int slot = a.in_slot ? a.in_slot[item] : item;
                     const uint8_t* src = reinterpret_cast<const uint8_t*>(a.in) + (size_t)slot * slab_bytes + (size_t)h * half_bytes;
-                    bulk_g2s(sA + (size_t)lane * slab_bytes + (size_t)h * half_bytes, src, half_bytes, a_full + h);
+                    if (MODE == MODE_DYN) bulk_g2s_hint(sA + (size_t)lane * slab_bytes + (size_t)h * half_bytes, src, half_bytes, a_full + h, pol_stream);
+                    else bulk_g2s(sA + (size_t)lane * slab_bytes + (size_t)h * half_bytes, src, half_bytes, a_full + h);
                 }
                 for (int tap = 0; tap < 9; tap++) {
                     mbar_wait(b_empty + s, bph ^ 1);
                     if (lane == 0) {
                         mbar_expect_tx(b_full + s, STAGE_BYTES);
-                        bulk_g2s(sB + s * STAGE_BYTES,
-                                 reinterpret_cast<const uint8_t*>(a.wB) + (size_t)(h * 9 + tap) * STAGE_BYTES, STAGE_BYTES,
-                                 b_full + s);
+                        bulk_g2s_hint(sB + s * STAGE_BYTES,
+                                      reinterpret_cast<const uint8_t*>(a.wB) + (size_t)(h * 9 + tap) * STAGE_BYTES, STAGE_BYTES,
+                                      b_full + s, pol_keep);
                     }
                     if (++s == (uint32_t)a.stages) { s = 0; bph ^= 1; }
                 }

@@ -425,6 +425,28 @@ k_tree_expand_backup(mzgo_tree_t t, mzgo_search_params_t p, const float* __restr
 constexpr int STEP_THREADS = 128;
 constexpr int STEP_EPT = 3;   // edges per thread: A <= 3 * TPG
 
+// ---- correctly rounded float64 division with a known reciprocal (Markstein 1990; Muller et al., Handbook of
+// Floating-Point Arithmetic, 2nd ed., section 4.7): with y = RN(1/b), q0 = RN(a*y) is within 1.5 ulp of a/b,
+// one FMA correction makes it faithful, and a second correction q2 = RN(q1 + (a - b*q1)*y) IS RN(a/b) whenever
+// nothing under- or overflows (here: |a| in [1e-60, 1e6], b in [1e-17, 1e3]).  Five dependent FP64 operations
+// and no branches instead of the ~20-instruction generic division; the PUCT score needs two per edge.
+// tests/test_tree_gpu.py::test_fast_division_is_correctly_rounded compares it with __ddiv_rn on 2^27 operands.
+__device__ __forceinline__ double div_rn_with_rcp(double a, double b, double y) {
+    double q = __dmul_rn(a, y);
+    double r = __fma_rn(-b, q, a);
+    q = __fma_rn(r, y, q);
+    r = __fma_rn(-b, q, a);
+    return __fma_rn(r, y, q);
+}
+// RN(1/d) for d = 0..RCP_TABLE-1 (filled by the host: 1.0 / d in IEEE double is correctly rounded)
+constexpr int RCP_TABLE = 1024;
+__device__ double g_rcp_table[RCP_TABLE];
+
+__device__ __forceinline__ double div_by_count(double a, int d) {
+    if (d < RCP_TABLE) return div_rn_with_rcp(a, (double)d, __ldg(&g_rcp_table[d]));
+    return __ddiv_rn(a, (double)d);
+}
+
 __device__ __forceinline__ int npar_root_after(int root_visit0, int act) { return root_visit0 + (act >= 0 ? 1 : 0); }
 
 template <int TPG>
@@ -495,7 +517,7 @@ __device__ __forceinline__ int step_level(StepShared<TPG>& sh, int sub, int tid,
     for (int e = 0; e < STEP_EPT; e++) {
         q[e] = 0.0;
         if ((pos >> e) & 1u) {
-            if (nv[e] > 0) q[e] = __ddiv_rn(vs[e], (double)nv[e]);
+            if (nv[e] > 0) q[e] = (fabs(vs[e]) < 1e6) ? div_by_count(vs[e], nv[e]) : __ddiv_rn(vs[e], (double)nv[e]);
             qmin = fmin(qmin, q[e]);
             qmax = fmax(qmax, q[e]);
         }
@@ -511,13 +533,18 @@ __device__ __forceinline__ int step_level(StepShared<TPG>& sh, int sub, int tid,
     const double sq = __dsqrt_rn((double)(v1 ? max(1, npar) : npar + 1));   // main.py:354 / self_play.py:297-300
     const bool norm = qmax > qmin;
     const double range = __dsub_rn(qmax, qmin);
+    // 1/range once per level; a range outside the proven window of div_rn_with_rcp takes the generic division
+    const bool fast = norm && range > 1e-17 && range < 1e3 && fabs(qmin) < 1e6 && fabs(qmax) < 1e6;
+    const double rrange = fast ? __drcp_rn(range) : 0.0;
     double best = -INFINITY;
     int best_a = -1, best_n = 0, best_c = -1;
 #pragma unroll
     for (int e = 0; e < STEP_EPT; e++) {
         if ((pos >> e) & 1u) {
-            const double qn = norm ? __ddiv_rn(__dsub_rn(q[e], qmin), range) : q[e];
-            const double u = __ddiv_rn(__dmul_rn(cp[e], sq), (double)(1 + nv[e]));
+            const double dq = __dsub_rn(q[e], qmin);
+            const double qn = norm ? (fast ? div_rn_with_rcp(dq, range, rrange) : __ddiv_rn(dq, range)) : q[e];
+            const double num = __dmul_rn(cp[e], sq);
+            const double u = (num < 1e6) ? div_by_count(num, 1 + nv[e]) : __ddiv_rn(num, (double)(1 + nv[e]));
             const double score = __dadd_rn(qn, u);
             if (score > best) { best = score; best_a = e * TPG + tid; best_n = nv[e]; best_c = ch[e]; }   // e ascending = action ascending
         }
@@ -551,7 +578,7 @@ __device__ __forceinline__ int step_level(StepShared<TPG>& sh, int sub, int tid,
 }
 
 template <int TPG>
-__global__ void __launch_bounds__(STEP_THREADS, 6)
+__global__ void __launch_bounds__(STEP_THREADS, 8)
 k_tree_step(mzgo_tree_t t, mzgo_search_params_t p, const float* __restrict__ soft, const float* __restrict__ reward,
             const float* __restrict__ value, const uint32_t* __restrict__ choice_stream, int stride, int do_backup,
             int do_select) {
@@ -693,62 +720,51 @@ k_tree_step(mzgo_tree_t t, mzgo_search_params_t p, const float* __restrict__ sof
     int npar = root_visit0 + (act >= 0 ? 1 : 0);
     int sel_parent = -1, sel_action = -1;
     const size_t stream_off = (size_t)g * stride;
-    {
-        // root level: float64 priors (main.py:276-282)
-        double cp[STEP_EPT];
-        uint32_t pos = 0u;
+    // The level loop works on ONE set of register arrays (nv_r / vs_r / ch_r / cp): they hold the prefetched and
+    // patched root level on entry and are reloaded for every level below, so there is a single copy of the
+    // level code (the kernel is instruction-cache sensitive).
+    double cp[STEP_EPT];
+    uint32_t pos = 0u;
 #pragma unroll
-        for (int e = 0; e < STEP_EPT; e++) {
-            cp[e] = __dmul_rn(p.c_puct, pr_r[e]);
-            if (e * TPG + tid < A && pr_r[e] > 0.0) pos |= 1u << e;
-        }
+    for (int e = 0; e < STEP_EPT; e++) {
+        cp[e] = __dmul_rn(p.c_puct, pr_r[e]);    // root: float64 priors (main.py:276-282)
+        if (e * TPG + tid < A && pr_r[e] > 0.0) pos |= 1u << e;
+    }
+    while (true) {
         int oa = -1, on = 0, oc = -1;
         const int rc = step_level<TPG>(sh, sub, tid, nv_r, cp, vs_r, ch_r, pos, npar, v1, ctr0, choice_stream, stream_off, p,
                                        (uint32_t)g, move_index, &oa, &on, &oc);
-        if (rc == 0) { sel_parent = 0; sel_action = oa; }
-        else if (rc == 1) {
-            if (tid == 0) path[0] = oa;          // node 0 * 512 + action
-            node = oc; npar = on; depth = 2;
-        } else node = -1 - node;                 // terminal at the root
-    }
-    while (sel_action < 0 && node > 0) {
+        if (rc == 0) { sel_parent = node; sel_action = oa; break; }
+        if (rc == 2 || oc <= 0) break;           // terminal leaf / dropped simulation (node keeps the leaf)
+        if (tid == 0 && depth <= A) path[depth - 1] = node * 512 + oa;
+        node = oc; npar = on; depth++;
         step_sync<TPG>();                        // shared scratch is reused by the next level
         const size_t base = ((size_t)g * M + node) * A;
-        int nv[STEP_EPT], ch[STEP_EPT];
         float prf[STEP_EPT];
-        double vs[STEP_EPT], cp[STEP_EPT];
-        uint32_t pos = 0u;
         // all loads of the level first, so that they are in flight together
 #pragma unroll
         for (int e = 0; e < STEP_EPT; e++) {
             const int a = e * TPG + tid;
-            nv[e] = 0; prf[e] = 0.f; vs[e] = 0.0; ch[e] = -1;
+            nv_r[e] = 0; prf[e] = 0.f; vs_r[e] = 0.0; ch_r[e] = -1;
             if (a < A) {
-                nv[e] = t.edge_visit[base + a];
+                nv_r[e] = t.edge_visit[base + a];
                 prf[e] = t.prior[base + a];
-                vs[e] = t.edge_vsum[base + a];
-                ch[e] = (int)t.child[base + a];
+                vs_r[e] = t.edge_vsum[base + a];
+                ch_r[e] = (int)t.child[base + a];
             }
         }
+        pos = 0u;
 #pragma unroll
         for (int e = 0; e < STEP_EPT; e++) {
             cp[e] = (double)__fmul_rn((float)p.c_puct, prf[e]);   // c*P rounds in float32 (NEP 50)
             if (prf[e] > 0.f) pos |= 1u << e;
         }
-        int oa = -1, on = 0, oc = -1;
-        const int rc = step_level<TPG>(sh, sub, tid, nv, cp, vs, ch, pos, npar, v1, ctr0, choice_stream, stream_off, p,
-                                       (uint32_t)g, move_index, &oa, &on, &oc);
-        if (rc == 0) { sel_parent = node; sel_action = oa; }
-        else if (rc == 1) {
-            if (tid == 0 && depth <= A) path[depth - 1] = node * 512 + oa;
-            node = oc; npar = on; depth++;
-        } else node = -1 - node;                 // terminal below the root
     }
     if (tid == 0) {
         const int nn = act >= 0 ? nw + 1 : nn0;
         if (sel_action < 0 && v1) {
             // terminal leaf: backpropagate(path, 0) -- a visit for every node on the path (self_play.py:188-190)
-            int nd = node < 0 ? -1 - node : node;
+            int nd = node;
             while (nd != 0) {
                 const int pk = t.parent[(size_t)g * M + nd];
                 t.edge_visit[((size_t)g * M + (pk >> 9)) * A + (pk & 511)] += 1;
@@ -892,6 +908,59 @@ k_tree_choose_action(mzgo_tree_t t, mzgo_search_params_t p, float temperature, c
 
 extern void mzgo_count_launch();
 
+// compares div_rn_with_rcp / div_by_count with the generic IEEE division on pseudo-random operands
+__global__ void k_fastdiv_check(unsigned long long seed, long long per_thread, unsigned long long* mismatches) {
+    const unsigned long long tid = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x;
+    unsigned long long bad = 0;
+    for (long long i = 0; i < per_thread; i++) {
+        uint32_t c[4] = {(uint32_t)i, (uint32_t)(i >> 32), (uint32_t)tid, (uint32_t)(tid >> 32)};
+        philox4x32_10(c, (uint32_t)seed, (uint32_t)(seed >> 32));
+        // numerator: random mantissa, exponent in [-200, 19] (about 1e-60 .. 1e6), random sign
+        const unsigned long long mant = (((unsigned long long)c[0] << 32) | c[1]) & 0x000FFFFFFFFFFFFFull;
+        const int ea = (int)(c[2] % 220u) - 200;
+        double a = __longlong_as_double((long long)(((unsigned long long)(1023 + ea) << 52) | mant));
+        if (c[3] & 1u) a = -a;
+        // (1) small integer divisors
+        const int d = 1 + (int)((c[3] >> 1) % (uint32_t)(RCP_TABLE - 1));
+        if (__double_as_longlong(div_by_count(a, d)) != __double_as_longlong(__ddiv_rn(a, (double)d))) bad++;
+        // (2) arbitrary divisors in [1e-17, 1e3) with a correctly rounded reciprocal
+        uint32_t c2[4] = {(uint32_t)i, 0x9e3779b9u, (uint32_t)tid, 0x7f4a7c15u};
+        philox4x32_10(c2, (uint32_t)seed, (uint32_t)(seed >> 32));
+        const unsigned long long mb = (((unsigned long long)c2[0] << 32) | c2[1]) & 0x000FFFFFFFFFFFFFull;
+        const int eb = (int)(c2[2] % 66u) - 56;                    // 2^-56 .. 2^9
+        const double b = __longlong_as_double((long long)(((unsigned long long)(1023 + eb) << 52) | mb));
+        if (__double_as_longlong(div_rn_with_rcp(a, b, __drcp_rn(b))) != __double_as_longlong(__ddiv_rn(a, b))) bad++;
+    }
+    if (bad) atomicAdd(mismatches, bad);
+}
+
+static int ensure_rcp_table() {
+    static thread_local int done_for = -1;
+    int dev = 0;
+    MZGO_CUDA(cudaGetDevice(&dev));
+    if (done_for == dev) return MZGO_OK;
+    static double host[RCP_TABLE];
+    host[0] = 0.0;
+    for (int d = 1; d < RCP_TABLE; d++) host[d] = 1.0 / (double)d;
+    MZGO_CUDA(cudaMemcpyToSymbol(g_rcp_table, host, sizeof(host)));
+    done_for = dev;
+    return MZGO_OK;
+}
+
+// Test hook: number of operand pairs (of 2 * blocks * 256 * per_thread) on which the fast division differs
+// from __ddiv_rn.  Synchronous.
+extern "C" long long mzgo_debug_fastdiv_check(unsigned long long seed, int blocks, long long per_thread) {
+    if (ensure_rcp_table()) return -1;
+    unsigned long long* dev_bad = nullptr;
+    if (cudaMalloc(&dev_bad, 8) != cudaSuccess) return -1;
+    cudaMemset(dev_bad, 0, 8);
+    k_fastdiv_check<<<blocks, 256>>>(seed, per_thread, dev_bad);
+    unsigned long long bad = 0;
+    const cudaError_t e = cudaMemcpy(&bad, dev_bad, 8, cudaMemcpyDeviceToHost);
+    cudaFree(dev_bad);
+    return e == cudaSuccess ? (long long)bad : -1;
+}
+
 static int check_tree(const mzgo_tree_t* t) {
     MZGO_CHECK_ARG(t != nullptr, "tree is NULL");
     MZGO_CHECK_ARG(t->G >= 0, "tree.G < 0");
@@ -949,6 +1018,7 @@ extern "C" int mzgo_tree_step(const mzgo_tree_t* tree, const mzgo_search_params_
                               int do_backup, int do_select, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
     if (int e = check_tree(tree)) return e;
+    if (int e = ensure_rcp_table()) return e;
     MZGO_CHECK_ARG(p && (!do_backup || (soft && reward && value)), "NULL argument");
     if (tree->G == 0) return MZGO_OK;
     if (tree->A <= STEP_EPT * 32)

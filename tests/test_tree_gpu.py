@@ -152,3 +152,13 @@ def test_idle_trees_are_left_alone():
     # Dirichlet noise: the mixed-in part sums to epsilon and differs between games
     assert np.all(rp[[0, 2, 3]] >= 0)
     assert not np.allclose(rp[0], rp[2])
+
+
+def test_fast_division_is_correctly_rounded():
+    """The tree-step kernel divides with a known reciprocal (five FP64 operations, Markstein's correction);
+    bit-exact visit counts need it to equal the IEEE division everywhere: 2^27 operand pairs, two divisor kinds."""
+    from muzero_go_b200 import _lib
+    lib = _lib.load()
+    _lib.require_device()
+    for seed in (1, 2):
+        assert lib.mzgo_debug_fastdiv_check(seed, 1024, 256) == 0
