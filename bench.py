@@ -25,6 +25,10 @@ WORKLOADS = {
     "19x19": dict(n=19, games=2048, sims=800, name="19x19 Go batched self-play, 2048 games, 800 sims/move"),
 }
 LATENT = 128
+# dram__bytes_read.sum + dram__bytes_write.sum per unit from the ncu --set full captures summarised in
+# profiles/r01/ncu_full_{9x9,19x19}_v8_raw.csv (writes are partly still in the 126 MB L2 when the kernel ends)
+NCU_TRAFFIC = {"rec_bytes_per_leaf": {9: 30.0e3, 19: 183.1e3}, "tree_bytes_per_game": {9: 3.19e3, 19: 12.24e3},
+               "source": "profiles/r01/ncu_full_*_v8_raw.csv"}
 
 
 def flops_recurrent(n, c=LATENT):
@@ -385,11 +389,17 @@ def run_ours(args, wl):
                 "gpu_launches": int(launches_all), "search_graph_replays": int(lib.mzgo_graph_replays()),
                 "roofline": {"bound": "tensor", "kernel": "mzgo_net_recurrent (dynamics conv3x3 + heads, one leaf batch)",
                              "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved / peak_tf,
-                             "traffic": None, "peak_source": peaks["source"] + " bf16 sustained",
+                             "traffic": (NCU_TRAFFIC["rec_bytes_per_leaf"][n] * live if n in NCU_TRAFFIC["rec_bytes_per_leaf"] else None),
+                             "traffic_unit": "bytes per launch (ncu dram read+write per leaf x leaves)",
+                             "algorithmic_bytes": 2 * LATENT * n * n * 2 * live, "peak_source": peaks["source"] + " bf16 sustained",
                              "launch_ms": kern_ms, "leaves_per_launch": live},
                 "roofline_tree": {"bound": "hbm", "kernel": "k_tree_step (expand + backup + select, all trees)",
                                   "achieved": tree_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                                  "frac": tree_gbs / peaks["hbm_gbs"], "traffic": None, "launch_ms": tree_ms,
+                                  "frac": tree_gbs / peaks["hbm_gbs"],
+                                  "traffic": (NCU_TRAFFIC["tree_bytes_per_game"][n] * tree_sims / tree_reps
+                                              if n in NCU_TRAFFIC["tree_bytes_per_game"] else None),
+                                  "traffic_note": "ncu capture at leaf depth 1; " + NCU_TRAFFIC["source"],
+                                  "launch_ms": tree_ms,
                                   "bytes_per_sim": bytes_tree(tree_depth), "mean_leaf_depth": tree_depth,
                                   "sims_per_launch": tree_sims / tree_reps,
                                   "state": f"simulations {S - tree_reps}..{S} of a search"},
