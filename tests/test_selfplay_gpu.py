@@ -131,14 +131,18 @@ def test_engine_invariants(n, c, G, S, precision):
                 st, count, passes = gymgo.init_state(n), 0, 0
 
 
-def test_engine_equals_stepwise_api():
+@pytest.mark.parametrize("n,c,G,S,precision,variant", [(5, 16, 16, 10, "fp32", "main"), (5, 128, 16, 40, "bf16", "main"),
+                                                       (9, 128, 150, 120, "bf16", "main"), (9, 128, 40, 100, "bf16", "self_play"),
+                                                       (13, 128, 9, 200, "bf16", "main"), (19, 128, 150, 24, "bf16", "main")])
+def test_engine_equals_stepwise_api(n, c, G, S, precision, variant):
     """mzgo_selfplay_run is the composition of the exported pieces: same seed => same moves as driving
-    net/tree/rules call by call from Python."""
+    net/tree/rules call by call from Python.  The engine runs the fused tree-step kernel and replays the search
+    loop from a CUDA graph; the stepwise side uses the stand-alone select / recurrent / expand_backup entry
+    points (tensor-core networks at 9x9, 13x13 and 19x19, both search variants)."""
     import muzero_go_b200 as mz
     from muzero_go_b200 import _lib
-    n, c, G, S = 5, 16, 16, 10
-    _, net = make_net(n, c, 9)
-    cfg = mz.SearchConfig(seed=1234)
+    _, net = make_net(n, c, 9, precision)
+    cfg = mz.SearchConfig.for_variant(variant, seed=1234)
     eng = mz.SelfPlayEngine(net, n, G, S, search=cfg, traj_capacity=6, restart_finished=True)
     eng.run(6)
     torch.cuda.synchronize()
