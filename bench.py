@@ -197,7 +197,7 @@ def run_ours(args, wl):
     while (G // waves) * per_game > 0.90 * free_b or G % waves:
         waves += 1
     T = 2
-    group = mz.WaveGroup(net, n, G, S, waves=waves, search=mz.SearchConfig(seed=1000 + rank), traj_capacity=T,
+    group = mz.WaveGroup(net, n, G, S, waves=waves, search=mz.SearchConfig(seed=1000, game_base=rank * G), traj_capacity=T,
                          restart_finished=True)
     eng = group.engines[0]          # the single-kernel timings below run on one wave's buffers
     GW = G // waves

@@ -141,7 +141,9 @@ typedef struct mzgo_search_params {
     int32_t c_puct_is_int;     /* 1: c*P exact in P's dtype (main.py); 0: float c, rounds in float32 below the root */
     uint64_t seed;             /* device RNG key (Philox) when no stream / noise is injected */
     int32_t variant;           /* MZGO_VARIANT_* */
-    int32_t reserved;
+    int32_t game_base;         /* global id of game 0 of this tree set: the device RNG is keyed by (seed, game_base + g,
+                                  move, draw), so a job's games play the same whichever way they are sharded over
+                                  ranks or waves */
 } mzgo_search_params_t;
 
 /* Root preparation, main.py:259-288.  root_soft: float32 softmax of the initial policy logits.

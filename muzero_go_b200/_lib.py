@@ -31,7 +31,7 @@ class SearchParams(C.Structure):
     """mzgo_search_params_t"""
     _fields_ = [("c_puct", C.c_double), ("discount", C.c_double), ("dirichlet_epsilon", C.c_double),
                 ("pass_epsilon", C.c_double), ("dirichlet_alpha", C.c_float), ("c_puct_is_int", C.c_int32),
-                ("seed", C.c_uint64), ("variant", C.c_int32), ("reserved", C.c_int32)]
+                ("seed", C.c_uint64), ("variant", C.c_int32), ("game_base", C.c_int32)]
 
 
 NET_PARAM_FIELDS = ["rep_w1", "rep_b1", "rep_w2", "rep_b2", "rep_w3", "rep_b3", "emb", "dyn_w", "dyn_b",

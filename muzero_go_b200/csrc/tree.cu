@@ -88,7 +88,7 @@ k_tree_reset_roots(mzgo_tree_t t, mzgo_search_params_t p, const float* __restric
         for (int j = 0; j < MAX_EPL; j++) {
             int a = j * 32 + lane;
             gam[j] = 0.f;
-            if (a < A) gam[j] = sample_gamma(p.dirichlet_alpha, p.seed, (uint32_t)g, 0x10000u + move_index, (uint32_t)a * 80u);
+            if (a < A) gam[j] = sample_gamma(p.dirichlet_alpha, p.seed, (uint32_t)(g + p.game_base), 0x10000u + move_index, (uint32_t)a * 80u);
             gsum += gam[j];
         }
         gsum = warp_sum_f(gsum);
@@ -205,7 +205,7 @@ k_tree_select(mzgo_tree_t t, mzgo_search_params_t p, const uint32_t* __restrict_
             // random.choice(unexpanded), main.py:322-325
             uint32_t ctr = t.choice_ctr[g];
             uint32_t r = choice_stream ? choice_stream[(size_t)g * stride + ctr]
-                                       : mzgo_rand_u32(p.seed, (uint32_t)g, 0x20000u + (uint32_t)t.move_index, ctr);
+                                       : mzgo_rand_u32(p.seed, (uint32_t)(g + p.game_base), 0x20000u + (uint32_t)t.move_index, ctr);
             int k = (int)(r % (uint32_t)n_open);
             int a_sel = -1;
 #pragma unroll
@@ -651,7 +651,7 @@ k_tree_step(mzgo_tree_t t, mzgo_search_params_t p, const float* __restrict__ sof
     while (true) {
         int oa = -1, on = 0, oc = -1;
         const int rc = step_level<TPG>(sh, sub, tid, nv_r, cp, vs_r, ch_r, pos, npar, v1, ctr0, choice_stream, stream_off, p,
-                                       (uint32_t)g, move_index, &oa, &on, &oc);
+                                       (uint32_t)(g + p.game_base), move_index, &oa, &on, &oc);
         if (rc == 0) { sel_parent = node; sel_action = oa; break; }
         if (rc == 2 || oc <= 0) break;           // terminal leaf / dropped simulation (node keeps the leaf)
         if (tid == 0 && depth <= A) path[depth - 1] = node * 512 + oa;
@@ -763,7 +763,7 @@ k_tree_choose_action(mzgo_tree_t t, mzgo_search_params_t p, float temperature, c
                 float v = __shfl_up_sync(FULL_MASK, incl, o);
                 if (lane >= o) incl += v;
             }
-            float target = u01(mzgo_rand_u32(p.seed, (uint32_t)g, 0x30000u + move_index, 0u)) * tot;
+            float target = u01(mzgo_rand_u32(p.seed, (uint32_t)(g + p.game_base), 0x30000u + move_index, 0u)) * tot;
             uint32_t hit = __ballot_sync(FULL_MASK, wsum > 0.f && target < incl);
             int hl = hit ? __ffs(hit) - 1 : 31 - __clz(__ballot_sync(FULL_MASK, wsum > 0.f));
             int mine = -1;
@@ -794,7 +794,7 @@ k_tree_choose_action(mzgo_tree_t t, mzgo_search_params_t p, float temperature, c
         }
     } else {
         // uniform over np.nonzero(valid_mask) (main.py:674-677)
-        int k = (int)(mzgo_rand_u32(p.seed, (uint32_t)g, 0x40000u + move_index, 0u) % (uint32_t)max(nvalid, 1));
+        int k = (int)(mzgo_rand_u32(p.seed, (uint32_t)(g + p.game_base), 0x40000u + move_index, 0u) % (uint32_t)max(nvalid, 1));
 #pragma unroll
         for (int j = 0; j < MAX_EPL; j++) {
             int a = j * 32 + lane;

@@ -130,9 +130,9 @@ class WaveGroup:
         per = num_games // waves
         self.engines = []
         for w in range(waves):
-            cfg = search
-            if search is not None and w > 0:       # independent RNG streams per wave (games are keyed by local index)
-                cfg = dataclasses.replace(search, seed=search.seed + 7919 * w)
+            # one RNG key space for the whole group: wave w owns the global game ids [base + w*per, base + (w+1)*per)
+            base_cfg = search if search is not None else SearchConfig()
+            cfg = dataclasses.replace(base_cfg, game_base=base_cfg.game_base + w * per)
             self.engines.append(SelfPlayEngine(net, board_size, per, num_simulations, search=cfg,
                                                share_search_buffers_with=self.engines[0] if w else None, **kw))
         e0 = self.engines[0]

@@ -21,6 +21,7 @@ class SearchConfig:
     dirichlet_alpha: float = 0.03
     pass_epsilon: float = 0.05
     seed: int = 0
+    game_base: int = 0        # global id of this engine's game 0 (RNG key), so sharding does not change the games
     variant: str = "main"     # "main" (main.py / play.py) or "self_play" (self_play.py:142-343), SURVEY 2.2
 
     VARIANTS = {"main": 0, "play": 0, "self_play": 1}
@@ -46,6 +47,7 @@ class SearchConfig:
         if self.variant not in self.VARIANTS:
             raise ValueError(f"unknown search variant {self.variant!r}")
         p.variant = self.VARIANTS[self.variant]
+        p.game_base = int(self.game_base)
         return p
 
 

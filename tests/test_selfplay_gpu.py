@@ -174,26 +174,30 @@ def test_engine_equals_stepwise_api(n, c, G, S, precision, variant):
         boards.step(action)
 
 
-def test_wave_group_equals_separate_engines():
-    """Waves share the trees, the latent arena and the scratch; because a search only lives for one move each
-    wave must play exactly what a stand-alone engine with the same seed plays (and the replayed search-loop
-    graph must give what plain launches give: the stand-alone engines below run with the same code path)."""
+def test_games_are_invariant_to_sharding_and_waves():
+    """The device RNG is keyed by (seed, global game id, move, draw) (SearchConfig.game_base), so a job's games
+    play the same moves whether they run as one engine, as waves that share search buffers, or as shards on
+    different ranks.  Also checks graph replay against plain launches (first move of every engine)."""
     import dataclasses
     import muzero_go_b200 as mz
     n, c, G, S, T = 5, 16, 12, 12, 5
     _, net = make_net(n, c, 3)
     cfg = mz.SearchConfig(seed=77)
+    whole = mz.SelfPlayEngine(net, n, G, S, search=cfg, traj_capacity=T)
+    whole.run(T)
     group = mz.WaveGroup(net, n, G, S, waves=3, search=cfg, traj_capacity=T)
     group.run(T)
     torch.cuda.synchronize()
     rows = group.trajectory_rows(0, T)
     assert tuple(rows["action"].shape) == (T, G) and group.read_counters()["moves"] == G * T
     assert group.engines[1].arena.data_ptr() == group.engines[0].arena.data_ptr()
-    for w in range(3):
-        solo = mz.SelfPlayEngine(net, n, G // 3, S, search=dataclasses.replace(cfg, seed=77 + 7919 * w), traj_capacity=T)
-        solo.run(T)
+    assert torch.equal(rows["action"], whole.traj_action)
+    assert torch.equal(rows["policy"], whole.traj_policy)
+    assert torch.equal(rows["boards"], whole.traj_boards)
+    for r in range(2):                               # two "ranks" of 6 games each
+        shard = mz.SelfPlayEngine(net, n, G // 2, S, search=dataclasses.replace(cfg, game_base=r * (G // 2)), traj_capacity=T)
+        shard.run(T)
         torch.cuda.synchronize()
-        lo, hi = w * (G // 3), (w + 1) * (G // 3)
-        assert torch.equal(rows["action"][:, lo:hi], solo.traj_action)
-        assert torch.equal(rows["policy"][:, lo:hi], solo.traj_policy)
-        assert torch.equal(rows["boards"][:, lo:hi], solo.traj_boards)
+        lo, hi = r * (G // 2), (r + 1) * (G // 2)
+        assert torch.equal(shard.traj_action, whole.traj_action[:, lo:hi])
+        assert torch.equal(shard.traj_policy, whole.traj_policy[:, lo:hi])
