@@ -17,7 +17,7 @@
 // The action embedding (main.py:98-100) is linear in the conv, so it is folded at weight-load time into
 // a per-action, per-border-class bias table [A][9][C] (border pixels see fewer taps).
 //
-// Warp roles (320 threads): warp 0 TMA producer (latent slab in two 64-channel halves, weight k-blocks
+// Warp roles (384 threads): warp 0 TMA producer (latent slab in two 64-channel halves, weight k-blocks
 // through an mbarrier ring), warp 1 TMEM owner + MMA issuer (descriptors precomputed, ~4 instructions
 // per tcgen05.mma), warps 2-9 epilogue (tcgen05.ld -> bias/ReLU -> heads with the 1x1 weights read as
 // kernel-parameter constants -> bf16 -> coalesced 16 B stores in the arena layout).
@@ -31,7 +31,7 @@
 namespace {
 
 constexpr int TC_C = 128;               // latent_dim of the tensor-core path
-constexpr int TC_THREADS = 352;         // producer, MMA issuer, 8 epilogue warps, finaliser
+constexpr int TC_THREADS = 384;         // producer, MMA issuer, 8 epilogue warps, 2 finalisers (384 x 168 registers)
 constexpr int TC_EPI_THREADS = 256;
 constexpr int TC_MAX_STAGES = 8;        // weight k-block ring (as many as fit)
 constexpr int TC_SLOTS = 4;             // 4 x 128 TMEM columns
@@ -106,6 +106,13 @@ __device__ __forceinline__ void bulk_g2s_hint(void* dst, const void* src, uint32
 __device__ __forceinline__ void st_global_v4_hint(void* ptr, uint4 v, uint64_t policy) {
     asm volatile("st.global.L2::cache_hint.v4.b32 [%0], {%1, %2, %3, %4}, %5;" ::"l"(ptr), "r"(v.x), "r"(v.y), "r"(v.z),
                  "r"(v.w), "l"(policy) : "memory");
+}
+// Predicated form without a "memory" clobber: nothing in the kernel reads these bytes back, and as a compiler
+// barrier (or behind a branch) the store kept the next channel chunk's shared-memory loads from being hoisted.
+__device__ __forceinline__ void st_global_v4_hint_if(void* ptr, uint4 v, uint64_t policy, bool ok) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %6, 0;\n\t@p st.global.L2::cache_hint.v4.b32 [%0], {%1, %2, %3, %4}, %5;\n\t}" ::"l"(ptr),
+        "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w), "l"(policy), "r"((uint32_t)ok));
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -228,14 +235,27 @@ __device__ __forceinline__ bool elect_one() {
 __device__ __forceinline__ int tc_items_lo(const TcArgs& a) { return (int)((long long)blockIdx.x * a.B / gridDim.x); }
 __device__ __forceinline__ int tc_items_hi(const TcArgs& a) { return (int)((long long)(blockIdx.x + 1) * a.B / gridDim.x); }
 
-// Which images of a group are live (bit i = image i).  Lane i looks at image i and the result is a
-// ballot, so every role of the kernel sees the same warp-uniform mask.
-__device__ __forceinline__ uint32_t tc_live_mask(const TcArgs& a, int base, int cnt, int lane) {
+// The item records of a group: lane i holds (action, input slot, output slot) of image i, -1 beyond the
+// group.  Every role loads them one group AHEAD (three independent loads, consumed an iteration later):
+// read at the top of the group they were three dependent L2 round trips on the way to the first bulk copy,
+// in front of every accumulator tile's first store, and in the launch's tail behind the last epilogue.
+struct TcItems {
+    int act, isl, osl;
+};
+__device__ __forceinline__ TcItems tc_load_items(const TcArgs& a, int base, int items_hi, int lane) {
+    TcItems r;
+    r.act = r.isl = r.osl = -1;
     const int item = base + lane;
-    bool ok = lane < cnt;
-    if (ok) ok = (!a.action || a.action[item] >= 0) && (!a.in_slot || a.in_slot[item] >= 0) &&
-                 (!a.out_slot || a.out_slot[item] >= 0);
-    return __ballot_sync(FULL_MASK, ok);
+    if (lane < a.images_per_group && item < items_hi) {
+        r.act = a.action ? __ldg(a.action + item) : 0;
+        r.isl = a.in_slot ? __ldg(a.in_slot + item) : item;
+        r.osl = a.out_slot ? __ldg(a.out_slot + item) : item;
+    }
+    return r;
+}
+// Which images of a group are live (bit i = image i): a ballot, so every role sees the same warp-uniform mask.
+__device__ __forceinline__ uint32_t tc_live_mask(const TcItems& t) {
+    return __ballot_sync(FULL_MASK, (t.act | t.isl | t.osl) >= 0);
 }
 
 struct TcCtx {
@@ -258,7 +278,7 @@ struct TcCtx {
 // and there is ONE copy of the unrolled channel loop in the instruction cache.
 // One thread = one output position x all COUT channels of its tile.
 template <int COUT, int MODE>
-__device__ __forceinline__ void tc_epilogue_role(const TcArgs& a, const TcCtx& cx) {
+__device__ __forceinline__ void tc_epilogue_role(const TcArgs& a, const TcCtx& cx, const TcItems& first) {
     constexpr int KC_OUT = COUT / 8;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int wq = warp & 3, pi = (warp - 2) >> 2;
@@ -282,9 +302,14 @@ __device__ __forceinline__ void tc_epilogue_role(const TcArgs& a, const TcCtx& c
     }
     uint32_t tile_ctr = 0, it = 0;
     const uint64_t pol_stream = l2_policy_evict_first();
-    for (int base = tc_items_lo(a); base < items_hi; base += images) {
+    // (the next group's records are requested at the END of a group, so that they are not live across the tile
+    // loop -- 128 accumulators per thread leave no registers to spare -- and travel during the wait for the
+    // next accumulator)
+    TcItems nx = first;
+    for (int base = tc_items_lo(a); base < items_hi; base += images, nx = tc_load_items(a, base, items_hi, lane)) {
         const int cnt = min(images, items_hi - base), NT = cnt * tpi;
-        const uint32_t live = tc_live_mask(a, base, cnt, lane);
+        const uint32_t live = tc_live_mask(nx);
+        const int my_osl = nx.osl;
         if (!live) continue;
         const uint32_t par = it & 1, use = it >> 1;
         if (MODE == MODE_DYN) mbar_wait(cx.tbl_full + par, use & 1);                 // bias tables of this group have landed
@@ -312,6 +337,7 @@ __device__ __forceinline__ void tc_epilogue_role(const TcArgs& a, const TcCtx& c
                 }
                 asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
             }
+            if (warp == 2 && lane == 0 && it == 2) tc_stamp(a, 18);
             // the accumulator now lives in registers: hand the TMEM slot back to the MMA warp at once
             tc_fence_before();
             __syncwarp();
@@ -323,14 +349,20 @@ __device__ __forceinline__ void tc_epilogue_role(const TcArgs& a, const TcCtx& c
             const int q = q0 + tt * 128 + wq * 32 + lane;
             const bool store_ok = q < ps;
             const float* tb = (MODE == MODE_DYN) ? s_tbl + (img * 9 + cls) * COUT : s_tbl;
-            const int item = base + img;
-            const int oslot = a.out_slot ? a.out_slot[item] : item;
+            const int oslot = __shfl_sync(FULL_MASK, my_osl, img);
             uint4* dst = reinterpret_cast<uint4*>(a.out) + (size_t)oslot * KC_OUT * ps + q;
             float pol = 0.f, val = 0.f, rew = 0.f;
+            const uint32_t keep = valid ? 0xffffffffu : 0u;
+            float4 nb0 = *reinterpret_cast<const float4*>(tb), nb1 = *reinterpret_cast<const float4*>(tb + 4);
 #pragma unroll
             for (int k = 0; k < KC_OUT; k++) {
-                const float4 b0 = *reinterpret_cast<const float4*>(tb + k * 8);
-                const float4 b1 = *reinterpret_cast<const float4*>(tb + k * 8 + 4);
+                // the next chunk's biases are requested one chunk ahead; the compiler barrier at the end of the
+                // body keeps the chunks in order (scheduled across chunks the 128 accumulators spill)
+                const float4 b0 = nb0, b1 = nb1;
+                if (k + 1 < KC_OUT) {
+                    nb0 = *reinterpret_cast<const float4*>(tb + (k + 1) * 8);
+                    nb1 = *reinterpret_cast<const float4*>(tb + (k + 1) * 8 + 4);
+                }
                 const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
                 float x[8];
 #pragma unroll
@@ -342,17 +374,20 @@ __device__ __forceinline__ void tc_epilogue_role(const TcArgs& a, const TcCtx& c
                     }
                     if (MODE == MODE_DYN) rew = fmaf(x[e], a.hw[2 * TC_C + k * 8 + e], rew);
                 }
-                if (store_ok) {
-                    uint4 w;
-                    w.x = pack_bf16(x[0], x[1]);
-                    w.y = pack_bf16(x[2], x[3]);
-                    w.z = pack_bf16(x[4], x[5]);
-                    w.w = pack_bf16(x[6], x[7]);
-                    if (!valid) w = make_uint4(0u, 0u, 0u, 0u);      // padding positions stay zero for the next conv
-                    if (MODE == MODE_PLAIN) dst[(size_t)k * ps] = w;          // read again by the next layer
-                    else st_global_v4_hint(dst + (size_t)k * ps, w, pol_stream);
+                uint4 w;                                             // padding positions stay zero for the next conv
+                w.x = pack_bf16(x[0], x[1]) & keep;
+                w.y = pack_bf16(x[2], x[3]) & keep;
+                w.z = pack_bf16(x[4], x[5]) & keep;
+                w.w = pack_bf16(x[6], x[7]) & keep;
+                if (MODE == MODE_PLAIN) {
+                    if (store_ok) *dst = w;                          // read again by the next layer
+                } else {
+                    st_global_v4_hint_if(dst, w, pol_stream, store_ok);
                 }
+                dst += ps;
+                asm volatile("" ::: "memory");
             }
+            if (warp == 2 && lane == 0 && it == 2) tc_stamp(a, 19);
             if (MODE != MODE_PLAIN) {
                 if (valid) s_pol[img * 384 + r * n + cc] = pol + a.sc.pol_b;
                 val = warp_sum_f(valid ? val : 0.f);
@@ -371,62 +406,137 @@ __device__ __forceinline__ void tc_epilogue_role(const TcArgs& a, const TcCtx& c
 }
 
 // ---------------------------------------------------------------------------------------- finaliser role
-// One warp: per image the value / reward heads (main.py:101-105, :118-120) and the policy softmax.
+// Two warps taking turns (warp 10 the even groups, warp 11 the odd ones: the groups' buffers are double
+// buffered by the same parity, so a short last group does not queue behind its predecessor): per group the
+// value / reward heads (main.py:101-105, :118-120) and the policy softmax of its (up to
+// TC_GROUP_TILES) images.  The group's last finaliser pass is the tail of the launch, so the images are worked
+// on side by side: lane i runs the head chain of image i, and every softmax pass has the loads of all images
+// (four positions per lane and image) in flight before the first dependent instruction.  The per-lane order of
+// the additions is the order of a plain loop over k = lane, lane + 32, ...
 template <int MODE>
-__device__ __forceinline__ void tc_finaliser_role(const TcArgs& a, const TcCtx& cx) {
+__device__ __forceinline__ void tc_finaliser_role(const TcArgs& a, const TcCtx& cx, const TcItems& first, uint32_t which) {
+    constexpr int MI = TC_GROUP_TILES;
     const int lane = threadIdx.x & 31;
     const int n = a.n, np = n * n;
     const int tpi = a.tiles_per_image, images = a.images_per_group;
     const int items_hi = tc_items_hi(a);
+    const float pass_logit = a.sc.pass_logit;
     uint32_t it = 0;
+    TcItems nx = first;
     for (int base = tc_items_lo(a); base < items_hi; base += images) {
         const int cnt = min(images, items_hi - base);
-        const uint32_t live = tc_live_mask(a, base, cnt, lane);
+        const uint32_t live = tc_live_mask(nx);
+        nx = tc_load_items(a, base + images, items_hi, lane);
         if (!live) continue;
         const uint32_t par = it & 1, use = it >> 1;
+        if (par != which) { it++; continue; }           // the other finaliser warp's group
         mbar_wait(cx.fin_full + par, use & 1);
+        const bool stamp = lane == 0 && (it == 1 || it == 2);
+        const int stamp0 = it == 2 ? 24 : 27;
+        if (stamp) tc_stamp(a, stamp0);
         float* s_pol = reinterpret_cast<float*>(cx.s_pol + par * cx.pol_stride);
         const float* s_part = cx.s_part + par * (TC_SLOTS * 4 * 2);
-        for (int img = 0; img < cnt; img++) {
-            if (!(live & (1u << img))) continue;
-            const int item = base + img;
+        if (lane < cnt && ((live >> lane) & 1u)) {
+            const int img = lane, item = base + img;
             float vs = 0.f, rs = 0.f;
             for (int k = 0; k < tpi * 4; k++) { vs += s_part[(img * tpi * 4 + k) * 2]; rs += s_part[(img * tpi * 4 + k) * 2 + 1]; }
-            if (lane == 0) {
-                const float vm = vs / (float)np + a.sc.val_b;
-                a.value[item] = fmaf(a.sc.vfc_w, vm, a.sc.vfc_b);
-                if (MODE == MODE_DYN) {
-                    const float rm = rs / (float)np + a.sc.rew_b;
-                    float rw = a.sc.ro_b;
+            const float vm = vs / (float)np + a.sc.val_b;
+            a.value[item] = fmaf(a.sc.vfc_w, vm, a.sc.vfc_b);
+            if (MODE == MODE_DYN) {
+                const float rm = rs / (float)np + a.sc.rew_b;
+                float rw = a.sc.ro_b;
 #pragma unroll
-                    for (int k = 0; k < 16; k++) rw = fmaf(a.sc.ro_w[k], fmaxf(fmaf(a.sc.rh_w[k], rm, a.sc.rh_b[k]), 0.f), rw);
-                    a.reward[item] = rw;
-                }
+                for (int k = 0; k < 16; k++) rw = fmaf(a.sc.ro_w[k], fmaxf(fmaf(a.sc.rh_w[k], rm, a.sc.rh_b[k]), 0.f), rw);
+                a.reward[item] = rw;
             }
-            const float* lg = s_pol + img * 384;
-            float* pol_out = a.policy + (size_t)item * (np + 1);
-            if (!a.want_softmax) {
-                for (int k = lane; k < np; k += 32) pol_out[k] = lg[k];
-                if (lane == 0) pol_out[np] = a.sc.pass_logit;
-            } else {
-                // softmax over np board logits + the pass logit (main.py:298); the exponentials are staged in
-                // place in shared memory so that the loops run np/32 times, not a fixed 12
-                float* ex = s_pol + img * 384;
-                float m = a.sc.pass_logit;
-                for (int k = lane; k < np; k += 32) m = fmaxf(m, lg[k]);
-                m = warp_max_f(m);
-                float se = 0.f;
-                for (int k = lane; k < np; k += 32) {
-                    const float e = __expf(lg[k] - m);
-                    ex[k] = e;
-                    se += e;
-                }
-                const float ep = __expf(a.sc.pass_logit - m);
-                se = warp_sum_f(se) + ep;
-                const float inv = 1.0f / se;
-                for (int k = lane; k < np; k += 32) pol_out[k] = ex[k] * inv;
-                if (lane == 0) pol_out[np] = ep * inv;
+        }
+        if (stamp) tc_stamp(a, stamp0 + 1);
+        bool on[MI];
+        float* pol_out[MI];
+#pragma unroll
+        for (int i = 0; i < MI; i++) {
+            on[i] = i < cnt && ((live >> i) & 1u);
+            pol_out[i] = a.policy + (size_t)(base + i) * (np + 1);
+        }
+        float v[MI][4];
+        if (!a.want_softmax) {
+            for (int k0 = lane; k0 < np; k0 += 128) {
+#pragma unroll
+                for (int i = 0; i < MI; i++)
+#pragma unroll
+                    for (int u = 0; u < 4; u++)
+                        if (on[i] && k0 + u * 32 < np) v[i][u] = s_pol[i * 384 + k0 + u * 32];
+#pragma unroll
+                for (int i = 0; i < MI; i++)
+#pragma unroll
+                    for (int u = 0; u < 4; u++)
+                        if (on[i] && k0 + u * 32 < np) pol_out[i][k0 + u * 32] = v[i][u];
             }
+#pragma unroll
+            for (int i = 0; i < MI; i++)
+                if (on[i] && lane == 0) pol_out[i][np] = pass_logit;
+        } else {
+            // softmax over np board logits + the pass logit (main.py:298); the exponentials are staged in place
+            float m[MI], se[MI];
+#pragma unroll
+            for (int i = 0; i < MI; i++) { m[i] = pass_logit; se[i] = 0.f; }
+            for (int k0 = lane; k0 < np; k0 += 128) {
+#pragma unroll
+                for (int i = 0; i < MI; i++)
+#pragma unroll
+                    for (int u = 0; u < 4; u++)
+                        v[i][u] = (on[i] && k0 + u * 32 < np) ? s_pol[i * 384 + k0 + u * 32] : pass_logit;
+#pragma unroll
+                for (int i = 0; i < MI; i++)
+#pragma unroll
+                    for (int u = 0; u < 4; u++) m[i] = fmaxf(m[i], v[i][u]);
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+                for (int i = 0; i < MI; i++) m[i] = fmaxf(m[i], __shfl_xor_sync(FULL_MASK, m[i], o));
+            for (int k0 = lane; k0 < np; k0 += 128) {
+#pragma unroll
+                for (int i = 0; i < MI; i++)
+#pragma unroll
+                    for (int u = 0; u < 4; u++)
+                        if (on[i] && k0 + u * 32 < np) v[i][u] = s_pol[i * 384 + k0 + u * 32];
+#pragma unroll
+                for (int i = 0; i < MI; i++)
+#pragma unroll
+                    for (int u = 0; u < 4; u++)
+                        if (on[i] && k0 + u * 32 < np) {
+                            const float e = __expf(v[i][u] - m[i]);
+                            s_pol[i * 384 + k0 + u * 32] = e;
+                            se[i] += e;
+                        }
+            }
+            if (stamp) tc_stamp(a, stamp0 + 2);
+            float ep[MI], inv[MI];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+                for (int i = 0; i < MI; i++) se[i] += __shfl_xor_sync(FULL_MASK, se[i], o);
+#pragma unroll
+            for (int i = 0; i < MI; i++) {
+                ep[i] = __expf(pass_logit - m[i]);
+                inv[i] = 1.0f / (se[i] + ep[i]);
+            }
+            for (int k0 = lane; k0 < np; k0 += 128) {
+#pragma unroll
+                for (int i = 0; i < MI; i++)
+#pragma unroll
+                    for (int u = 0; u < 4; u++)
+                        if (on[i] && k0 + u * 32 < np) v[i][u] = s_pol[i * 384 + k0 + u * 32];
+#pragma unroll
+                for (int i = 0; i < MI; i++)
+#pragma unroll
+                    for (int u = 0; u < 4; u++)
+                        if (on[i] && k0 + u * 32 < np) pol_out[i][k0 + u * 32] = v[i][u] * inv[i];
+            }
+#pragma unroll
+            for (int i = 0; i < MI; i++)
+                if (on[i] && lane == 0) pol_out[i][np] = ep[i] * inv[i];
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(cx.fin_empty + par);
@@ -513,7 +623,7 @@ __device__ __forceinline__ void tc_mma_group(const TcArgs& a, const TcMmaCtx& mx
 }
 
 template <int CIN, int COUT>
-__device__ __forceinline__ void tc_mma_role(const TcArgs& a, const TcMmaCtx& mx) {
+__device__ __forceinline__ void tc_mma_role(const TcArgs& a, const TcMmaCtx& mx, const TcItems& first) {
     constexpr int KC_IN = CIN / 8;
     const int lane = threadIdx.x & 31;
     const int ps = a.ps, q0 = a.n + 2;
@@ -528,9 +638,11 @@ __device__ __forceinline__ void tc_mma_role(const TcArgs& a, const TcMmaCtx& mx)
         st.a_lo[j] = desc_lo(mx.sA + img * slab_bytes + (uint32_t)(q0 + tt * 128) * 16, ps * 16);
     }
     const int items_hi = tc_items_hi(a);
+    TcItems nx = first;
     for (int base = tc_items_lo(a); base < items_hi; base += images) {
         const int cnt = min(images, items_hi - base);
-        const uint32_t live = tc_live_mask(a, base, cnt, lane);
+        const uint32_t live = tc_live_mask(nx);
+        nx = tc_load_items(a, base + images, items_hi, lane);
         if (!live) continue;
         switch (cnt * tpi) {
             case 1: tc_mma_group<CIN, COUT, 1>(a, mx, st); break;
@@ -567,6 +679,8 @@ k_tc_conv(const __grid_constant__ TcArgs a) {
     const int n = a.n, ps = a.ps;
     const int images = a.images_per_group;
     if (threadIdx.x == 0) tc_stamp(a, 0);
+    // the first group's item records travel while the barriers and the TMEM allocation are set up
+    const TcItems first = tc_load_items(a, tc_items_lo(a), tc_items_hi(a), lane);
     const uint32_t slab_bytes = (uint32_t)KC_IN * ps * 16;
     const uint32_t half_bytes = slab_bytes / NH;
     const int q0 = n + 2;                           // flat position of pixel (0,0)
@@ -593,9 +707,11 @@ k_tc_conv(const __grid_constant__ TcArgs a) {
         uint32_t it = 0, s = 0, bph = 0;
         const uint64_t pol_stream = l2_policy_evict_first(), pol_keep = l2_policy_evict_last();
         const int items_hi = tc_items_hi(a);
+        TcItems nx = first;
         for (int base = tc_items_lo(a); base < items_hi; base += images) {
-            const int cnt = min(images, items_hi - base);
-            const uint32_t live = tc_live_mask(a, base, cnt, lane);
+            const TcItems cur = nx;
+            const uint32_t live = tc_live_mask(cur);
+            nx = tc_load_items(a, base + images, items_hi, lane);
             if (!live) continue;
             if (MODE == MODE_DYN) {
                 // per-action bias tables of this group -> s_tbl[parity] (free once the epilogue of group it-2 is through)
@@ -603,20 +719,16 @@ k_tc_conv(const __grid_constant__ TcArgs a) {
                 if (use > 0) mbar_wait(fin_full + par, (use - 1) & 1);
                 if (lane == 0) mbar_expect_tx(tbl_full + par, 9u * COUT * 4 * __popc(live));
                 __syncwarp();
-                if ((live >> lane) & 1u) {
-                    const int item = base + lane;
+                if ((live >> lane) & 1u)
                     bulk_g2s(smem + L.tbl_off + par * L.tbl_stride + (uint32_t)lane * 9 * COUT * 4,
-                             a.tbl + (size_t)a.action[item] * 9 * COUT, 9u * COUT * 4, tbl_full + par);
-                }
+                             a.tbl + (size_t)cur.act * 9 * COUT, 9u * COUT * 4, tbl_full + par);
             }
             for (int h = 0; h < NH; h++) {
                 mbar_wait(a_empty + h, (it & 1) ^ 1);
                 if (lane == 0) mbar_expect_tx(a_full + h, half_bytes * __popc(live));
                 __syncwarp();
                 if ((live >> lane) & 1u) {
-                    const int item = base + lane;
-                    const int slot = a.in_slot ? a.in_slot[item] : item;
-                    const uint8_t* src = reinterpret_cast<const uint8_t*>(a.in) + (size_t)slot * slab_bytes + (size_t)h * half_bytes;
+                    const uint8_t* src = reinterpret_cast<const uint8_t*>(a.in) + (size_t)cur.isl * slab_bytes + (size_t)h * half_bytes;
                     if (MODE == MODE_DYN) bulk_g2s_hint(sA + (size_t)lane * slab_bytes + (size_t)h * half_bytes, src, half_bytes, a_full + h, pol_stream);
                     else bulk_g2s(sA + (size_t)lane * slab_bytes + (size_t)h * half_bytes, src, half_bytes, a_full + h);
                 }
@@ -640,7 +752,7 @@ k_tc_conv(const __grid_constant__ TcArgs a) {
         mx.a_full = a_full; mx.a_empty = a_empty; mx.b_full = b_full; mx.b_empty = b_empty;
         mx.acc_full = acc_full; mx.acc_empty = acc_empty;
         mx.tmem_base = tmem_base;
-        tc_mma_role<CIN, COUT>(a, mx);
+        tc_mma_role<CIN, COUT>(a, mx, first);
     } else {
         TcCtx cx;
         cx.s_tbl = smem + L.tbl_off;
@@ -654,8 +766,8 @@ k_tc_conv(const __grid_constant__ TcArgs a) {
         cx.fin_full = fin_full;
         cx.fin_empty = fin_empty;
         cx.tmem_base = tmem_base;
-        if (warp < 10) tc_epilogue_role<COUT, MODE>(a, cx);              // 8 warps: TMEM lane quarter x tile parity
-        else if (MODE != MODE_PLAIN) tc_finaliser_role<MODE>(a, cx);     // heads + softmax per image
+        if (warp < 10) tc_epilogue_role<COUT, MODE>(a, cx, first);             // 8 warps: TMEM lane quarter x tile parity
+        else if (MODE != MODE_PLAIN) tc_finaliser_role<MODE>(a, cx, first, (uint32_t)warp - 10u);    // heads + softmax per image
     }
     tc_fence_before();
     __syncthreads();

@@ -15,7 +15,9 @@ from muzero_go_b200 import _lib  # noqa: E402
 
 NAMES = {0: "entry", 1: "setup done", 2: "mma g0 start", 3: "mma g0 issued", 4: "mma g1 start", 5: "mma g1 issued",
          6: "mma g2 start", 7: "mma g2 issued", 10: "epi g0 first acc", 11: "epi g0 done", 12: "epi g1 first acc",
-         13: "epi g1 done", 14: "epi g2 first acc", 15: "epi g2 done", 20: "fin g0", 21: "fin g1", 22: "fin g2", 30: "exit"}
+         13: "epi g1 done", 14: "epi g2 first acc", 15: "epi g2 done", 27: "fin g1 woke", 28: "fin g1 heads", 29: "fin g1 exps", 24: "fin g2 woke", 25: "fin g2 heads", 26: "fin g2 exps",
+         18: "epi g2 acc in regs", 19: "epi g2 stored",
+         20: "fin g0", 21: "fin g1", 22: "fin g2", 30: "exit"}
 
 
 def main():
