@@ -247,6 +247,17 @@ int mzgo_net_recurrent(const mzgo_net_t* net, void* arena /*device*/, const int3
                        const int32_t* action, const int32_t* out_slot, float* reward, float* value,
                        float* policy, int want_softmax, int B, void* stream);
 
+/* bf16 mode only: mzgo_net_recurrent on every game's selected leaf (in_slot / action / out_slot are the tree's
+ * leaf_in_slot / leaf_action / leaf_out_slot) with the search fused behind it in the same kernel: as soon as a
+ * game's outputs are final, a warp group of the same CTA runs mzgo_tree_step for it (expansion + backup and, when
+ * do_select != 0, the selection of its next leaf; same arithmetic, main.py:294-363).  One launch per
+ * simulation; this is what mzgo_search_run enqueues in bf16 mode.  reward / value / policy (softmax) still
+ * receive the network outputs. */
+int mzgo_net_recurrent_tree(const mzgo_net_t* net, void* arena /*device*/, const mzgo_tree_t* tree,
+                            const mzgo_search_params_t* params, const uint32_t* choice_stream /*device, optional*/,
+                            int stride, float* reward /*device [G]*/, float* value /*device [G]*/,
+                            float* policy /*device [G][A]*/, int do_select, void* stream);
+
 /* PredictionNetwork.forward alone (main.py:116-125) on the latents in slot[b]: value [B], policy [B][A]. */
 int mzgo_net_predict(const mzgo_net_t* net, const void* arena /*device*/, const int32_t* slot /*device [B]*/,
                      float* value, float* policy, int want_softmax, int B, void* stream);

@@ -87,6 +87,8 @@ _PROTOS = {
     "mzgo_net_prepare": (i32, [C.POINTER(NetDesc), vp]),
     "mzgo_net_initial": (i32, [C.POINTER(NetDesc), vp, vp, vp, vp, vp, vp, i32, i32, vp]),
     "mzgo_net_recurrent": (i32, [C.POINTER(NetDesc), vp, vp, vp, vp, vp, vp, vp, i32, i32, vp]),
+    "mzgo_net_recurrent_tree": (i32, [C.POINTER(NetDesc), vp, C.POINTER(TreeDesc), C.POINTER(SearchParams), vp, i32, vp, vp,
+                                      vp, i32, vp]),
     "mzgo_net_predict": (i32, [C.POINTER(NetDesc), vp, vp, vp, vp, i32, i32, vp]),
     "mzgo_net_export_latent": (i32, [C.POINTER(NetDesc), vp, vp, vp, i32, vp]),
     "mzgo_net_import_latent": (i32, [C.POINTER(NetDesc), vp, vp, vp, i32, vp]),

@@ -4,6 +4,7 @@
 // choice, env.step, trajectory append, two-pass / move-cap termination) and the game epilogue
 // main.py:703-711.  The host loop below only enqueues kernels; per simulation it enqueues
 // select -> recurrent inference -> expand/backup for the whole batch of games.
+#include <stdlib.h>
 #include <string.h>
 
 #include <mutex>
@@ -114,6 +115,21 @@ extern "C" int mzgo_search_run(const mzgo_selfplay_t* sp, const uint32_t* choice
     if (int e = check_sp(sp)) return e;
     const mzgo_tree_t* t = &sp->tree;
     cudaStream_t st = (cudaStream_t)stream;
+    static const bool unfused = getenv("MZGO_NO_FUSED_TREE") != nullptr;      // A/B switch for measurements
+    if (sp->net.precision == 1 && !unfused && sp->num_simulations > 0 && t->A <= 96) {
+        // bf16 mode, boards up to 9x9 (a warp per game in the tree step): ONE launch per simulation.  The first
+        // selection, then S x [recurrent inference with the expansion + backup of its leaf and the next selection
+        // behind it in the same kernel].  On larger boards a game takes 128 threads and a CTA's seven games
+        // three rounds, which costs more than the launch it saves (19x19: 8.7 vs 9.3 M sims/s): two launches.
+        if (int e = mzgo_tree_step(t, &sp->params, sp->leaf_policy, sp->leaf_reward, sp->leaf_value, choice_stream, stride,
+                                   0, 1, st))
+            return e;
+        for (int s = 0; s < sp->num_simulations; s++)
+            if (int e = mzgo_net_recurrent_tree(&sp->net, sp->arena, t, &sp->params, choice_stream, stride, sp->leaf_reward,
+                                                sp->leaf_value, sp->leaf_policy, s + 1 < sp->num_simulations, stream))
+                return e;
+        return MZGO_OK;
+    }
     // per simulation: [expand/backup of the previous leaf + next selection] -> recurrent inference
     for (int s = 0; s < sp->num_simulations; s++) {
         if (int e = mzgo_tree_step(t, &sp->params, sp->leaf_policy, sp->leaf_reward, sp->leaf_value, choice_stream, stride,

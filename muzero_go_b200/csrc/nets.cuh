@@ -46,4 +46,6 @@ int mzgo_tc_initial(const mzgo_net_t* net, const float* obs, const uint32_t* boa
 int mzgo_tc_recurrent(const mzgo_net_t* net, void* arena, const int32_t* in_slot, const int32_t* action,
                       const int32_t* out_slot, float* reward, float* value, float* policy, int want_softmax, int B,
                       cudaStream_t st);
-
+int mzgo_tc_recurrent_tree(const mzgo_net_t* net, void* arena, const mzgo_tree_t* tree, const mzgo_search_params_t* sp,
+                           const uint32_t* choice_stream, int stride, float* reward, float* value, float* policy,
+                           int do_select, cudaStream_t st);

@@ -48,6 +48,20 @@ extern "C" int mzgo_net_recurrent(const mzgo_net_t* net, void* arena, const int3
     return mzgo_tc_recurrent(net, arena, in_slot, action, out_slot, reward, value, policy, want_softmax, B, st);
 }
 
+extern "C" int mzgo_net_recurrent_tree(const mzgo_net_t* net, void* arena, const mzgo_tree_t* tree,
+                                       const mzgo_search_params_t* params, const uint32_t* choice_stream, int stride,
+                                       float* reward, float* value, float* policy, int do_select, void* stream) {
+    if (int e = mzgo_net_check(net)) return e;
+    MZGO_CHECK_ARG(net->precision == 1, "the fused network + tree step needs the bf16 (tensor core) mode");
+    MZGO_CHECK_ARG(arena && tree && params && reward && value && policy, "NULL argument");
+    MZGO_CHECK_ARG(tree->A == net->A && tree->G >= 0 && tree->G <= net->max_batch, "tree does not match the network (A=%d, G=%d)",
+                   tree->A, tree->G);
+    MZGO_CHECK_ARG(tree->leaf_in_slot && tree->leaf_action && tree->leaf_out_slot && tree->move_index_dev, "tree has a NULL array");
+    if (tree->G == 0) return MZGO_OK;
+    return mzgo_tc_recurrent_tree(net, arena, tree, params, choice_stream, stride, reward, value, policy, do_select,
+                                  (cudaStream_t)stream);
+}
+
 extern "C" int mzgo_net_predict(const mzgo_net_t* net, const void* arena, const int32_t* slot, float* value,
                                 float* policy, int want_softmax, int B, void* stream) {
     if (int e = mzgo_net_check(net)) return e;

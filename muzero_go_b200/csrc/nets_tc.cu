@@ -27,6 +27,7 @@
 #include <unordered_map>
 
 #include "nets.cuh"
+#include "tree_step.cuh"
 
 namespace {
 
@@ -178,6 +179,14 @@ struct TcArgs {
     int B;                       // items
     int n, ps, tiles_per_image, images_per_group, stages;
     unsigned long long* trace;   // optional (tools/tc_trace.py): [grid][32] globaltimer stamps of the roles
+    // mzgo_net_recurrent_tree: items are the games' selected leaves (in_slot / action / out_slot = the tree's
+    // leaf records), and once the CTA's roles are through, all of its threads run the tree step of the CTA's
+    // games (expand + backup, and the next selection when tree_mode == 1): one launch per simulation
+    int tree_mode;
+    int choice_stride;
+    const uint32_t* choice_stream;
+    mzgo_tree_t tree;
+    mzgo_search_params_t sp;
     TcScalars sc;
     float hw[3 * TC_C];          // policy / value / reward 1x1 conv weights: read as constant-bank operands
 };
@@ -772,6 +781,27 @@ k_tc_conv(const __grid_constant__ TcArgs a) {
     tc_fence_before();
     __syncthreads();
     if (threadIdx.x == 0) tc_stamp(a, 30);
+    if (MODE == MODE_DYN && a.tree_mode) {
+        // ===================================================== tree phase (tree_step.cuh, the code of k_tree_step)
+        // Item i of the launch is game i's leaf, and a CTA's items are a contiguous range of games: what the
+        // search does with the outputs is CTA-local.  The finalisers' value / reward / policy stores are ordered
+        // before these (L2) loads by the barrier above; the scratch aliases the input slabs, which are dead.
+        const int g_lo = tc_items_lo(a), g_hi = tc_items_hi(a);
+        const int do_select = a.tree_mode == 1;
+        const int sub128 = threadIdx.x >> 7;
+        if (a.tree.A <= STEP_EPT * 32) {
+            StepShared<32>* sh = reinterpret_cast<StepShared<32>*>(sA) + sub128;      // a warp per game
+            for (int g = g_lo + warp; g < g_hi; g += TC_THREADS / 32)
+                tree_step_body<32, 2>(a.tree, a.sp, a.policy, a.reward, a.value, a.choice_stream, a.choice_stride, 1, do_select,
+                                      *sh, warp & 3, lane, g, [] {});
+        } else {
+            StepShared<128>* sh = reinterpret_cast<StepShared<128>*>(sA) + sub128;    // 128 threads per game
+            for (int g = g_lo + sub128; g < g_hi; g += TC_THREADS / 128)
+                tree_step_body<128, 2>(a.tree, a.sp, a.policy, a.reward, a.value, a.choice_stream, a.choice_stride, 1, do_select,
+                                       *sh, 0, threadIdx.x & 127, g, [] {});
+        }
+        if (threadIdx.x == 0) tc_stamp(a, 31);
+    }
     if (warp == 1) {
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem_base) : "memory");
@@ -1098,4 +1128,29 @@ int mzgo_tc_recurrent(const mzgo_net_t* net, void* arena, const int32_t* in_slot
     a.want_softmax = want_softmax;
     if (int e = fill_heads(net, a)) return e;
     return launch_tc_conv<TC_C, TC_C, MODE_DYN>(a, net->n, B, st);
+}
+
+// mzgo_net_recurrent on the tree's selected leaves with the tree step behind it in the same launch (every CTA
+// expands + backs up the leaves it evaluated and, if do_select, selects its games' next leaves)
+int mzgo_tc_recurrent_tree(const mzgo_net_t* net, void* arena, const mzgo_tree_t* tree, const mzgo_search_params_t* sp,
+                           const uint32_t* choice_stream, int stride, float* reward, float* value, float* policy,
+                           int do_select, cudaStream_t st) {
+    if (int e = ensure_rcp_table()) return e;
+    char* ws = (char*)net->workspace;
+    NetWorkspace w = mzgo_net_layout(net->n, net->C, net->precision, net->max_batch);
+    TcArgs a{};
+    a.in = (const __nv_bfloat16*)arena;
+    a.out = (__nv_bfloat16*)arena;
+    a.in_slot = tree->leaf_in_slot; a.action = tree->leaf_action; a.out_slot = tree->leaf_out_slot;
+    a.wB = (const __nv_bfloat16*)(ws + w.tc_w);
+    a.tbl = (const float*)(ws + w.tc_embbias);
+    a.reward = reward; a.value = value; a.policy = policy;
+    a.want_softmax = 1;
+    a.tree_mode = do_select ? 1 : 2;
+    a.choice_stream = choice_stream;
+    a.choice_stride = stride;
+    a.tree = *tree;
+    a.sp = *sp;
+    if (int e = fill_heads(net, a)) return e;
+    return launch_tc_conv<TC_C, TC_C, MODE_DYN>(a, net->n, tree->G, st);
 }

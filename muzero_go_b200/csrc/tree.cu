@@ -5,7 +5,7 @@
 // are bit-exact when both sides consume identical float32 network outputs (SURVEY.md 8a "dtype facts"):
 //   root priors float64, child priors float32, PUCT score float64 with every operation individually
 //   rounded (no FMA contraction), ties broken towards the lowest action index.
-#include "tree_math.cuh"
+#include "tree_step.cuh"
 
 namespace {
 
@@ -362,345 +362,18 @@ k_tree_expand_backup(mzgo_tree_t t, mzgo_search_params_t p, const float* __restr
 //      backup path, the child link when the leaf hangs off the root) are patched in registers;
 //   2. the backup read-modify-write of the path edges;
 //   3. one batch per level below the root (visits, priors, value sums and child links together).
-constexpr int STEP_THREADS = 128;
-constexpr int STEP_EPT = 3;   // edges per thread: A <= 3 * TPG
-
-__device__ __forceinline__ int npar_root_after(int root_visit0, int act) { return root_visit0 + (act >= 0 ? 1 : 0); }
-
-template <int TPG>
-__device__ __forceinline__ void step_sync() {
-    if (TPG == 32) __syncwarp(); else __syncthreads();
-}
-
-template <int TPG>
-struct StepShared {
-    static constexpr int GPB = STEP_THREADS / TPG, WPG = TPG / 32, NW = STEP_EPT * WPG;
-    uint32_t open[GPB][NW];      // ballot words per game (word w covers actions [32w, 32w+32))
-    uint32_t live[GPB][WPG];
-    double qmin[GPB][WPG], qmax[GPB][WPG], best[GPB][WPG];
-    int besta[GPB][WPG], bestn[GPB][WPG], bestc[GPB][WPG];
-    float pri[GPB][STEP_EPT * TPG];   // self_play.py variant: masked child priors before the renormalisation
-    float tot[GPB];
-};
-
-// One PUCT level (main.py:318-358) on register-resident edge data.  Returns 0: an unexpanded edge was drawn
-// (*out_a), 1: descend through *out_a into child *out_c (which has *out_n visits), 2: nothing selectable.
-template <int TPG>
-__device__ __forceinline__ int step_level(StepShared<TPG>& sh, int sub, int tid, const int (&nv)[STEP_EPT],
-                                          const double (&cp)[STEP_EPT], const double (&vs)[STEP_EPT],
-                                          const int (&ch)[STEP_EPT], uint32_t pos, int npar, bool v1, uint32_t rnd_or_ctr,
-                                          const uint32_t* choice_stream, size_t stream_off, const mzgo_search_params_t& p,
-                                          uint32_t g, uint32_t move_index, int* out_a, int* out_n, int* out_c) {
-    constexpr int WPG = TPG / 32, NW = STEP_EPT * WPG;
-    const int wig = tid >> 5, lane = tid & 31;
-#pragma unroll
-    for (int e = 0; e < STEP_EPT; e++) {
-        const bool opn = ((pos >> e) & 1u) && nv[e] == 0;
-        const uint32_t b = __ballot_sync(FULL_MASK, opn);
-        if (lane == 0) sh.open[sub][e * WPG + wig] = b;
-    }
-    const uint32_t any_live = __ballot_sync(FULL_MASK, pos != 0u);
-    if (lane == 0) sh.live[sub][wig] = any_live;
-    step_sync<TPG>();
-    int n_open = 0;
-    uint32_t all_live = 0u;
-#pragma unroll
-    for (int w = 0; w < NW; w++) n_open += __popc(sh.open[sub][w]);
-#pragma unroll
-    for (int w = 0; w < WPG; w++) all_live |= sh.live[sub][w];
-    if (n_open > 0) {
-        // random.choice(unexpanded), main.py:322-325
-        const uint32_t r = choice_stream ? choice_stream[stream_off + rnd_or_ctr]
-                                         : mzgo_rand_u32(p.seed, g, 0x20000u + move_index, rnd_or_ctr);
-        int k = (int)(r % (uint32_t)n_open);
-        int a_sel = -1;
-#pragma unroll
-        for (int w = 0; w < NW; w++) {
-            const uint32_t b = sh.open[sub][w];
-            const int c = __popc(b);
-            if (a_sel < 0) {
-                if (k < c) a_sel = w * 32 + (int)__fns(b, 0, k + 1);
-                else k -= c;
-            }
-        }
-        // word w = e * WPG + wig covers the edges e * TPG + wig * 32 + [0, 32): the same numbering as the action index
-        *out_a = a_sel;
-        return 0;
-    }
-    if (!all_live) return 2;                     // nothing selectable: simulation dropped / terminal leaf
-    // Q of every live edge, min-max normalisation set = prior > 0 (main.py:328-339)
-    double q[STEP_EPT];
-    double qmin = INFINITY, qmax = -INFINITY;
-#pragma unroll
-    for (int e = 0; e < STEP_EPT; e++) {
-        q[e] = 0.0;
-        if ((pos >> e) & 1u) {
-            if (nv[e] > 0) q[e] = (fabs(vs[e]) < 1e6) ? div_by_count(vs[e], nv[e]) : __ddiv_rn(vs[e], (double)nv[e]);
-            qmin = fmin(qmin, q[e]);
-            qmax = fmax(qmax, q[e]);
-        }
-    }
-    qmin = warp_min_d(qmin);
-    qmax = warp_max_d(qmax);
-    if (WPG > 1) {
-        if (lane == 0) { sh.qmin[sub][wig] = qmin; sh.qmax[sub][wig] = qmax; }
-        step_sync<TPG>();
-#pragma unroll
-        for (int w = 0; w < WPG; w++) { qmin = fmin(qmin, sh.qmin[sub][w]); qmax = fmax(qmax, sh.qmax[sub][w]); }
-    }
-    const double sq = __dsqrt_rn((double)(v1 ? max(1, npar) : npar + 1));   // main.py:354 / self_play.py:297-300
-    const bool norm = qmax > qmin;
-    const double range = __dsub_rn(qmax, qmin);
-    // 1/range once per level; a range outside the proven window of div_rn_with_rcp takes the generic division
-    const bool fast = norm && range > 1e-17 && range < 1e3 && fabs(qmin) < 1e6 && fabs(qmax) < 1e6;
-    const double rrange = fast ? __drcp_rn(range) : 0.0;
-    double best = -INFINITY;
-    int best_a = -1, best_n = 0, best_c = -1;
-#pragma unroll
-    for (int e = 0; e < STEP_EPT; e++) {
-        if ((pos >> e) & 1u) {
-            const double dq = __dsub_rn(q[e], qmin);
-            const double qn = norm ? (fast ? div_rn_with_rcp(dq, range, rrange) : __ddiv_rn(dq, range)) : q[e];
-            const double num = __dmul_rn(cp[e], sq);
-            const double u = (num < 1e6) ? div_by_count(num, 1 + nv[e]) : __ddiv_rn(num, (double)(1 + nv[e]));
-            const double score = __dadd_rn(qn, u);
-            if (score > best) { best = score; best_a = e * TPG + tid; best_n = nv[e]; best_c = ch[e]; }   // e ascending = action ascending
-        }
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        const double ob = __shfl_xor_sync(FULL_MASK, best, o);
-        const int oa = __shfl_xor_sync(FULL_MASK, best_a, o);
-        const int on = __shfl_xor_sync(FULL_MASK, best_n, o);
-        const int oc = __shfl_xor_sync(FULL_MASK, best_c, o);
-        const bool take = (oa >= 0) && (best_a < 0 || ob > best || (ob == best && oa < best_a));
-        if (take) { best = ob; best_a = oa; best_n = on; best_c = oc; }
-    }
-    if (WPG > 1) {
-        if (lane == 0) { sh.best[sub][wig] = best; sh.besta[sub][wig] = best_a; sh.bestn[sub][wig] = best_n; sh.bestc[sub][wig] = best_c; }
-        step_sync<TPG>();
-        best = sh.best[sub][0]; best_a = sh.besta[sub][0]; best_n = sh.bestn[sub][0]; best_c = sh.bestc[sub][0];
-#pragma unroll
-        for (int w = 1; w < WPG; w++) {
-            const double ob = sh.best[sub][w];
-            const int oa = sh.besta[sub][w], on = sh.bestn[sub][w], oc = sh.bestc[sub][w];
-            const bool take = (oa >= 0) && (best_a < 0 || ob > best || (ob == best && oa < best_a));
-            if (take) { best = ob; best_a = oa; best_n = on; best_c = oc; }
-        }
-    }
-    if (best_a < 0) return 2;                    // only NaN / -inf scores: the reference falls out of the loop too
-    *out_a = best_a;
-    *out_n = best_n;
-    *out_c = best_c;
-    return 1;
-}
+// (the step itself lives in tree_step.cuh: the network kernel of nets_tc.cu runs the same code as a warp-group role)
 
 template <int TPG>
 __global__ void __launch_bounds__(STEP_THREADS, 8)
-k_tree_step(mzgo_tree_t t, mzgo_search_params_t p, const float* __restrict__ soft, const float* __restrict__ reward,
-            const float* __restrict__ value, const uint32_t* __restrict__ choice_stream, int stride, int do_backup,
-            int do_select) {
+k_tree_step(mzgo_tree_t t, mzgo_search_params_t p, const float* soft, const float* reward, const float* value,
+            const uint32_t* __restrict__ choice_stream, int stride, int do_backup, int do_select) {
     constexpr int GPB = STEP_THREADS / TPG;     // games per block
     __shared__ StepShared<TPG> sh;
-    const bool v1 = p.variant == MZGO_VARIANT_SELFPLAY;
     const int sub = threadIdx.x / TPG, tid = threadIdx.x % TPG;
     const int g = blockIdx.x * GPB + sub;
     if (g >= t.G) return;                        // TPG == 128: the whole block; TPG == 32: whole warps
-    const int A = t.A, M = t.M;
-    int* path = reinterpret_cast<int*>(t.prior + (size_t)g * M * A);   // scratch row of the root (its priors are float64, elsewhere)
-    const size_t rbase = (size_t)g * M * A;      // edges of the root
-
-    // ---------------------------------------------------------------- round trip 1: every independent load
-    const int act = do_backup ? t.leaf_action[g] : -1;
-    const int par = t.leaf_parent[g];
-    const int nw = t.leaf_node[g];
-    const int depth_b = t.leaf_depth[g];
-    const float rew_g = do_backup ? reward[g] : 0.f, val_g = do_backup ? value[g] : 0.f;
-    const int is_active = t.active[g];
-    const uint32_t move_index = (uint32_t)*t.move_index_dev;   // written by the root preparation of this move
-    const int pk0 = path[0];                     // first edge of the stored path (an edge of the root)
-    const int pk_raw = tid < A ? path[tid] : -1;
-    const int root_visit0 = t.root_visit[g];
-    const uint32_t ctr0 = t.choice_ctr[g];
-    const int nn0 = t.n_nodes[g];
-    const float* mask = t.root_mask + (size_t)g * A;
-    float mk[STEP_EPT], sf[STEP_EPT];
-    int nv_r[STEP_EPT], ch_r[STEP_EPT];
-    double pr_r[STEP_EPT], vs_r[STEP_EPT];
-#pragma unroll
-    for (int e = 0; e < STEP_EPT; e++) {
-        const int a = e * TPG + tid;
-        mk[e] = 0.f; sf[e] = 0.f; nv_r[e] = 0; ch_r[e] = -1; pr_r[e] = 0.0; vs_r[e] = 0.0;
-        if (a < A) {
-            mk[e] = mask[a];
-            if (do_backup) sf[e] = soft[(size_t)g * A + a];
-            if (do_select) {
-                nv_r[e] = t.edge_visit[rbase + a];
-                pr_r[e] = t.root_prior[(size_t)g * A + a];
-                vs_r[e] = t.edge_vsum[rbase + a];
-                ch_r[e] = (int)t.child[rbase + a];
-            }
-        }
-    }
-
-    // ---------------------------------------------------------------- expand + backup
-    // backup_value = reward.item() + discount * value.item()   (main.py:311), float64
-    const double bv = __dadd_rn((double)rew_g, __dmul_rn(p.discount, (double)val_g));
-    if (act >= 0 && v1) {
-        // policy_child *= valid_mask; /= sum (float32 pairwise)   self_play.py:210-214
-#pragma unroll
-        for (int e = 0; e < STEP_EPT; e++) {
-            const int a = e * TPG + tid;
-            if (a < A) sh.pri[sub][a] = masked_child_prior(sf[e], mk[e], a == A - 1, p.pass_epsilon);
-        }
-    }
-    if (v1) {                                    // uniform for the block: p is a kernel parameter
-        step_sync<TPG>();
-        if (tid == 0 && act >= 0) sh.tot[sub] = np_pairwise_sum<float>(sh.pri[sub], A);
-        step_sync<TPG>();
-    }
-    if (act >= 0) {
-        const int depth = depth_b;
-        const size_t nbase = ((size_t)g * M + nw) * A;
-        const int pk_mine = (depth <= A && tid < depth) ? pk_raw : -1;
-#pragma unroll
-        for (int e = 0; e < STEP_EPT; e++) {
-            const int a = e * TPG + tid;
-            if (a < A) {
-                // prior_child = policy_child[a] if valid_mask[a] > 0 else 0   (the ROOT's mask, main.py:303)
-                float pr = mk[e] > 0.f ? sf[e] : 0.f;
-                if (v1) pr = renorm_child_prior(sh.pri[sub][a], sh.tot[sub], mk[e], a == A - 1, p.pass_epsilon, mask, A);
-                t.prior[nbase + a] = pr;
-                t.edge_visit[nbase + a] = 0;
-                t.edge_vsum[nbase + a] = 0.0;
-                t.child[nbase + a] = (int16_t)-1;
-            }
-        }
-        // self_play.py:340-343: node i levels above the new leaf gets value * (-1)^i; edge d of the path holds the
-        // statistics of the node at depth d + 1, i.e. i = depth - 1 - d, and the root has i = depth
-        if (depth <= A) {
-            if (pk_mine >= 0) {
-                const size_t e = ((size_t)g * M + (pk_mine >> 9)) * A + (pk_mine & 511);
-                const int ev = t.edge_visit[e];
-                const double es = t.edge_vsum[e];
-                t.edge_visit[e] = ev + 1;
-                t.edge_vsum[e] = __dadd_rn(es, (v1 && ((depth - 1 - tid) & 1)) ? -bv : bv);
-            }
-            for (int d = tid + TPG; d < depth; d += TPG) {
-                const int pk = path[d];
-                const size_t e = ((size_t)g * M + (pk >> 9)) * A + (pk & 511);
-                t.edge_visit[e] += 1;
-                t.edge_vsum[e] = __dadd_rn(t.edge_vsum[e], (v1 && ((depth - 1 - d) & 1)) ? -bv : bv);
-            }
-        }
-        if (tid == 0) {
-            t.child[((size_t)g * M + par) * A + act] = (int16_t)nw;
-            t.parent[(size_t)g * M + nw] = par * 512 + act;
-            t.n_nodes[g] = nw + 1;
-            if (depth > A) {                     // path longer than the scratch row: walk the parent links
-                int node = nw;
-                double sv = bv;
-                while (node != 0) {
-                    const int pk = t.parent[(size_t)g * M + node];
-                    const int pn = pk >> 9, pa = pk & 511;
-                    const size_t e = ((size_t)g * M + pn) * A + pa;
-                    t.edge_visit[e] += 1;
-                    t.edge_vsum[e] = __dadd_rn(t.edge_vsum[e], sv);
-                    if (v1) sv = -sv;
-                    node = pn;
-                }
-            }
-            t.root_visit[g] = root_visit0 + 1;
-            t.root_vsum[g] = __dadd_rn(t.root_vsum[g], (v1 && (depth & 1)) ? -bv : bv);
-            t.sims_done[g] += 1;
-            t.depth_sum[g] += depth;
-        }
-        // the root level fetched above predates this backup: patch the one root edge on the path (the same
-        // float64 addition the backup thread performs on the same operands) and the new child link
-        const int a_first = pk0 & 511;           // stored paths always start with an edge of the root
-        const double sv0 = (v1 && ((depth - 1) & 1)) ? -bv : bv;
-#pragma unroll
-        for (int e = 0; e < STEP_EPT; e++) {
-            const int a = e * TPG + tid;
-            if (a == a_first) { nv_r[e] += 1; vs_r[e] = __dadd_rn(vs_r[e], sv0); }
-            if (par == 0 && a == act) ch_r[e] = nw;
-        }
-    }
-    if (!do_select) return;
-    step_sync<TPG>();                            // the statistics written above are read below by other threads
-
-    // ---------------------------------------------------------------- select
-    if (!is_active) {
-        if (tid == 0) { t.leaf_parent[g] = -1; t.leaf_action[g] = -1; }
-        return;
-    }
-    int node = 0, depth = 1;
-    int npar = root_visit0 + (act >= 0 ? 1 : 0);
-    int sel_parent = -1, sel_action = -1;
-    const size_t stream_off = (size_t)g * stride;
-    // The level loop works on ONE set of register arrays (nv_r / vs_r / ch_r / cp): they hold the prefetched and
-    // patched root level on entry and are reloaded for every level below, so there is a single copy of the
-    // level code (the kernel is instruction-cache sensitive).
-    double cp[STEP_EPT];
-    uint32_t pos = 0u;
-#pragma unroll
-    for (int e = 0; e < STEP_EPT; e++) {
-        cp[e] = __dmul_rn(p.c_puct, pr_r[e]);    // root: float64 priors (main.py:276-282)
-        if (e * TPG + tid < A && pr_r[e] > 0.0) pos |= 1u << e;
-    }
-    while (true) {
-        int oa = -1, on = 0, oc = -1;
-        const int rc = step_level<TPG>(sh, sub, tid, nv_r, cp, vs_r, ch_r, pos, npar, v1, ctr0, choice_stream, stream_off, p,
-                                       (uint32_t)(g + p.game_base), move_index, &oa, &on, &oc);
-        if (rc == 0) { sel_parent = node; sel_action = oa; break; }
-        if (rc == 2 || oc <= 0) break;           // terminal leaf / dropped simulation (node keeps the leaf)
-        if (tid == 0 && depth <= A) path[depth - 1] = node * 512 + oa;
-        node = oc; npar = on; depth++;
-        step_sync<TPG>();                        // shared scratch is reused by the next level
-        const size_t base = ((size_t)g * M + node) * A;
-        float prf[STEP_EPT];
-        // all loads of the level first, so that they are in flight together
-#pragma unroll
-        for (int e = 0; e < STEP_EPT; e++) {
-            const int a = e * TPG + tid;
-            nv_r[e] = 0; prf[e] = 0.f; vs_r[e] = 0.0; ch_r[e] = -1;
-            if (a < A) {
-                nv_r[e] = t.edge_visit[base + a];
-                prf[e] = t.prior[base + a];
-                vs_r[e] = t.edge_vsum[base + a];
-                ch_r[e] = (int)t.child[base + a];
-            }
-        }
-        pos = 0u;
-#pragma unroll
-        for (int e = 0; e < STEP_EPT; e++) {
-            cp[e] = (double)__fmul_rn((float)p.c_puct, prf[e]);   // c*P rounds in float32 (NEP 50)
-            if (prf[e] > 0.f) pos |= 1u << e;
-        }
-    }
-    if (tid == 0) {
-        const int nn = act >= 0 ? nw + 1 : nn0;
-        if (sel_action < 0 && v1) {
-            // terminal leaf: backpropagate(path, 0) -- a visit for every node on the path (self_play.py:188-190)
-            int nd = node;
-            while (nd != 0) {
-                const int pk = t.parent[(size_t)g * M + nd];
-                t.edge_visit[((size_t)g * M + (pk >> 9)) * A + (pk & 511)] += 1;
-                nd = pk >> 9;
-            }
-            t.root_visit[g] = npar_root_after(root_visit0, act) + 1;
-        }
-        if (sel_action >= 0) t.choice_ctr[g] = ctr0 + 1u;
-        if (sel_action >= 0 && nn >= M) sel_action = -1;   // arena full: drop (cannot happen when M > simulations)
-        if (sel_action >= 0 && depth <= A) path[depth - 1] = sel_parent * 512 + sel_action;
-        t.leaf_parent[g] = sel_action >= 0 ? sel_parent : -1;
-        t.leaf_action[g] = sel_action;
-        t.leaf_node[g] = nn;
-        t.leaf_depth[g] = depth;
-        t.leaf_in_slot[g] = sel_action >= 0 ? g * M + sel_parent : -1;
-        t.leaf_out_slot[g] = sel_action >= 0 ? g * M + nn : -1;
-        if (sel_action < 0) t.dropped[g] += 1;
-    }
+    tree_step_body<TPG, 0>(t, p, soft, reward, value, choice_stream, stride, do_backup, do_select, sh, sub, tid, g, [] {});
 }
 
 // main.py:666-669

@@ -22,31 +22,55 @@ __device__ __forceinline__ double warp_max_d(double v) {
 __device__ __forceinline__ float add_rn(float a, float b) { return __fadd_rn(a, b); }
 __device__ __forceinline__ double add_rn(double a, double b) { return __dadd_rn(a, b); }
 
+// numpy's base case: fewer than 8 elements in order, else 8 strided accumulators combined pairwise, then the tail
 template <typename T>
-__device__ T np_pairwise_sum(const T* a, int n) {
+__device__ __forceinline__ T np_block_sum(const T* a, int n) {
     if (n < 8) {
         T r = (T)0;
         for (int i = 0; i < n; i++) r = add_rn(r, a[i]);
         return r;
     }
-    if (n <= 128) {
-        T r[8];
+    T r[8];
 #pragma unroll
-        for (int k = 0; k < 8; k++) r[k] = a[k];
-        int i = 8;
-        for (; i < n - (n % 8); i += 8) {
+    for (int k = 0; k < 8; k++) r[k] = a[k];
+    int i = 8;
+    for (; i < n - (n % 8); i += 8) {
 #pragma unroll
-            for (int k = 0; k < 8; k++) r[k] = add_rn(r[k], a[i + k]);
-        }
-        T res = add_rn(add_rn(add_rn(r[0], r[1]), add_rn(r[2], r[3])), add_rn(add_rn(r[4], r[5]), add_rn(r[6], r[7])));
-        for (; i < n; i++) res = add_rn(res, a[i]);
-        return res;
+        for (int k = 0; k < 8; k++) r[k] = add_rn(r[k], a[i + k]);
     }
-    int n2 = n / 2;
-    n2 -= n2 % 8;
-    return add_rn(np_pairwise_sum(a, n2), np_pairwise_sum(a + n2, n - n2));
+    T res = add_rn(add_rn(add_rn(r[0], r[1]), add_rn(r[2], r[3])), add_rn(add_rn(r[4], r[5]), add_rn(r[6], r[7])));
+    for (; i < n; i++) res = add_rn(res, a[i]);
+    return res;
 }
-__device__ float np_pairwise_sum_f32(const float* a, int n) { return np_pairwise_sum<float>(a, n); }
+
+// The recursion sum(a, n) = sum(a, n2) + sum(a + n2, n - n2), n2 = n/2 rounded down to a multiple of 8, for
+// n > 128, run on an explicit stack: no device function call (ptxas ignores setmaxnreg in kernels with calls).
+template <typename T>
+__device__ __forceinline__ T np_pairwise_sum(const T* a, int n) {
+    constexpr int DEPTH = 12;                   // n <= 128 * 2^11
+    const T* ptr[DEPTH];
+    int cnt[DEPTH], st[DEPTH];
+    T acc[DEPTH];
+    int top = 0;
+    ptr[0] = a; cnt[0] = n; st[0] = 0;
+    T ret = (T)0;
+    while (top >= 0) {
+        int n2 = cnt[top] / 2;
+        n2 -= n2 % 8;
+        if (st[top] == 0) {
+            if (cnt[top] <= 128 || top == DEPTH - 1) { ret = np_block_sum(ptr[top], cnt[top]); top--; }
+            else { st[top] = 1; ptr[top + 1] = ptr[top]; cnt[top + 1] = n2; st[top + 1] = 0; top++; }
+        } else if (st[top] == 1) {
+            acc[top] = ret;
+            st[top] = 2; ptr[top + 1] = ptr[top] + n2; cnt[top + 1] = cnt[top] - n2; st[top + 1] = 0; top++;
+        } else {
+            ret = add_rn(acc[top], ret);
+            top--;
+        }
+    }
+    return ret;
+}
+__device__ __forceinline__ float np_pairwise_sum_f32(const float* a, int n) { return np_pairwise_sum<float>(a, n); }
 
 // self_play.py:210: policy_child *= valid_mask -- float32 * float64 in float64, rounded back to float32.
 // The float64 mask is 0 / 1 on the board and pass_epsilon (or 1.0 when no board move is legal) for the pass.
