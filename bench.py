@@ -162,7 +162,7 @@ def run_reference(args, wl):
             "moves_per_sec": sum(mvals) / len(mvals),
             "cpu_baseline": {"value": v, "unit": "sims/s", "cores": procs, "kind": "port", "sample": sample},
             "e2e": {"value": v, "unit": "sims/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------------------ GPU arm
@@ -409,12 +409,31 @@ def run_ours(args, wl):
                                    "bytes_per_ply": rules_bytes / NB, "plies_per_sec": NB / (rules_ms * 1e-3)},
                 "cpu_baseline": cpu, "clocks": clocks,
                 "weight_broadcast_bytes": bytes_bcast}
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
+_JSON_OUT = None
+
+
+def claim_stdout():
+    """The contract is ONE JSON line on stdout, and libraries write there too (NCCL prints its version banner on
+    the first communicator): file descriptor 1 is pointed at stderr for the run and the line goes to the saved one."""
+    global _JSON_OUT
+    sys.stdout.flush()
+    _JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+
+
+def emit(line):
+    out = _JSON_OUT if _JSON_OUT is not None else sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 def main():
+    claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=4)
