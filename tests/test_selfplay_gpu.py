@@ -201,3 +201,53 @@ def test_games_are_invariant_to_sharding_and_waves():
         lo, hi = r * (G // 2), (r + 1) * (G // 2)
         assert torch.equal(shard.traj_action, whole.traj_action[:, lo:hi])
         assert torch.equal(shard.traj_policy, whole.traj_policy[:, lo:hi])
+
+
+@pytest.mark.parametrize("n,G,S,variant", [(5, 33, 30, "main"), (9, 300, 60, "main"), (9, 64, 60, "self_play"),
+                                           (13, 20, 40, "main"), (19, 151, 12, "main")])
+def test_recurrent_tree_equals_separate_calls(n, G, S, variant):
+    """mzgo_net_recurrent_tree (network + tree phase in one launch: a warp per game up to 9x9, 128 threads per
+    game above; fewer games than SMs, more games than a CTA has warps) leaves the same trees as
+    select / mzgo_net_recurrent / expand_backup: visit counts, value sums, priors and the chosen moves, bit-exact."""
+    import muzero_go_b200 as mz
+    from muzero_go_b200 import _lib
+    _, net = make_net(n, 128, 5, "bf16")
+    cfg = mz.SearchConfig.for_variant(variant, seed=99)
+    A, M = n * n + 1, S + 1
+    dev = torch.device("cuda")
+    L, s = _lib.load(), _lib.stream_ptr()
+    d = net.descriptor(G)
+    roots = (torch.arange(G, dtype=torch.int32, device=dev) * M).contiguous()
+    boards = mz.GoBoards(G, n).reset()
+    boards.step(torch.randint(0, n * n, (G,), dtype=torch.int32, device=dev) % (n * n))     # different positions per game
+
+    def search(fused):
+        tree = mz.Tree(G, A, M)
+        arena = net.new_arena(G * M)
+        val, rew, pol = torch.empty(G, device=dev), torch.empty(G, device=dev), torch.empty((G, A), device=dev)
+        _lib.check(L.mzgo_net_initial(d, None, _lib.ptr(boards.records), _lib.ptr(arena), _lib.ptr(roots), _lib.ptr(val),
+                                      _lib.ptr(pol), 1, G, s))
+        tree.reset_roots(cfg, pol, boards, n, noise=None, move_index=3)
+        p = cfg.to_struct()
+        if fused:
+            _lib.check(L.mzgo_tree_step(tree.desc, p, _lib.ptr(pol), _lib.ptr(rew), _lib.ptr(val), None, 0, 0, 1, s))
+            for i in range(S):
+                _lib.check(L.mzgo_net_recurrent_tree(d, _lib.ptr(arena), tree.desc, p, None, 0, _lib.ptr(rew), _lib.ptr(val),
+                                                     _lib.ptr(pol), 1 if i + 1 < S else 0, s))
+        else:
+            for _ in range(S):
+                tree.select(cfg, None)
+                _lib.check(L.mzgo_net_recurrent(d, _lib.ptr(arena), _lib.ptr(tree.leaf_in_slot), _lib.ptr(tree.leaf_action),
+                                                _lib.ptr(tree.leaf_out_slot), _lib.ptr(rew), _lib.ptr(val), _lib.ptr(pol), 1, G, s))
+                tree.expand_backup(cfg, pol, rew, val)
+        action, policy, root_value = tree.choose_action(cfg, 0.0, move_index=3)
+        torch.cuda.synchronize()
+        return tree, action, policy, root_value
+
+    ta, aa, pa, va = search(True)
+    tb, ab, pb, vb = search(False)
+    assert torch.equal(aa, ab) and torch.equal(pa, pb) and torch.equal(va, vb)
+    for name in ("edge_visit", "edge_vsum", "child", "root_visit", "root_vsum", "n_nodes", "sims_done", "depth_sum"):
+        assert torch.equal(getattr(ta, name), getattr(tb, name)), name
+    # (node 0's float32 prior row is the fused step's path scratch: the root's priors are the float64 root_prior)
+    assert torch.equal(ta.prior[:, 1:], tb.prior[:, 1:]) and torch.equal(ta.root_prior, tb.root_prior)
