@@ -11,6 +11,9 @@ from .networks import MuZeroNet
 from .mcts import MCTS, MCTSNode
 from .agent import MuZeroAgent
 from .selfplay import SelfPlayEngine, WaveGroup
+from .replay import MultiVersionReplayBuffer, PrioritizedReplayBuffer, episodes_from_rows, load_episodes, save_episodes
+from .trainer import BatchedTrainer, TrainConfig
 
 __all__ = ["MzgoError", "GoBoards", "GoEnv", "govars", "make", "SearchConfig", "Tree", "MuZeroNet", "MCTS", "WaveGroup",
-           "MCTSNode", "MuZeroAgent", "SelfPlayEngine"]
+           "MCTSNode", "MuZeroAgent", "SelfPlayEngine", "MultiVersionReplayBuffer", "PrioritizedReplayBuffer",
+           "episodes_from_rows", "load_episodes", "save_episodes", "BatchedTrainer", "TrainConfig"]

@@ -1,0 +1,189 @@
+"""Batched trainer -- SURVEY §8(f) rank 1, first slice.
+
+The reference (`MuZeroAgent.train`, /root/reference/main.py:381-501) takes `batch_size` trajectories and runs
+forward, backward, gradient clipping and an Adam step for EACH of them in turn at batch size 1.  Here the K-step
+unroll runs over the whole batch and the optimizer steps once on the mean of the per-trajectory losses; every
+per-trajectory quantity (targets, the three losses, their weights) is the reference's, so with `batch_size == 1`
+a step is the reference's step (tests/test_trainer.py pins the loss and the updated weights against the real
+`MuZeroAgent.train`, tests/golden/train_*.npz).
+
+Status: the differentiable forward and backward go through torch autograd on the parameter containers of
+`MuZeroNet` (cuDNN / cuBLAS on the GPU) -- library kernels.  The hand-written part of this repo is the self-play
+path; the trainer's own kernels (dgrad / wgrad on tcgen05) are the next step of this row, see DESIGN.md §7.
+
+  reward_value_transform      main.py:67-69
+  n-step value target         main.py:503-522 (`compute_target_value`)
+  losses                      main.py:396-476
+  clip 1.0, Adam 1e-4, StepLR(1000, 0.9)      main.py:377-379, :478-480, :498-499
+"""
+import dataclasses
+import random
+
+import numpy as np
+import torch
+import torch.nn.functional as F
+
+
+@dataclasses.dataclass
+class TrainConfig:
+    """main.py:27-56 (the values the trainer reads)."""
+    unroll_steps: int = 10
+    discount: float = 0.99
+    value_loss_weight: float = 1.0
+    policy_loss_weight: float = 1.0
+    reward_loss_weight: float = 1.0
+    learning_rate: float = 1e-4
+    use_value_transform: bool = True
+    max_grad_norm: float = 1.0
+    lr_step_size: int = 1000
+    lr_gamma: float = 0.9
+
+
+def reward_value_transform(x, epsilon=0.001):
+    """h(x) = sign(x) (sqrt(|x| + 1) - 1) + eps x   (main.py:67-69)"""
+    return torch.sign(x) * (torch.sqrt(torch.abs(x) + 1) - 1) + epsilon * x
+
+
+# ---- differentiable forward on the parameter containers of MuZeroNet (main.py:72-142) ---------------------------
+def representation(net, obs):
+    r = net.representation
+    x = F.relu(F.conv2d(obs, r.conv1.weight, r.conv1.bias, padding=1))
+    x = F.relu(F.conv2d(x, r.conv2.weight, r.conv2.bias, padding=1))
+    return F.relu(F.conv2d(x, r.conv3.weight, r.conv3.bias, padding=1))
+
+
+def prediction(net, latent):
+    p = net.prediction
+    value = F.conv2d(latent, p.value_conv.weight, p.value_conv.bias).mean(dim=(2, 3))
+    value = F.linear(value, p.value_fc.weight, p.value_fc.bias)
+    board = F.conv2d(latent, p.policy_conv.weight, p.policy_conv.bias).flatten(1)
+    logits = torch.cat([board, p.pass_logit.expand(board.shape[0], 1)], dim=1)
+    return value, logits
+
+
+def dynamics(net, latent, action):
+    d = net.dynamics
+    emb = F.embedding(action, d.action_embedding.weight)[:, :, None, None]
+    x = F.relu(F.conv2d(latent + emb, d.conv.weight, d.conv.bias, padding=1))
+    r = F.conv2d(x, d.reward_conv.weight, d.reward_conv.bias).mean(dim=(2, 3))
+    r = F.linear(F.relu(F.linear(r, d.fc_reward_hidden.weight, d.fc_reward_hidden.bias)), d.fc_reward_output.weight,
+                 d.fc_reward_output.bias)
+    return x, r
+
+
+@dataclasses.dataclass
+class Batch:
+    observations: torch.Tensor     # [B, 6, N, N] float32: the state at the start index
+    actions: torch.Tensor          # [B, K] int64 (pass once the recorded actions run out, main.py:433-438)
+    target_reward: torch.Tensor    # [B, K] float32
+    target_value: torch.Tensor     # [B, K+1] float32
+    target_policy: torch.Tensor    # [B, K+1, A] float32 (uniform past the end of the game, main.py:407-410)
+
+
+def build_batch(net, trajectories, start_indices, cfg, action_size, device):
+    """The targets of main.py:396-460 for every trajectory of the batch.  The bootstrap values of the n-step
+    targets (a fresh initial inference of observation index + unroll_steps, main.py:516-521) are ONE batched
+    no-grad forward over all (trajectory, step) pairs that need one."""
+    B, K = len(trajectories), cfg.unroll_steps
+    uniform = np.ones(action_size) / action_size
+    boot_obs, boot_where = [], []
+    tv = np.zeros((B, K + 1), dtype=np.float64)
+    factors = np.zeros((B, K + 1), dtype=np.float64)
+    tr = np.zeros((B, K), dtype=np.float64)
+    tp = np.zeros((B, K + 1, action_size), dtype=np.float64)
+    acts = np.zeros((B, K), dtype=np.int64)
+    for b, (traj, s) in enumerate(zip(trajectories, start_indices)):
+        rewards, T = traj["rewards"], len(traj["rewards"])
+        for k in range(K + 1):
+            index = s + k
+            target, factor = 0.0, 1.0
+            for j in range(index, min(index + K, T)):                    # main.py:508-514
+                target += factor * rewards[j]
+                factor *= cfg.discount
+            tv[b, k], factors[b, k] = target, factor
+            if index + K < T:                                            # main.py:516
+                boot_obs.append(np.asarray(traj["observations"][index + K], dtype=np.float32))
+                boot_where.append((b, k))
+            tp[b, k] = traj["policies"][index] if index < len(traj["policies"]) else uniform
+            if k >= 1:
+                i = index - 1
+                acts[b, k - 1] = traj["actions"][i] if i < len(traj["actions"]) else action_size - 1
+                tr[b, k - 1] = rewards[i] if i < T else 0.0
+    if boot_obs:
+        with torch.no_grad():
+            obs = torch.from_numpy(np.stack(boot_obs)).to(device)
+            value, _ = prediction(net, representation(net, obs))
+            value = value.flatten().double().cpu().numpy()
+        for (b, k), v in zip(boot_where, value):
+            tv[b, k] += factors[b, k] * v
+    first = np.stack([np.asarray(t["observations"][s], dtype=np.float32) for t, s in zip(trajectories, start_indices)])
+    f32 = dict(dtype=torch.float32, device=device)
+    return Batch(torch.from_numpy(first).to(device), torch.from_numpy(acts).to(device), torch.tensor(tr, **f32),
+                 torch.tensor(tv, **f32), torch.tensor(tp, **f32))
+
+
+class BatchedTrainer:
+    """`MuZeroAgent`'s optimizer side (main.py:377-379, :381-501) on a batch."""
+
+    def __init__(self, net, action_size, cfg=None):
+        self.net, self.action_size, self.cfg = net, int(action_size), cfg or TrainConfig()
+        self.optimizer = torch.optim.Adam(net.parameters(), lr=self.cfg.learning_rate)
+        self.scheduler = torch.optim.lr_scheduler.StepLR(self.optimizer, step_size=self.cfg.lr_step_size,
+                                                         gamma=self.cfg.lr_gamma)
+
+    @property
+    def device(self):
+        return next(self.net.parameters()).device
+
+    def losses(self, batch):
+        """Per-trajectory step_loss [B] (main.py:396-476) and the three weighted components [B] each."""
+        cfg = self.cfg
+
+        def vloss(value, target):
+            if cfg.use_value_transform:
+                return (reward_value_transform(value) - reward_value_transform(target)) ** 2
+            return (value - target) ** 2
+
+        def ploss(logits, target):                     # F.kl_div(..., reduction='batchmean') at batch size 1
+            return F.kl_div(F.log_softmax(logits, dim=1), target, reduction="none").sum(dim=1)
+
+        latent = representation(self.net, batch.observations)
+        value, logits = prediction(self.net, latent)
+        v = cfg.value_loss_weight * vloss(value.flatten(), batch.target_value[:, 0])
+        p = cfg.policy_loss_weight * ploss(logits, batch.target_policy[:, 0])
+        r = torch.zeros_like(v)
+        for k in range(1, cfg.unroll_steps + 1):
+            latent, reward = dynamics(self.net, latent, batch.actions[:, k - 1])
+            value, logits = prediction(self.net, latent)
+            r = r + cfg.reward_loss_weight * (reward.flatten() - batch.target_reward[:, k - 1]) ** 2
+            v = v + cfg.value_loss_weight * vloss(value.flatten(), batch.target_value[:, k])
+            p = p + cfg.policy_loss_weight * ploss(logits, batch.target_policy[:, k])
+        return v + p + r, {"value": v, "policy": p, "reward": r}
+
+    def train_step(self, batch):
+        """zero_grad, backward of the mean per-trajectory loss, clip_grad_norm_(1.0), Adam step (main.py:394,
+        :478-480).  Returns the per-trajectory losses (detached)."""
+        self.optimizer.zero_grad()
+        per_traj, parts = self.losses(batch)
+        per_traj.mean().backward()
+        torch.nn.utils.clip_grad_norm_(self.net.parameters(), max_norm=self.cfg.max_grad_norm)
+        self.optimizer.step()
+        return per_traj.detach(), {k: v.detach() for k, v in parts.items()}
+
+    def train(self, replay_buffer, batch_size, rng=random):
+        """main.py:381-501: sample, one random start index per trajectory, train, write the batch-average loss
+        back as every sampled trajectory's priority, step the learning-rate schedule.  None if the buffer
+        cannot fill a batch."""
+        batch, indices = replay_buffer.sample(batch_size)
+        if not batch or len(batch) < batch_size:
+            return None
+        starts = [rng.randint(0, len(t["actions"]) - 1) for t in batch]
+        b = build_batch(self.net, batch, starts, self.cfg, self.action_size, self.device)
+        per_traj, parts = self.train_step(b)
+        avg_loss = float(per_traj.sum().item()) / batch_size
+        if indices is not None:
+            replay_buffer.update_priorities(indices, [avg_loss] * len(indices))
+        self.scheduler.step()
+        self.last = {"training_loss": avg_loss, "lr": self.optimizer.param_groups[0]["lr"],
+                     **{k + "_loss": float(v.sum().item()) / batch_size for k, v in parts.items()}}
+        return avg_loss

@@ -195,6 +195,103 @@ def make_mcts(tag, modname, n, sims, seed, mode, plies, c=16, c_puct=None):
           "depth hist", np.bincount(res["sel_depth"]))
 
 
+# --------------------------------------------------------------------------- trainer
+def synthetic_trajectory(n, moves, seed):
+    """A main.py-schema trajectory (main.py:636-711) from a random legal game of the oracle rules: observations
+    (moves + 2: the terminal state is appended twice, :690 and :710), actions, visit-count-like policies,
+    per-move rewards with the winner appended (:709)."""
+    rng = np.random.default_rng(seed)
+    A = n * n + 1
+    st = gymgo.init_state(n)
+    traj = {"observations": [st.copy()], "actions": [], "rewards": [], "policies": []}
+    for _ in range(moves):
+        valid = gymgo.valid_moves(st)
+        counts = rng.integers(0, 40, size=A) * (valid > 0)
+        if counts.sum() == 0:
+            counts = (valid > 0).astype(np.int64)
+        a = int(np.argmax(counts))
+        traj["policies"].append(counts / counts.sum())
+        traj["actions"].append(a)
+        st = gymgo.next_state(st, a)
+        traj["rewards"].append(float(rng.integers(-1, 2)) * 0.25)
+        traj["observations"].append(st.copy())
+        if gymgo.game_ended(st):
+            break
+    traj["rewards"].append(float(gymgo.winning(st)))
+    traj["observations"].append(st.copy())
+    return traj
+
+
+def make_train(tag, n, c, moves, start_index, seed):
+    """The REAL MuZeroAgent.train (main.py:381-501) on a buffer holding one trajectory, batch_size 1, with
+    random.randint patched to `start_index`: the returned avg_loss is that trajectory's step_loss, and the
+    network afterwards has taken one clipped Adam step on it."""
+    main = ref_loader.configure(ref_loader.load("main"), n)
+    A = n * n + 1
+    main.config.latent_dim = c
+    main.device = torch.device("cpu")
+    torch.manual_seed(seed)
+    agent = main.MuZeroAgent(n, c, A, 8)
+    with torch.no_grad():
+        agent.net.prediction.pass_logit.fill_(0.21)
+        agent.net.prediction.value_fc.weight.fill_(0.8)
+    before = {k: v.detach().clone().numpy() for k, v in agent.net.state_dict().items()}
+    traj = synthetic_trajectory(n, moves, seed)
+    rb = main.MultiVersionReplayBuffer(8, 1, True)
+    rb.add(traj)
+    real_randint, real_wandb = main.random.randint, main.wandb
+    main.random.randint = lambda lo, hi: start_index
+    main.wandb = type("NoWandb", (), {"log": staticmethod(lambda *a, **k: None)})     # logging only (main.py:488-500)
+    agent.net.train()
+    try:
+        loss = agent.train(rb, 1)
+    finally:
+        main.random.randint, main.wandb = real_randint, real_wandb
+    after = {k: v.detach().clone().numpy() for k, v in agent.net.state_dict().items()}
+    out = {"n": n, "c": c, "start_index": start_index, "loss": np.float64(loss),
+           "priority_after": np.float64(rb.buffers[0].priorities[0]),
+           "lr_after": np.float64(agent.optimizer.param_groups[0]["lr"]),
+           "observations": np.stack(traj["observations"]), "actions": np.asarray(traj["actions"], dtype=np.int64),
+           "rewards": np.asarray(traj["rewards"], dtype=np.float64), "policies": np.stack(traj["policies"]),
+           "unroll_steps": main.config.unroll_steps, "discount": main.config.discount}
+    for k, v in before.items():
+        out["w0." + k] = v
+    for k, v in after.items():
+        out["w1." + k] = v
+    np.savez_compressed(os.path.join(OUT, f"train_{tag}.npz"), **out)
+    print(f"train_{tag}: T={len(traj['actions'])} start={start_index} loss={loss:.6f}")
+
+
+def make_replay(seed):
+    """Sampling order of the REAL replay buffers (main.py:158-244) under a fixed numpy seed: FIFO eviction,
+    priority updates, multi-version mapping."""
+    main = ref_loader.load("main")
+    np.random.seed(seed)
+    rb = main.MultiVersionReplayBuffer(5, 2, True)
+    log = []
+    for i in range(7):                       # capacity 5: items 0 and 1 are evicted
+        rb.add({"id": i})
+    s, m = rb.sample(3)
+    log.append([x["id"] for x in s] + [b * 100 + l for b, l in m])
+    rb.update_priorities(m, [4.0, 0.5, 2.0])
+    rb.add_version()
+    for i in range(7, 10):
+        rb.add({"id": i})
+    for _ in range(3):
+        s, m = rb.sample(4)
+        log.append([x["id"] for x in s] + [b * 100 + l for b, l in m])
+        rb.update_priorities(m, [0.25] * 4)
+    rb.add_version()                         # deque(maxlen=2): the first version's buffer falls out
+    rb.add({"id": 10})
+    s, m = rb.sample(2)
+    log.append([x["id"] for x in s] + [b * 100 + l for b, l in m])
+    flat = np.full((len(log), 8), -1, dtype=np.int64)
+    for i, row in enumerate(log):
+        flat[i, :len(row)] = row
+    np.savez_compressed(os.path.join(OUT, "replay_sampling.npz"), seed=seed, log=flat)
+    print("replay_sampling:", flat.tolist())
+
+
 def main():
     if not ref_loader.available():
         sys.exit("reference not available here")
@@ -210,6 +307,10 @@ def main():
     make_mcts("main_N5_S300_endgame", "main", 5, 300, seed=15, mode="table", plies=40)
     make_mcts("play_N9_S300_table", "play", 9, 300, seed=16, mode="table", plies=20)
     make_mcts("selfplay_N9_S300_table", "self_play", 9, 300, seed=17, mode="table", plies=20)
+    make_train("N5_C16_mid", 5, 16, 30, start_index=4, seed=20)
+    make_train("N5_C16_tail", 5, 16, 14, start_index=9, seed=21)     # unroll runs past the end of the game
+    make_train("N6_C32_head", 6, 32, 40, start_index=0, seed=22)
+    make_replay(seed=5)
 
 
 if __name__ == "__main__":
