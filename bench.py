@@ -414,6 +414,84 @@ def run_ours(args, wl):
         dist.destroy_process_group()
 
 
+def run_train(args):
+    """Extra line for SURVEY 8(f) rank 1 (not the headline metric): the batched trainer on the reference's own
+    training configuration (main.py:27-37: 6x6 board, C=128, batch of 128 trajectories, K=10 unroll), next to the
+    reference's procedure (one forward / backward / Adam step per trajectory at batch size 1) on the host cores."""
+    import torch
+    import muzero_go_b200 as mz
+    from muzero_go_b200.trainer import build_batch
+    n, C, B, K = 6, LATENT, 128, 10
+    A = n * n + 1
+    dev = torch.device("cuda:0")
+    torch.manual_seed(0)
+    net = mz.MuZeroNet(C, A, precision="bf16").to(dev)
+    T = int(n * n * 1.5)
+    eng = mz.SelfPlayEngine(net, n, 512, 8, search=mz.SearchConfig(seed=3), traj_capacity=T, restart_finished=True)
+    eng.run(T)
+    torch.cuda.synchronize()
+    episodes, _ = mz.episodes_from_rows(eng.trajectory_rows(0, T), n)
+    rb = mz.MultiVersionReplayBuffer(5000, 1, True)
+    for ep in episodes:
+        rb.add(ep)
+    tr = mz.BatchedTrainer(net, A)
+    import random as _random
+    np_seed = 0
+    import numpy as np
+    np.random.seed(np_seed)
+    for _ in range(max(args.warmup, 3)):
+        tr.train(rb, B)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        tr.train(rb, B)                                   # host batch assembly + upload + bootstrap + step
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    batch, _ = rb.sample(B)
+    starts = [_random.randint(0, len(t["actions"]) - 1) for t in batch]
+    bt = build_batch(net, batch, starts, tr.cfg, A, dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    for _ in range(3):
+        tr.train_step(bt)
+    e0.record()
+    for _ in range(args.steps):
+        tr.train_step(bt)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / args.steps
+    flops = 3 * B * (flops_initial(n) + K * flops_recurrent(n))          # forward + backward (dgrad, wgrad)
+    peaks = measured_peaks()
+    cpu = None
+    if not args.no_cpu_baseline:
+        from oracle import nets_ref, train_ref
+        torch.set_num_threads(os.cpu_count() or 1)
+        ref = nets_ref.MuZeroNetRef(C, A)
+        opt = torch.optim.Adam(ref.parameters(), lr=1e-4)
+        done, t0 = 0, time.perf_counter()
+        while time.perf_counter() - t0 < 15.0:
+            traj = batch[done % B]
+            opt.zero_grad()
+            loss, _ = train_ref.trajectory_loss(ref, traj, starts[done % B], A)
+            loss.backward()
+            torch.nn.utils.clip_grad_norm_(ref.parameters(), 1.0)
+            opt.step()
+            done += 1
+        cpu = {"value": done / (time.perf_counter() - t0), "unit": "trajectories/s", "cores": os.cpu_count(), "kind": "port",
+               "sample": "15 s of the reference's procedure (main.py:395-480: forward, backward, clip, Adam per trajectory "
+                         "at batch size 1) with the oracle networks, torch CPU, all cores"}
+    emit({"metric": "training_trajectories_per_sec", "value": B / (ms * 1e-3), "unit": "trajectories/s", "n_gpus": 1,
+          "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+          "vs_baseline": None, "dtype": "f32", "data": "self-play episodes of a random-init network (device engine)",
+          "config": {"workload": "main.py Config: 6x6, batch of 128 trajectories, K=10 unroll, C=128; one optimizer step per batch",
+                     "episodes_in_buffer": len(rb)},
+          "e2e": {"value": B * args.steps / e2e_s, "unit": "trajectories/s", "note": "BatchedTrainer.train: sampling, host batch assembly, "
+                  "upload, bootstrap forward, step"},
+          "roofline": {"bound": "tensor", "kernel": "torch autograd forward + backward (cuDNN fp32/tf32 convolutions; library kernels)",
+                       "achieved": flops / (ms * 1e-3) / 1e12, "peak": peaks["bf16_sustained"], "unit": "TFLOP/s",
+                       "frac": flops / (ms * 1e-3) / 1e12 / peaks["bf16_sustained"], "traffic": None},
+          "cpu_baseline": cpu})
+
+
 _JSON_OUT = None
 
 
@@ -444,10 +522,13 @@ def main():
     ap.add_argument("--games", type=int, default=0)
     ap.add_argument("--sims", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--train", action="store_true", help="extra line: the batched trainer (SURVEY 8(f) rank 1)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
     wl = WORKLOADS[args.workload]
-    if args.impl == "reference":
+    if args.train:
+        run_train(args)
+    elif args.impl == "reference":
         run_reference(args, wl)
     else:
         run_ours(args, wl)
