@@ -13,7 +13,8 @@ from .agent import MuZeroAgent
 from .selfplay import SelfPlayEngine, WaveGroup
 from .replay import MultiVersionReplayBuffer, PrioritizedReplayBuffer, episodes_from_rows, load_episodes, save_episodes
 from .trainer import BatchedTrainer, TrainConfig
+from .arena import ArenaConfig, ArenaEvaluator
 
 __all__ = ["MzgoError", "GoBoards", "GoEnv", "govars", "make", "SearchConfig", "Tree", "MuZeroNet", "MCTS", "WaveGroup",
            "MCTSNode", "MuZeroAgent", "SelfPlayEngine", "MultiVersionReplayBuffer", "PrioritizedReplayBuffer",
-           "episodes_from_rows", "load_episodes", "save_episodes", "BatchedTrainer", "TrainConfig"]
+           "episodes_from_rows", "load_episodes", "save_episodes", "BatchedTrainer", "TrainConfig", "ArenaConfig", "ArenaEvaluator"]

@@ -292,6 +292,35 @@ def make_replay(seed):
     print("replay_sampling:", flat.tolist())
 
 
+def make_arena(seed):
+    """The REAL SelfPlayEvaluator.evaluate (main.py:595-608) with play_game replaced by recorded per-game results:
+    win rate (with the reference's inversion of the odd games) and both Elo ratings over successive calls."""
+    main = ref_loader.load("main")
+    rng = np.random.default_rng(seed)
+    real_wandb = main.wandb
+    main.wandb = type("NoWandb", (), {"log": staticmethod(lambda *a, **k: None)})
+    rows = []
+    try:
+        ev = main.SelfPlayEvaluator(None, None, None, num_games=10)
+        for p in (0.5, 0.9, 0.2, 0.8, 0.95):
+            results = (rng.random(10) < p).astype(np.int64)
+            calls = []
+
+            def fake_play_game(starting_player=0, _r=results, _c=calls):
+                _c.append(starting_player)
+                return int(_r[len(_c) - 1])
+            ev.play_game = fake_play_game
+            wr, elo = ev.evaluate()
+            assert calls == [i % 2 for i in range(10)]
+            rows.append(list(results) + [wr, ev.current_elo, ev.best_elo])
+    finally:
+        main.wandb = real_wandb
+    np.savez_compressed(os.path.join(OUT, "arena_evaluate.npz"), rows=np.asarray(rows, dtype=np.float64),
+                        threshold=main.config.evaluation_win_threshold, elo_k=main.config.elo_k,
+                        initial_elo=main.config.initial_elo)
+    print("arena_evaluate:", [r[10:] for r in rows])
+
+
 def main():
     if not ref_loader.available():
         sys.exit("reference not available here")
@@ -311,6 +340,7 @@ def main():
     make_train("N5_C16_tail", 5, 16, 14, start_index=9, seed=21)     # unroll runs past the end of the game
     make_train("N6_C32_head", 6, 32, 40, start_index=0, seed=22)
     make_replay(seed=5)
+    make_arena(seed=6)
 
 
 if __name__ == "__main__":
