@@ -125,11 +125,24 @@ def build_batch(net, trajectories, start_indices, cfg, action_size, device):
 class BatchedTrainer:
     """`MuZeroAgent`'s optimizer side (main.py:377-379, :381-501) on a batch."""
 
-    def __init__(self, net, action_size, cfg=None):
+    def __init__(self, net, action_size, cfg=None, cuda_graph=None):
+        """cuda_graph (default: on when the network lives on a GPU): a training step is ~1,300 small kernels
+        (11 network evaluations forward and backward on a 6x6 .. 19x19 board), i.e. launch bound; the whole step
+        -- losses, backward, clipping, Adam -- is captured once per batch shape and replayed."""
         self.net, self.action_size, self.cfg = net, int(action_size), cfg or TrainConfig()
-        self.optimizer = torch.optim.Adam(net.parameters(), lr=self.cfg.learning_rate)
-        self.scheduler = torch.optim.lr_scheduler.StepLR(self.optimizer, step_size=self.cfg.lr_step_size,
-                                                         gamma=self.cfg.lr_gamma)
+        on_gpu = next(net.parameters()).is_cuda
+        self.cuda_graph = on_gpu if cuda_graph is None else bool(cuda_graph and on_gpu)
+        if self.cuda_graph:
+            # the captured Adam reads its step size from device memory: StepLR below updates it in place
+            self._lr = torch.tensor(self.cfg.learning_rate, dtype=torch.float64, device=next(net.parameters()).device)
+            self.optimizer = torch.optim.Adam(net.parameters(), lr=self._lr, capturable=True)
+            self.scheduler = None
+        else:
+            self.optimizer = torch.optim.Adam(net.parameters(), lr=self.cfg.learning_rate)
+            self.scheduler = torch.optim.lr_scheduler.StepLR(self.optimizer, step_size=self.cfg.lr_step_size,
+                                                             gamma=self.cfg.lr_gamma)
+        self._sched_calls = 0
+        self._graphs = {}
 
     @property
     def device(self):
@@ -160,15 +173,71 @@ class BatchedTrainer:
             p = p + cfg.policy_loss_weight * ploss(logits, batch.target_policy[:, k])
         return v + p + r, {"value": v, "policy": p, "reward": r}
 
-    def train_step(self, batch):
-        """zero_grad, backward of the mean per-trajectory loss, clip_grad_norm_(1.0), Adam step (main.py:394,
-        :478-480).  Returns the per-trajectory losses (detached)."""
-        self.optimizer.zero_grad()
+    def _step_eager(self, batch):
+        self.optimizer.zero_grad(set_to_none=True)
         per_traj, parts = self.losses(batch)
         per_traj.mean().backward()
         torch.nn.utils.clip_grad_norm_(self.net.parameters(), max_norm=self.cfg.max_grad_norm)
         self.optimizer.step()
         return per_traj.detach(), {k: v.detach() for k, v in parts.items()}
+
+    def _capture(self, batch):
+        """One CUDA graph per batch shape.  The warm-up iterations torch asks for before a capture run on a side
+        stream and are undone afterwards (weights and Adam state restored), so capturing changes nothing."""
+        import copy
+        fields = [f.name for f in dataclasses.fields(Batch)]
+        static = Batch(**{k: getattr(batch, k).clone() for k in fields})
+        net_state = copy.deepcopy(self.net.state_dict())
+        opt_state = copy.deepcopy(self.optimizer.state_dict())
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(3):
+                self._step_eager(static)
+        torch.cuda.current_stream().wait_stream(side)
+        self.net.load_state_dict(net_state)
+        if opt_state["state"]:
+            self.optimizer.load_state_dict(opt_state)
+            self.optimizer.param_groups[0]["lr"] = self._lr    # load_state_dict stores a copy: keep OUR tensor
+        else:
+            # a fresh optimizer: keep the moment buffers the warm-up created and zero them.  They must exist
+            # BEFORE the capture -- created inside it, their zero-fill would be replayed with every step.
+            for st in self.optimizer.state.values():
+                for v in st.values():
+                    if torch.is_tensor(v):
+                        v.zero_()
+        self.optimizer.zero_grad(set_to_none=True)
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            out = self._step_eager(static)
+        return graph, static, out
+
+    def train_step(self, batch):
+        """zero_grad, backward of the mean per-trajectory loss, clip_grad_norm_(1.0), Adam step (main.py:394,
+        :478-480).  Returns the per-trajectory losses (detached)."""
+        if not self.cuda_graph:
+            return self._step_eager(batch)
+        key = tuple(tuple(getattr(batch, f.name).shape) for f in dataclasses.fields(Batch))
+        if key not in self._graphs:
+            self._graphs[key] = self._capture(batch)
+        graph, static, (per_traj, parts) = self._graphs[key]
+        for f in dataclasses.fields(Batch):
+            getattr(static, f.name).copy_(getattr(batch, f.name))
+        graph.replay()
+        return per_traj.clone(), {k: v.clone() for k, v in parts.items()}
+
+    def _schedule(self):
+        """StepLR(step_size, gamma) (main.py:379, :498)."""
+        self._sched_calls += 1
+        if self.scheduler is not None:
+            self.scheduler.step()
+        elif self._sched_calls % self.cfg.lr_step_size == 0:
+            self._lr.mul_(self.cfg.lr_gamma)
+
+    @property
+    def lr(self):
+        lr = self.optimizer.param_groups[0]["lr"]
+        return float(lr.item()) if torch.is_tensor(lr) else float(lr)
 
     def train(self, replay_buffer, batch_size, rng=random):
         """main.py:381-501: sample, one random start index per trajectory, train, write the batch-average loss
@@ -183,7 +252,7 @@ class BatchedTrainer:
         avg_loss = float(per_traj.sum().item()) / batch_size
         if indices is not None:
             replay_buffer.update_priorities(indices, [avg_loss] * len(indices))
-        self.scheduler.step()
-        self.last = {"training_loss": avg_loss, "lr": self.optimizer.param_groups[0]["lr"],
+        self._schedule()
+        self.last = {"training_loss": avg_loss, "lr": self.lr,
                      **{k + "_loss": float(v.sum().item()) / batch_size for k, v in parts.items()}}
         return avg_loss

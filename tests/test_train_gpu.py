@@ -46,3 +46,42 @@ def test_selfplay_to_training_loop():
     torch.cuda.synchronize()
     assert eng2.read_counters()["moves"] == G * T
     assert not torch.equal(eng2.traj_policy, eng.traj_policy)
+
+
+def test_graph_replayed_step_equals_eager_step():
+    """The CUDA-graph-replayed training step (capture once per batch shape, warm-up undone) moves the weights like
+    the eager step does: three steps on fresh batches, same losses and weights to 1e-6; the learning-rate
+    schedule acts on the captured optimizer."""
+    import copy
+    import muzero_go_b200 as mz
+    from muzero_go_b200.trainer import Batch, BatchedTrainer, TrainConfig
+    n, c, B, K = 6, 32, 16, 10
+    A = n * n + 1
+    dev = torch.device("cuda")
+    torch.manual_seed(2)
+    net_a = mz.MuZeroNet(c, A).to(dev)
+    net_b = copy.deepcopy(net_a)
+    cfg = TrainConfig(lr_step_size=2, lr_gamma=0.5)
+    eager, graphed = BatchedTrainer(net_a, A, cfg, cuda_graph=False), BatchedTrainer(net_b, A, cfg, cuda_graph=True)
+    g = torch.Generator(device="cpu").manual_seed(7)
+
+    def batch():
+        pol = torch.rand(B, K + 1, A, generator=g)
+        return Batch((torch.rand(B, 6, n, n, generator=g) < 0.3).float().to(dev), torch.randint(0, A, (B, K), generator=g).to(dev),
+                     (torch.rand(B, K, generator=g) - 0.5).to(dev), (torch.rand(B, K + 1, generator=g) * 2 - 1).to(dev),
+                     (pol / pol.sum(-1, keepdim=True)).to(dev))
+    w0 = [p.detach().clone() for p in net_b.parameters()]
+    for step in range(4):
+        b = batch()
+        la, _ = eager.train_step(b)
+        if step == 0:
+            graphed._graphs[tuple(tuple(getattr(b, f).shape) for f in ("observations", "actions", "target_reward", "target_value", "target_policy"))] = graphed._capture(b)
+            assert all(torch.equal(p, q) for p, q in zip(net_b.parameters(), w0))      # capturing changed nothing
+        lb, _ = graphed.train_step(b)
+        assert torch.allclose(la, lb, rtol=1e-5, atol=1e-6), step
+        for p, q in zip(net_a.parameters(), net_b.parameters()):
+            assert torch.allclose(p, q, rtol=0, atol=2e-6), step
+        eager._schedule()
+        graphed._schedule()
+        assert abs(eager.lr - graphed.lr) < 1e-12
+    assert abs(graphed.lr - 0.25e-4) < 1e-12 and len(graphed._graphs) == 1
