@@ -14,7 +14,8 @@ from .selfplay import SelfPlayEngine, WaveGroup
 from .replay import MultiVersionReplayBuffer, PrioritizedReplayBuffer, episodes_from_rows, load_episodes, save_episodes
 from .trainer import BatchedTrainer, TrainConfig
 from .arena import ArenaConfig, ArenaEvaluator
+from .device_replay import DeviceReplay, train_on_device
 
 __all__ = ["MzgoError", "GoBoards", "GoEnv", "govars", "make", "SearchConfig", "Tree", "MuZeroNet", "MCTS", "WaveGroup",
            "MCTSNode", "MuZeroAgent", "SelfPlayEngine", "MultiVersionReplayBuffer", "PrioritizedReplayBuffer",
-           "episodes_from_rows", "load_episodes", "save_episodes", "BatchedTrainer", "TrainConfig", "ArenaConfig", "ArenaEvaluator"]
+           "episodes_from_rows", "load_episodes", "save_episodes", "BatchedTrainer", "TrainConfig", "ArenaConfig", "ArenaEvaluator", "DeviceReplay", "train_on_device"]

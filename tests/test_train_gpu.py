@@ -85,3 +85,49 @@ def test_graph_replayed_step_equals_eager_step():
         graphed._schedule()
         assert abs(eager.lr - graphed.lr) < 1e-12
     assert abs(graphed.lr - 0.25e-4) < 1e-12 and len(graphed._graphs) == 1
+
+
+def test_device_replay_batch_equals_host_batch():
+    """DeviceReplay (games as padded device tensors, gathers, rules-kernel planes) builds the batch that
+    trainer.build_batch builds from the reference-schema dicts of the same games and start indices: actions,
+    reward targets and policies exactly, value targets to 1e-6 (their bootstrap forward runs in another batch)."""
+    import muzero_go_b200 as mz
+    from muzero_go_b200.device_replay import DeviceReplay, train_on_device
+    from muzero_go_b200.trainer import TrainConfig, build_batch
+    n, c, G, S, T = 5, 16, 20, 10, 38
+    A = n * n + 1
+    torch.manual_seed(6)
+    net = mz.MuZeroNet(c, A).cuda()
+    eng = mz.SelfPlayEngine(net, n, G, S, search=mz.SearchConfig(seed=11), traj_capacity=T, restart_finished=True)
+    eng.run(T)
+    torch.cuda.synchronize()
+    rows = eng.trajectory_rows(0, T)
+    # fed in two pieces: games that straddle the cut are completed by the second call
+    dr = DeviceReplay(64, n, device="cuda")
+    dr.add_rows({k: v[:17] for k, v in rows.items()})
+    dr.add_rows({k: v[17:] for k, v in rows.items()})
+    episodes, _ = mz.episodes_from_rows(rows, n)
+    assert len(dr) == len(episodes) >= G
+    # match the stored games to the host episodes by content (the ring stores them in completion order)
+    key = lambda acts: tuple(int(a) for a in acts)
+    by_actions = {key(ep["actions"]): ep for ep in episodes}
+    slots = torch.arange(len(dr), device="cuda")
+    lengths = dr.length[slots].tolist()
+    eps = [by_actions[key(dr.actions[e, :L].tolist())] for e, L in zip(slots.tolist(), lengths)]
+    cfg = TrainConfig(unroll_steps=10)
+    starts = [0, lengths[1] - 1] + [(7 * i) % L for i, L in enumerate(lengths[2:])]     # first move, last move, others
+    starts_t = torch.tensor(starts, device="cuda")
+    got = dr.build_batch(net, slots, starts_t, cfg)
+    want = build_batch(net, eps, starts, cfg, A, torch.device("cuda"))
+    assert torch.equal(got.observations, want.observations) and torch.equal(got.actions, want.actions)
+    assert torch.equal(got.target_reward, want.target_reward) and torch.equal(got.target_policy, want.target_policy)
+    assert torch.allclose(got.target_value, want.target_value, rtol=0, atol=1e-6)
+    # sampling + a training step entirely on the device
+    tr = mz.BatchedTrainer(net, A, cfg)
+    gen = torch.Generator(device="cuda").manual_seed(3)
+    drawn = dr.sample(8, gen)
+    assert drawn is not None and len(set(drawn[0].tolist())) == 8 and bool((drawn[1] < dr.length[drawn[0]]).all())
+    assert dr.sample(10 ** 6) is None
+    losses = [train_on_device(tr, dr, 8, gen) for _ in range(3)]
+    assert all(np.isfinite(l) for l in losses)
+    assert sorted(set(dr.priority[: len(dr)].tolist())) != [1.0]          # the losses were written back as priorities
