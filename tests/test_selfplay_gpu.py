@@ -204,10 +204,11 @@ def test_games_are_invariant_to_sharding_and_waves():
 
 
 @pytest.mark.parametrize("n,G,S,variant", [(5, 33, 30, "main"), (9, 300, 60, "main"), (9, 64, 60, "self_play"),
-                                           (13, 20, 40, "main"), (19, 151, 12, "main")])
+                                           (13, 20, 40, "main"), (19, 151, 12, "main"), (5, 2000, 6, "main"),
+                                           (13, 700, 5, "self_play")])
 def test_recurrent_tree_equals_separate_calls(n, G, S, variant):
     """mzgo_net_recurrent_tree (network + tree phase in one launch: a warp per game up to 9x9, 128 threads per
-    game above; fewer games than SMs, more games than a CTA has warps) leaves the same trees as
+    game above; fewer games than SMs, more games per CTA than it has warps / 128-thread groups) leaves the same trees as
     select / mzgo_net_recurrent / expand_backup: visit counts, value sums, priors and the chosen moves, bit-exact."""
     import muzero_go_b200 as mz
     from muzero_go_b200 import _lib
