@@ -245,9 +245,9 @@ def run_ours(args, wl):
         for w, rec in enumerate(dev_boards):
             rec.copy_(host_boards[w * GW:(w + 1) * GW], non_blocking=True)
 
-    def boards_down():
+    def boards_down(non_blocking=False):
         for w, rec in enumerate(dev_boards):
-            host_boards[w * GW:(w + 1) * GW].copy_(rec)
+            host_boards[w * GW:(w + 1) * GW].copy_(rec, non_blocking=non_blocking)
 
     boards_down()
     row_bytes = mzdist.pack_rows(group.trajectory_rows(0, 1))
@@ -258,8 +258,8 @@ def run_ours(args, wl):
         boards_up()
         rows = step()
         host_row.copy_(mzdist.pack_rows(rows), non_blocking=True)
-        torch.cuda.synchronize()
-        boards_down()                                        # next step's input comes from the host again
+        boards_down(non_blocking=True)                       # next step's input comes from the host again
+        torch.cuda.synchronize()                             # both read-backs have landed in pinned memory
     barrier()
     e2e_s = time.perf_counter() - t0
     c2 = group.read_counters()
