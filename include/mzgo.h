@@ -327,6 +327,11 @@ int mzgo_search_run(const mzgo_selfplay_t* sp, const uint32_t* choice_stream, in
 long long mzgo_debug_fastdiv_check(unsigned long long seed, int blocks, long long per_thread);
 int mzgo_debug_tc_trace(void* buf /*device*/);
 
+/* mzgo_rules_step / mzgo_rules_playout run a warp per board below this many boards and a thread per board from
+ * it on (board sizes 5, 6, 9, 13, 19; same results bit for bit).  Returns the previous value; a negative
+ * argument only reads it.  Default 32768. */
+int mzgo_debug_rules_tpb_min(int min_boards);
+
 /* Number of searches mzgo_selfplay_run served by replaying its captured CUDA graph of the search loop
  * (the graph is captured on the second move of an engine; MZGO_NO_GRAPH=1 in the environment disables it). */
 long long mzgo_graph_replays(void);

@@ -195,6 +195,8 @@ __device__ uint64_t mzgo_board_hash(const Board& b, int n, int lane) {
     return h;
 }
 
+#include "rules_tpb.cuh"
+
 // ------------------------------------------------------------------------------------------ kernels
 constexpr int WARPS_PER_BLOCK = 4;
 
@@ -368,6 +370,27 @@ k_rules_playout(uint32_t* boards, const uint32_t* R, int T, int32_t* actions_out
 
 extern void mzgo_count_launch();
 
+// From this many boards on, step and playout run a THREAD per board (rules_tpb.cuh); below, a warp per board
+// has more parallelism to offer (1024 self-play games are 1024 warps but only 32 warps of threads).
+static int g_tpb_min = 32768;
+
+extern "C" int mzgo_debug_rules_tpb_min(int min_boards) {
+    const int old = g_tpb_min;
+    if (min_boards >= 0) g_tpb_min = min_boards;
+    return old;
+}
+
+template <int N>
+static void launch_step_tpb(uint32_t* boards, const int32_t* actions, int32_t* status, int nboards, cudaStream_t st) {
+    k_rules_step_tpb<N><<<ceil_div(nboards, TPB_THREADS), TPB_THREADS, 0, st>>>(boards, actions, status, nboards);
+}
+template <int N>
+static void launch_playout_tpb(uint32_t* boards, const uint32_t* R, int T, int32_t* actions_out, uint64_t* hash_out,
+                               int nboards, cudaStream_t st) {
+    k_rules_playout_tpb<N><<<ceil_div(nboards, TPB_THREADS), TPB_THREADS, 0, st>>>(boards, R, T, actions_out, hash_out, nboards);
+}
+static bool tpb_size(int n) { return n == 5 || n == 6 || n == 9 || n == 13 || n == 19; }
+
 static int check_boards(const void* boards, int nboards, int n) {
     MZGO_CHECK_ARG(boards != nullptr, "boards is NULL");
     MZGO_CHECK_ARG(nboards >= 0, "nboards < 0");
@@ -390,7 +413,17 @@ extern "C" int mzgo_rules_step(uint32_t* boards, const int32_t* actions, int32_t
     if (int e = check_boards(boards, nboards, n)) return e;
     MZGO_CHECK_ARG(actions != nullptr, "actions is NULL");
     if (nboards == 0) return MZGO_OK;
-    k_rules_step<<<ceil_div(nboards, WARPS_PER_BLOCK), WARPS_PER_BLOCK * 32, 0, (cudaStream_t)stream>>>(
+    cudaStream_t st = (cudaStream_t)stream;
+    if (nboards >= g_tpb_min && tpb_size(n)) {
+        switch (n) {
+            case 5: launch_step_tpb<5>(boards, actions, status, nboards, st); break;
+            case 6: launch_step_tpb<6>(boards, actions, status, nboards, st); break;
+            case 9: launch_step_tpb<9>(boards, actions, status, nboards, st); break;
+            case 13: launch_step_tpb<13>(boards, actions, status, nboards, st); break;
+            default: launch_step_tpb<19>(boards, actions, status, nboards, st); break;
+        }
+    } else
+    k_rules_step<<<ceil_div(nboards, WARPS_PER_BLOCK), WARPS_PER_BLOCK * 32, 0, st>>>(
         boards, actions, status, nboards, n);
     mzgo_count_launch();
     MZGO_LAUNCH_CHECK();
@@ -443,7 +476,17 @@ extern "C" int mzgo_rules_playout(uint32_t* boards, const uint32_t* R, int T, in
     MZGO_CHECK_ARG(R != nullptr, "R is NULL");
     MZGO_CHECK_ARG(T >= 0, "T < 0");
     if (nboards == 0 || T == 0) return MZGO_OK;
-    k_rules_playout<<<ceil_div(nboards, WARPS_PER_BLOCK), WARPS_PER_BLOCK * 32, 0, (cudaStream_t)stream>>>(
+    cudaStream_t st = (cudaStream_t)stream;
+    if (nboards >= g_tpb_min && tpb_size(n) && !trace_out) {
+        switch (n) {
+            case 5: launch_playout_tpb<5>(boards, R, T, actions_out, hash_out, nboards, st); break;
+            case 6: launch_playout_tpb<6>(boards, R, T, actions_out, hash_out, nboards, st); break;
+            case 9: launch_playout_tpb<9>(boards, R, T, actions_out, hash_out, nboards, st); break;
+            case 13: launch_playout_tpb<13>(boards, R, T, actions_out, hash_out, nboards, st); break;
+            default: launch_playout_tpb<19>(boards, R, T, actions_out, hash_out, nboards, st); break;
+        }
+    } else
+    k_rules_playout<<<ceil_div(nboards, WARPS_PER_BLOCK), WARPS_PER_BLOCK * 32, 0, st>>>(
         boards, R, T, actions_out, hash_out, trace_out, nboards, n);
     mzgo_count_launch();
     MZGO_LAUNCH_CHECK();

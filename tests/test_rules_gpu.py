@@ -56,6 +56,53 @@ def test_config3_full_size_4096_boards():
     assert plies > boards * 300
 
 
+@pytest.fixture
+def thread_per_board():
+    """Route step / playout through the thread-per-board kernels (rules_tpb.cuh) whatever the batch size."""
+    from muzero_go_b200 import _lib
+    lib = _lib.load()
+    old = lib.mzgo_debug_rules_tpb_min(0)
+    yield
+    lib.mzgo_debug_rules_tpb_min(old)
+
+
+@pytest.mark.parametrize("n,boards,T", [(5, 70, 80), (6, 64, 100), (9, 200, 200), (13, 33, 400), (19, 130, 722)])
+def test_thread_per_board_playout_bit_exact(thread_per_board, n, boards, T):
+    """The large-batch kernels: actions, per-ply state hashes, final planes and areas against the C oracle
+    (ragged last block, every supported board size)."""
+    import muzero_go_b200 as mz
+    R = philox_table(300 + n, (boards, T))
+    ref_states = gymgo_fast.init_states(boards, n)
+    plies, ref_actions, _, ref_hash = gymgo_fast.playout(ref_states, R, hashes=True)
+    gb = mz.GoBoards(boards, n).reset()
+    acts, hsh, _ = gb.playout(R, want_hash=True)
+    assert np.array_equal(acts.cpu().numpy(), ref_actions)
+    assert np.array_equal(hsh.cpu().numpy().view(np.uint64), ref_hash)
+    assert np.array_equal(gb.planes(torch.uint8).cpu().numpy(), ref_states)
+    assert plies == int((ref_actions >= 0).sum())
+
+
+def test_thread_per_board_equals_warp_per_board_at_scale(thread_per_board):
+    """65,536 boards of 19x19, 40 plies: the two kernel families leave identical records and actions."""
+    import muzero_go_b200 as mz
+    from muzero_go_b200 import _lib
+    n, boards, T = 19, 65536, 40
+    R = philox_table(9, (boards, T))
+    a = mz.GoBoards(boards, n).reset()
+    acts_a, hash_a, _ = a.playout(R, want_hash=True)
+    _lib.load().mzgo_debug_rules_tpb_min(1 << 30)
+    b = mz.GoBoards(boards, n).reset()
+    acts_b, hash_b, _ = b.playout(R, want_hash=True)
+    assert torch.equal(acts_a, acts_b) and torch.equal(hash_a, hash_b) and torch.equal(a.records, b.records)
+    # one more ply through the step entry point, with some boards left alone and some illegal moves
+    _lib.load().mzgo_debug_rules_tpb_min(0)
+    move = torch.randint(-1, n * n + 1, (boards,), dtype=torch.int32, device="cuda")
+    st_a = a.step(move)
+    _lib.load().mzgo_debug_rules_tpb_min(1 << 30)
+    st_b = b.step(move)
+    assert torch.equal(st_a, st_b) and torch.equal(a.records, b.records) and int((st_a != 0).sum()) > 0
+
+
 def test_step_api_matches_python_oracle_and_reports_errors():
     import muzero_go_b200 as mz
     n, boards = 7, 32
