@@ -328,8 +328,8 @@ long long mzgo_debug_fastdiv_check(unsigned long long seed, int blocks, long lon
 int mzgo_debug_tc_trace(void* buf /*device*/);
 
 /* mzgo_rules_step / mzgo_rules_playout run a warp per board below this many boards and a thread per board from
- * it on (board sizes 5, 6, 9, 13, 19; same results bit for bit).  Returns the previous value; a negative
- * argument only reads it.  Default 32768. */
+ * it on (board sizes 5, 6, 9, where it is the faster one on large batches; 13 and 19 only when the value is 0;
+ * same results bit for bit).  Returns the previous value; a negative argument only reads it.  Default 32768. */
 int mzgo_debug_rules_tpb_min(int min_boards);
 
 /* Number of searches mzgo_selfplay_run served by replaying its captured CUDA graph of the search loop

@@ -389,7 +389,10 @@ static void launch_playout_tpb(uint32_t* boards, const uint32_t* R, int T, int32
                                int nboards, cudaStream_t st) {
     k_rules_playout_tpb<N><<<ceil_div(nboards, TPB_THREADS), TPB_THREADS, 0, st>>>(boards, R, T, actions_out, hash_out, nboards);
 }
-static bool tpb_size(int n) { return n == 5 || n == 6 || n == 9 || n == 13 || n == 19; }
+// Measured on 2^20 mid-game boards, one ply each: 9x9 1.55 -> 0.74 ms, but 19x19 4.1 -> 6.2 ms (254 registers per
+// thread leave 8 warps per SM, and a warp waits for the board with the most groups to classify): by default the
+// thread-per-board kernels serve boards up to 9x9; 13x13 and 19x19 only when the switch is forced to 0 (tests).
+static bool tpb_size(int n) { return n == 5 || n == 6 || n == 9 || (g_tpb_min == 0 && (n == 13 || n == 19)); }
 
 static int check_boards(const void* boards, int nboards, int n) {
     MZGO_CHECK_ARG(boards != nullptr, "boards is NULL");

@@ -2,8 +2,9 @@
 //
 // The warp-per-board kernels of rules.cu spend ~4,400 warp instructions on a 19x19 ply: with one board per
 // warp every shuffle, vote and flood-fill iteration serves one board, and the kernel is issue bound at ~1 % of
-// the HBM bandwidth its 324 B per ply would allow.  For LARGE batches (the playout / step entry points switch
-// over at g_tpb_min boards) a thread owns a whole board instead: the three planes are N rows of uint32 in
+// the HBM bandwidth its 324 B per ply would allow.  For LARGE batches of boards up to 9x9 (the playout / step
+// entry points switch over at g_tpb_min boards; see tpb_size in rules.cu for why not 19x19) a thread owns a whole
+// board instead: the three planes are N rows of uint32 in
 // registers (N is a template parameter, every row loop is unrolled), vertical neighbours are the adjacent array
 // elements, and one warp instruction advances 32 boards.  The arithmetic is the same bit for bit (the same
 // hfill carry trick per row; flood fill sweeps the rows down and up until nothing changes, which reaches the same
