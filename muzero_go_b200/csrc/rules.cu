@@ -68,6 +68,26 @@ __device__ __forceinline__ int count_upto2(uint32_t x) {
     return (row & (row - 1u)) ? 2 : 1;
 }
 
+// flood() that stops as soon as the part of the component found so far has `need` liberties (1 or 2) in `empt`:
+// a component has at least the liberties of any part of it, and callers only ask "none / exactly one / more".
+// Returns min(liberties, 2) of what it returns in *grp -- the whole component unless it stopped early.
+__device__ __forceinline__ int flood_libs(uint32_t seed, uint32_t mask, uint32_t empt, uint32_t bm, int need, int lane,
+                                          uint32_t* grp) {
+    uint32_t g = hfill(seed & mask, mask);
+    int libs;
+    while (true) {
+        const uint32_t lb = dilate4(g, bm, lane) & empt;
+        if (need == 1) libs = __any_sync(FULL_MASK, lb != 0u) ? 1 : 0;
+        else libs = count_upto2(lb);
+        if (libs >= need) break;
+        uint32_t v = (shfl_up0(g, lane) | shfl_dn0(g, lane)) & mask & ~g;
+        if (!__any_sync(FULL_MASK, v != 0u)) break;
+        g = hfill(g | v, mask);
+    }
+    *grp = g;
+    return libs;
+}
+
 // state_utils.compute_invalid_moves(state, player, ko): invalid plane for the NEXT mover.
 // own = stones of `player` (who just moved), opp = stones of the next mover.
 __device__ uint32_t compute_invalid(uint32_t own, uint32_t opp, uint32_t ko_row, int n, int lane) {
@@ -91,8 +111,10 @@ __device__ uint32_t compute_invalid(uint32_t own, uint32_t opp, uint32_t ko_row,
         uint32_t bit;
         int sl = first_point(seeds, &bit);
         int is_own = __shfl_sync(FULL_MASK, (own & bit) != 0u, sl);
-        uint32_t grp = flood(lane == sl ? bit : 0u, is_own ? own : opp, lane);
-        int libs = count_upto2(dilate4(grp, bm, lane) & empt);
+        // only the stones next to a surrounded empty point matter below, and every one of them is a seed: a
+        // group found to have two liberties need not be completed (its other seeds are classified the same way)
+        uint32_t grp;
+        int libs = flood_libs(lane == sl ? bit : 0u, is_own ? own : opp, empt, bm, 2, lane, &grp);
         if (libs == 1) atari |= grp;
         else if (libs > 1) multi |= grp;
         seeds &= ~grp;
@@ -131,9 +153,9 @@ __device__ int board_step(Board& b, int action, int n, int lane) {
         while (__any_sync(FULL_MASK, cand != 0u)) {
             uint32_t bit;
             int sl = first_point(cand, &bit);
-            uint32_t grp = flood(lane == sl ? bit : 0u, opp, lane);
-            uint32_t libs = dilate4(grp, bm, lane) & ~occ;
-            if (!__any_sync(FULL_MASK, libs != 0u)) {
+            uint32_t grp;                     // complete unless a liberty turned up on the way (then it lives)
+            const int libs = flood_libs(lane == sl ? bit : 0u, opp, ~occ & bm, bm, 1, lane, &grp);
+            if (libs == 0) {
                 nkilled++;
                 single = (count_upto2(grp) == 1);
                 single_row = grp;

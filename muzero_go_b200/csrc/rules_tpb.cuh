@@ -52,6 +52,38 @@ __device__ __forceinline__ void t_flood(uint32_t (&g)[N], const uint32_t (&mask)
     }
 }
 
+// t_flood that stops once the part found so far has `need` (1 or 2) liberties in `empt` (see flood_libs in
+// rules.cu).  Returns min(liberties, 2) of what is left in g.
+template <int N>
+__device__ __forceinline__ int t_flood_libs(uint32_t (&g)[N], const uint32_t (&mask)[N], const uint32_t (&empt)[N], int need) {
+#pragma unroll
+    for (int r = 0; r < N; r++) g[r] = hfill(g[r] & mask[r], mask[r]);
+    while (true) {
+        int libs = 0;
+#pragma unroll
+        for (int r = 0; r < N; r++) {
+            uint32_t v = (g[r] << 1) | (g[r] >> 1);
+            if (r > 0) v |= g[r - 1];
+            if (r < N - 1) v |= g[r + 1];
+            libs += __popc(v & empt[r]);
+        }
+        if (libs > 2) libs = 2;
+        if (libs >= need) return libs;
+        bool changed = false;
+#pragma unroll
+        for (int r = 1; r < N; r++) {
+            const uint32_t v = g[r - 1] & mask[r] & ~g[r];
+            if (v) { g[r] = hfill(g[r] | v, mask[r]); changed = true; }
+        }
+#pragma unroll
+        for (int r = N - 2; r >= 0; r--) {
+            const uint32_t v = g[r + 1] & mask[r] & ~g[r];
+            if (v) { g[r] = hfill(g[r] | v, mask[r]); changed = true; }
+        }
+        if (!changed) return libs;
+    }
+}
+
 template <int N>
 __device__ __forceinline__ bool t_any(const uint32_t (&x)[N]) {
     uint32_t o = 0u;
@@ -101,18 +133,16 @@ __device__ __forceinline__ void t_compute_invalid(const uint32_t (&own)[N], cons
     t_dilate4<N>(e1, seeds);
 #pragma unroll
     for (int r = 0; r < N; r++) { seeds[r] &= occ[r]; atari[r] = 0u; multi[r] = 0u; }
-    uint32_t grp[N], mask[N], nb[N];
+    uint32_t grp[N], mask[N], empt[N];
+#pragma unroll
+    for (int r = 0; r < N; r++) empt[r] = ~occ[r] & BM;
     while (t_first_point<N>(seeds, grp)) {
         uint32_t hit_own = 0u;
 #pragma unroll
         for (int r = 0; r < N; r++) hit_own |= own[r] & grp[r];
 #pragma unroll
         for (int r = 0; r < N; r++) mask[r] = hit_own ? own[r] : opp[r];
-        t_flood<N>(grp, mask);
-        t_dilate4<N>(grp, nb);
-#pragma unroll
-        for (int r = 0; r < N; r++) nb[r] &= ~occ[r];
-        const int libs = t_count_upto2<N>(nb);
+        const int libs = t_flood_libs<N>(grp, mask, empt, 2);
 #pragma unroll
         for (int r = 0; r < N; r++) {
             if (libs == 1) atari[r] |= grp[r];
@@ -156,18 +186,14 @@ __device__ __forceinline__ int t_board_step(TBoard<N>& b, int action) {
 #pragma unroll
         for (int r = 0; r < N; r++) open |= adj[r] & ~opp[r];
         const bool surrounded = open == 0u;
-        uint32_t cand[N], kill[N], grp[N], nb[N], single_row[N];
+        constexpr uint32_t BM = (1u << N) - 1u;
+        uint32_t cand[N], kill[N], grp[N], empt[N], single_row[N];
 #pragma unroll
-        for (int r = 0; r < N; r++) { cand[r] = adj[r] & opp[r]; kill[r] = 0u; single_row[r] = 0u; }
+        for (int r = 0; r < N; r++) { cand[r] = adj[r] & opp[r]; kill[r] = 0u; single_row[r] = 0u; empt[r] = ~(own[r] | opp[r]) & BM; }
         int nkilled = 0;
         bool single = false;
         while (t_first_point<N>(cand, grp)) {
-            t_flood<N>(grp, opp);
-            t_dilate4<N>(grp, nb);
-            uint32_t libs = 0u;
-#pragma unroll
-            for (int r = 0; r < N; r++) libs |= nb[r] & ~(own[r] | opp[r]);
-            if (libs == 0u) {
+            if (t_flood_libs<N>(grp, opp, empt, 1) == 0) {
                 nkilled++;
                 single = t_count_upto2<N>(grp) == 1;
 #pragma unroll
