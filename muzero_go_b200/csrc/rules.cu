@@ -104,12 +104,27 @@ __device__ uint32_t compute_invalid(uint32_t own, uint32_t opp, uint32_t ko_row,
     const uint32_t e1 = empt & l & r & u & d;
     if (!__any_sync(FULL_MASK, e1 != 0u)) return occ | ko_row;
 
-    // classify the groups that touch a surrounded empty point: exactly one liberty / more
-    uint32_t seeds = dilate4(e1, bm, lane) & occ;
-    uint32_t atari = 0u, multi = 0u;
-    while (__any_sync(FULL_MASK, seeds != 0u)) {
+    // Classify the stones next to a surrounded empty point p: is p their group's only liberty, or one of several?
+    // A group holding a stone next to an empty point that is NOT surrounded has a liberty other than p, so it has
+    // several: grow those stones through both colours at once (one flood for the whole board instead of one per
+    // group) until every seed is reached or nothing changes.  What is left are groups whose liberties are all
+    // surrounded points (eyes); only those are counted one by one.
+    const uint32_t seeds = dilate4(e1, bm, lane) & occ;
+    const uint32_t open = dilate4(empt & ~e1, bm, lane);
+    uint32_t go = hfill(own & open, own), gp = hfill(opp & open, opp);
+    uint32_t rem = seeds & ~(go | gp);
+    while (__any_sync(FULL_MASK, rem != 0u)) {
+        const uint32_t vo = (shfl_up0(go, lane) | shfl_dn0(go, lane)) & own & ~go;
+        const uint32_t vp = (shfl_up0(gp, lane) | shfl_dn0(gp, lane)) & opp & ~gp;
+        if (!__any_sync(FULL_MASK, (vo | vp) != 0u)) break;
+        go = hfill(go | vo, own);
+        gp = hfill(gp | vp, opp);
+        rem &= ~(go | gp);
+    }
+    uint32_t atari = 0u, multi = go | gp;
+    while (__any_sync(FULL_MASK, rem != 0u)) {
         uint32_t bit;
-        int sl = first_point(seeds, &bit);
+        int sl = first_point(rem, &bit);
         int is_own = __shfl_sync(FULL_MASK, (own & bit) != 0u, sl);
         // only the stones next to a surrounded empty point matter below, and every one of them is a seed: a
         // group found to have two liberties need not be completed (its other seeds are classified the same way)
@@ -117,7 +132,7 @@ __device__ uint32_t compute_invalid(uint32_t own, uint32_t opp, uint32_t ko_row,
         int libs = flood_libs(lane == sl ? bit : 0u, is_own ? own : opp, empt, bm, 2, lane, &grp);
         if (libs == 1) atari |= grp;
         else if (libs > 1) multi |= grp;
-        seeds &= ~grp;
+        rem &= ~grp;
     }
     uint32_t possible = dilate4((own & multi) | (opp & atari), bm, lane);
     uint32_t definite = dilate4((own & atari) | (opp & multi), bm, lane);
@@ -125,19 +140,17 @@ __device__ uint32_t compute_invalid(uint32_t own, uint32_t opp, uint32_t ko_row,
 }
 
 // gogame.next_state.  Returns 0 ok, -1 illegal, -2 game over (board untouched on error).
-__device__ int board_step(Board& b, int action, int n, int lane) {
-    const int np = n * n;
+// The move is (row r, column c), or the pass when r == n (callers that already hold the coordinates skip the division).
+__device__ int board_move(Board& b, int r, int c, int n, int lane) {
     if (b.done) return -2;
-    if (action < 0 || action > np) return -1;
     const uint32_t bm = row_mask(n, lane);
     uint32_t own = b.turn ? b.wh : b.bl;
     uint32_t opp = b.turn ? b.bl : b.wh;
     uint32_t ko_row = 0u;
-    if (action == np) {
+    if (r == n) {
         if (b.pass) b.done = 1;
         b.pass = 1;
     } else {
-        const int r = action / n, c = action - r * n;
         const uint32_t stone = (lane == r) ? (1u << c) : 0u;
         if (__any_sync(FULL_MASK, (b.inv & stone) != 0u)) return -1;
         b.pass = 0;
@@ -147,7 +160,9 @@ __device__ int board_step(Board& b, int action, int n, int lane) {
         // adj_data: every in-board neighbour holds an opponent stone (before captures)
         const int surrounded = !__any_sync(FULL_MASK, (adj & ~opp) != 0u);
         // update_pieces: opponent groups touching the stone with no liberty (measured once)
-        uint32_t cand = adj & opp, kill = 0u;
+        // (a neighbour that itself touches an empty point lives; its group mates, if any are neighbours too, are
+        // then found alive by their own flood)
+        uint32_t cand = adj & opp & ~dilate4(~occ & bm, bm, lane), kill = 0u;
         int nkilled = 0, single = 0;
         uint32_t single_row = 0u;
         while (__any_sync(FULL_MASK, cand != 0u)) {
@@ -172,6 +187,24 @@ __device__ int board_step(Board& b, int action, int n, int lane) {
     b.turn ^= 1;
     b.ply++;
     return 0;
+}
+
+__device__ __forceinline__ int board_step(Board& b, int action, int n, int lane) {
+    if (b.done) return -2;
+    if (action < 0 || action > n * n) return -1;
+    const int r = action / n;           // the pass n*n gives r == n
+    return board_move(b, r, action - r * n, n, lane);
+}
+
+// position of the k-th (0-based) set bit of v; v has more than k set bits
+__device__ __forceinline__ int kth_set_bit(uint32_t v, int k) {
+    int pos = 0;
+#pragma unroll
+    for (int w = 16; w > 0; w >>= 1) {
+        const int c = __popc(v & ((1u << w) - 1u));
+        if (k >= c) { k -= c; pos += w; v >>= w; }
+    }
+    return pos;
 }
 
 __device__ __forceinline__ void board_load(Board& b, const uint32_t* rec, int n, int lane) {
@@ -358,13 +391,13 @@ k_rules_playout(uint32_t* boards, const uint32_t* R, int T, int32_t* actions_out
             int excl = incl - cnt;
             uint32_t hit = __ballot_sync(FULL_MASK, k >= excl && k < incl);
             a = np;
+            int hl = n, col = 0;
             if (hit) {
-                int hl = __ffs(hit) - 1;
-                int col = __fns(valid, 0, k - excl + 1);
-                col = __shfl_sync(FULL_MASK, col, hl);
+                hl = __ffs(hit) - 1;
+                col = __shfl_sync(FULL_MASK, kth_set_bit(valid, (k - excl) & 31), hl);
                 a = hl * n + col;
             }
-            board_step(b, a, n, lane);
+            board_move(b, hl, col, n, lane);
         }
         if (actions_out && lane == 0) actions_out[(size_t)bidx * T + t] = a;
         if (hash_out) {

@@ -129,13 +129,41 @@ __device__ __forceinline__ void t_compute_invalid(const uint32_t (&own)[N], cons
 #pragma unroll
     for (int r = 0; r < N; r++) inv[r] = occ[r] | ko[r];
     if (!t_any<N>(e1)) return;
-    uint32_t seeds[N], atari[N], multi[N];
+    // one flood for the whole board first (see compute_invalid in rules.cu): stones next to an empty point that is
+    // not surrounded, grown through their own colour, are groups with more than one liberty
+    uint32_t seeds[N], atari[N], multi[N], empt[N], grp[N], mask[N];
     t_dilate4<N>(e1, seeds);
 #pragma unroll
-    for (int r = 0; r < N; r++) { seeds[r] &= occ[r]; atari[r] = 0u; multi[r] = 0u; }
-    uint32_t grp[N], mask[N], empt[N];
+    for (int r = 0; r < N; r++) { empt[r] = ~occ[r] & BM; grp[r] = empt[r] & ~e1[r]; }
+    t_dilate4<N>(grp, multi);                                    // multi = points next to a non-surrounded empty point
+    uint32_t rem = 0u;
 #pragma unroll
-    for (int r = 0; r < N; r++) empt[r] = ~occ[r] & BM;
+    for (int r = 0; r < N; r++) {
+        seeds[r] &= occ[r];
+        atari[r] = 0u;
+        multi[r] = hfill(multi[r] & own[r], own[r]) | hfill(multi[r] & opp[r], opp[r]);
+        seeds[r] &= ~multi[r];
+        rem |= seeds[r];
+    }
+    while (rem) {
+        bool changed = false;
+#pragma unroll
+        for (int r = 1; r < N; r++) {
+            const uint32_t vo = multi[r - 1] & own[r - 1] & own[r] & ~multi[r];
+            const uint32_t vp = multi[r - 1] & opp[r - 1] & opp[r] & ~multi[r];
+            if (vo | vp) { multi[r] |= hfill(vo, own[r]) | hfill(vp, opp[r]); changed = true; }
+        }
+#pragma unroll
+        for (int r = N - 2; r >= 0; r--) {
+            const uint32_t vo = multi[r + 1] & own[r + 1] & own[r] & ~multi[r];
+            const uint32_t vp = multi[r + 1] & opp[r + 1] & opp[r] & ~multi[r];
+            if (vo | vp) { multi[r] |= hfill(vo, own[r]) | hfill(vp, opp[r]); changed = true; }
+        }
+        rem = 0u;
+#pragma unroll
+        for (int r = 0; r < N; r++) { seeds[r] &= ~multi[r]; rem |= seeds[r]; }
+        if (!changed) break;
+    }
     while (t_first_point<N>(seeds, grp)) {
         uint32_t hit_own = 0u;
 #pragma unroll
@@ -189,7 +217,10 @@ __device__ __forceinline__ int t_board_step(TBoard<N>& b, int action) {
         constexpr uint32_t BM = (1u << N) - 1u;
         uint32_t cand[N], kill[N], grp[N], empt[N], single_row[N];
 #pragma unroll
-        for (int r = 0; r < N; r++) { cand[r] = adj[r] & opp[r]; kill[r] = 0u; single_row[r] = 0u; empt[r] = ~(own[r] | opp[r]) & BM; }
+        for (int r = 0; r < N; r++) { kill[r] = 0u; single_row[r] = 0u; empt[r] = ~(own[r] | opp[r]) & BM; }
+        t_dilate4<N>(empt, cand);                 // a neighbour that itself touches an empty point lives
+#pragma unroll
+        for (int r = 0; r < N; r++) cand[r] = adj[r] & opp[r] & ~cand[r];
         int nkilled = 0;
         bool single = false;
         while (t_first_point<N>(cand, grp)) {
@@ -308,17 +339,19 @@ k_rules_playout_tpb(uint32_t* boards, const uint32_t* R, int T, int32_t* actions
 #pragma unroll
                 for (int r = 0; r < N; r++) nvalid += __popc(~b.inv[r] & BM);
                 int k = (int)(R[(size_t)bidx * T + t] % (uint32_t)nvalid);
-                a = NP;
                 bool found = false;
+                uint32_t hit_row = 0u;
+                int hr = 0;
 #pragma unroll
                 for (int r = 0; r < N; r++) {
                     const uint32_t valid = ~b.inv[r] & BM;
                     const int c = __popc(valid);
                     if (!found) {
-                        if (k < c) { a = r * N + (int)__fns(valid, 0, k + 1); found = true; }
+                        if (k < c) { hit_row = valid; hr = r; found = true; }
                         else k -= c;
                     }
                 }
+                a = found ? hr * N + kth_set_bit(hit_row, k) : NP;
                 t_board_step<N>(b, a);
             }
             if (actions_out) actions_out[(size_t)bidx * T + t] = a;

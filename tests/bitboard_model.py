@@ -67,7 +67,22 @@ def compute_invalid(own, opp, ko, n):
     if not any(e1):
         return [occ[i] | ko[i] for i in range(32)]
     seeds = [a & b for a, b in zip(dilate4(e1, bm), occ)]
-    atari, multi = [0] * 32, [0] * 32
+    # one flood for the whole board: stones next to a non-surrounded empty point, grown through their own colour
+    opn = dilate4([empt[i] & ~e1[i] & M32 for i in range(32)], bm)
+    go = [hfill(own[i] & opn[i], own[i]) for i in range(32)]
+    gp = [hfill(opp[i] & opn[i], opp[i]) for i in range(32)]
+    rem = [seeds[i] & ~(go[i] | gp[i]) & M32 for i in range(32)]
+    while any(rem):
+        uo, do, up_, dp = shup(go), shdn(go), shup(gp), shdn(gp)
+        vo = [(uo[i] | do[i]) & own[i] & ~go[i] & M32 for i in range(32)]
+        vp = [(up_[i] | dp[i]) & opp[i] & ~gp[i] & M32 for i in range(32)]
+        if not any(vo) and not any(vp):
+            break
+        go = [hfill(go[i] | vo[i], own[i]) for i in range(32)]
+        gp = [hfill(gp[i] | vp[i], opp[i]) for i in range(32)]
+        rem = [rem[i] & ~(go[i] | gp[i]) & M32 for i in range(32)]
+    atari, multi = [0] * 32, [go[i] | gp[i] for i in range(32)]
+    seeds = rem
     while any(seeds):
         l, bit = first_point(seeds)
         is_own = bool(own[l] & bit)
@@ -114,7 +129,8 @@ class Board:
             occ = [a | b for a, b in zip(own, opp)]
             adj = dilate4(stone, bm)
             surrounded = not any(a & ~o & M32 for a, o in zip(adj, opp))
-            cand = [a & o for a, o in zip(adj, opp)]
+            live = dilate4([~o & b & M32 for o, b in zip(occ, bm)], bm)   # next to an empty point: lives
+            cand = [a & o & ~v & M32 for a, o, v in zip(adj, opp, live)]
             kill, nk, single, single_row = [0] * 32, 0, False, [0] * 32
             while any(cand):
                 l, bit = first_point(cand)
