@@ -69,16 +69,19 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([x.strip() for x in line.split(",")])
+            self.rows.append((time.perf_counter(), [x.strip() for x in line.split(",")]))
 
-    def stop(self):
+    def count(self, since):
+        return sum(1 for t, _ in self.rows if t >= since)
+
+    def stop(self, since=0.0):
+        """Summary of the samples read after host time `since` (the GPU has been under the bench load from then on)."""
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
         self.proc.terminate()
         sm, mx, reasons = [], None, set()
-        for r in self.rows:
-            if len(r) < 7:
+        for t, r in self.rows:
+            if len(r) < 7 or t < since:
                 continue
             try:
                 sm.append(float(r[0]))
@@ -215,13 +218,14 @@ def run_ours(args, wl):
             mzdist.gather_trajectories(rows, A)
         return rows
 
+    sampler = ClockSampler(local)
+    sampler.start()                 # nvidia-smi takes longer to start than a short timed region lasts: start it first
+    t_load = time.perf_counter()
     for _ in range(W):
         step()
     barrier()
     lib.mzgo_launch_count(1)
     c0 = group.read_counters()
-    sampler = ClockSampler(local)
-    sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     e0.record()
@@ -230,9 +234,21 @@ def run_ours(args, wl):
     e1.record()
     barrier()
     ms = e0.elapsed_time(e1)
-    clocks = sampler.stop()
     launches = int(lib.mzgo_launch_count(0))
     c1 = group.read_counters()
+    # the same steps keep running, untimed, until nvidia-smi has delivered a few samples under this load (a 9x9 timed
+    # region is ~20 ms, the sampling period 100 ms); the samples span warm-up, the timed steps and these
+    # (the count is a function of the max-over-ranks time so that every rank runs the same number of gathers)
+    ms_all = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(ms_all, op=dist.ReduceOp.MAX)
+    ms_max = float(ms_all.item())
+    extra = 0 if ms_max >= 600.0 else min(2000, int((600.0 - ms_max) / max(ms_max / K, 1e-3)) + 1)
+    for _ in range(extra):
+        step()
+    torch.cuda.synchronize()
+    clocks = sampler.stop(t_load + 0.05)
+    barrier()
     sims_done = c1["simulations"] - c0["simulations"]
     moves_done = c1["moves"] - c0["moves"]
     depth = (c1["leaf_depth_sum"] - c0["leaf_depth_sum"]) / max(1, sims_done)
@@ -253,6 +269,7 @@ def run_ours(args, wl):
     row_bytes = mzdist.pack_rows(group.trajectory_rows(0, 1))
     host_row = torch.empty(row_bytes.shape, dtype=torch.uint8).pin_memory()
     barrier()
+    c1e = group.read_counters()
     t0 = time.perf_counter()
     for _ in range(K):
         boards_up()
@@ -263,7 +280,7 @@ def run_ours(args, wl):
     barrier()
     e2e_s = time.perf_counter() - t0
     c2 = group.read_counters()
-    e2e_sims = c2["simulations"] - c1["simulations"]
+    e2e_sims = c2["simulations"] - c1e["simulations"]
 
     # ---- dominant kernel (recurrent inference of one leaf batch), timed alone with CUDA events
     d = eng.descriptor()

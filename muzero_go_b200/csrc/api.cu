@@ -1,4 +1,5 @@
 // Error plumbing, ABI version, device probe and launch accounting for libmzgo.so.
+#include <stdlib.h>
 #include "common.cuh"
 
 static thread_local char g_err[512] = "";
@@ -14,6 +15,13 @@ void mzgo_set_error(const char* fmt, ...) {
 void mzgo_count_launch() { g_launches++; }
 void mzgo_count_launches(int k) { g_launches += k; }
 int64_t mzgo_launch_count_peek() { return g_launches; }
+
+static int g_pdl = -1;
+bool mzgo_pdl_enabled() {
+    if (g_pdl < 0) g_pdl = getenv("MZGO_NO_PDL") ? 0 : 1;
+    return g_pdl == 1;
+}
+void mzgo_pdl_disable() { g_pdl = 0; }
 
 static unsigned long long g_net_generation = 0;
 unsigned long long mzgo_net_generation() { return g_net_generation; }

@@ -34,6 +34,42 @@ void mzgo_set_error(const char* fmt, ...);
 
 static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 
+// ---- programmatic dependent launch (PDL) ----
+// The kernels of the search loop (tree step, network) run back to back, each consuming what the one before wrote.
+// Launched with the programmatic-serialisation attribute, the next kernel's blocks are scheduled as soon as every
+// block of the running kernel has passed griddep_launch() and SM resources free up, do their private set-up
+// (barriers, TMEM allocation) and then sit in griddep_wait() until the kernel before them has completed and its
+// writes are visible.  Nothing produced by an earlier kernel may be read before griddep_wait().  Both instructions
+// are no-ops in a launch without the attribute.  MZGO_NO_PDL=1 switches the attribute off (A/B measurements).
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void griddep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+bool mzgo_pdl_enabled();
+void mzgo_pdl_disable();
+
+template <typename... KArgs, typename... Args>
+static inline cudaError_t mzgo_launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                                          Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = mzgo_pdl_enabled() ? 1 : 0;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+    if (e != cudaSuccess && cfg.numAttrs) {      // a driver / stream that refuses the attribute: plain launches from now on
+        cudaGetLastError();
+        mzgo_pdl_disable();
+        cfg.numAttrs = 0;
+        e = cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+    }
+    return e;
+}
+
 // ---- warp helpers ----
 __device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }
 

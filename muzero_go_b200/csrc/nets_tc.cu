@@ -687,9 +687,6 @@ k_tc_conv(const __grid_constant__ TcArgs a) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n = a.n, ps = a.ps;
     const int images = a.images_per_group;
-    if (threadIdx.x == 0) tc_stamp(a, 0);
-    // the first group's item records travel while the barriers and the TMEM allocation are set up
-    const TcItems first = tc_load_items(a, tc_items_lo(a), tc_items_hi(a), lane);
     const uint32_t slab_bytes = (uint32_t)KC_IN * ps * 16;
     const uint32_t half_bytes = slab_bytes / NH;
     const int q0 = n + 2;                           // flat position of pixel (0,0)
@@ -705,6 +702,12 @@ k_tc_conv(const __grid_constant__ TcArgs a) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(s_tmem)) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
+    // everything above is private to the CTA; what follows reads what the kernel before this one wrote (PDL, common.cuh)
+    griddep_wait();
+    griddep_launch();
+    if (threadIdx.x == 0) tc_stamp(a, 0);
+    // the first group's item records travel while the set-up above is published to the CTA
+    const TcItems first = tc_load_items(a, tc_items_lo(a), tc_items_hi(a), lane);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -1019,7 +1022,7 @@ int launch_tc_conv(TcArgs& a, int n, int B, cudaStream_t st) {
     a.stages = stages;
     const TcSmemLayout L = tc_smem_layout(n, CIN, COUT, stages, MODE == MODE_DYN);
     const int grid = B < num_sms() ? B : num_sms();
-    k_tc_conv<CIN, COUT, MODE><<<grid, TC_THREADS, L.total, st>>>(a);
+    MZGO_CUDA(mzgo_launch_pdl(k_tc_conv<CIN, COUT, MODE>, dim3(grid), dim3(TC_THREADS), L.total, st, a));
     mzgo_count_launch();
     MZGO_LAUNCH_CHECK();
     return MZGO_OK;

@@ -372,6 +372,8 @@ k_tree_step(mzgo_tree_t t, mzgo_search_params_t p, const float* soft, const floa
     __shared__ StepShared<TPG> sh;
     const int sub = threadIdx.x / TPG, tid = threadIdx.x % TPG;
     const int g = blockIdx.x * GPB + sub;
+    griddep_wait();                              // the network outputs of the launch before (PDL, common.cuh)
+    griddep_launch();
     if (g >= t.G) return;                        // TPG == 128: the whole block; TPG == 32: whole warps
     tree_step_body<TPG, 0>(t, p, soft, reward, value, choice_stream, stride, do_backup, do_select, sh, sub, tid, g, [] {});
 }
@@ -600,11 +602,11 @@ extern "C" int mzgo_tree_step(const mzgo_tree_t* tree, const mzgo_search_params_
     MZGO_CHECK_ARG(p && (!do_backup || (soft && reward && value)), "NULL argument");
     if (tree->G == 0) return MZGO_OK;
     if (tree->A <= STEP_EPT * 32)
-        k_tree_step<32><<<ceil_div(tree->G, STEP_THREADS / 32), STEP_THREADS, 0, st>>>(*tree, *p, soft, reward, value,
-                                                                                      choice_stream, stride, do_backup, do_select);
+        MZGO_CUDA(mzgo_launch_pdl(k_tree_step<32>, dim3(ceil_div(tree->G, STEP_THREADS / 32)), dim3(STEP_THREADS), 0, st, *tree, *p,
+                                  soft, reward, value, choice_stream, stride, do_backup, do_select));
     else
-        k_tree_step<128><<<tree->G, STEP_THREADS, 0, st>>>(*tree, *p, soft, reward, value, choice_stream, stride,
-                                                          do_backup, do_select);
+        MZGO_CUDA(mzgo_launch_pdl(k_tree_step<128>, dim3(tree->G), dim3(STEP_THREADS), 0, st, *tree, *p, soft, reward, value,
+                                  choice_stream, stride, do_backup, do_select));
     mzgo_count_launch();
     MZGO_LAUNCH_CHECK();
     return MZGO_OK;
