@@ -87,6 +87,7 @@ class MuZeroNet(nn.Module):
         self._ws_key = None
         self._desc = None
         self._prepared_key = None
+        self._weights_version = 0
 
     # ------------------------------------------------------------------ descriptor / workspace
     @property
@@ -128,12 +129,19 @@ class MuZeroNet(nn.Module):
         for name, t in zip(_lib.NET_PARAM_FIELDS, params):
             setattr(d, name, t.data_ptr())
         d.workspace, d.workspace_bytes = self._ws.data_ptr(), self._ws.numel()
-        key = tuple((t.data_ptr(), t._version) for t in params) + (self._ws.data_ptr(),)
+        # tensor._version catches eager in-place updates (optimizer.step, load_state_dict, broadcast); a replayed
+        # CUDA graph updates the parameters WITHOUT touching it, hence the explicit counter (mark_weights_changed)
+        key = tuple((t.data_ptr(), t._version) for t in params) + (self._ws.data_ptr(), self._weights_version)
         if key != self._prepared_key:
             _lib.check(_lib.load().mzgo_net_prepare(d, _lib.stream_ptr()))
             self._prepared_key = key
         self._desc = d
         return d
+
+    def mark_weights_changed(self):
+        """Tell the network that its parameters were rewritten behind torch's version counters (a CUDA-graph
+        replay of an optimizer step, a raw-pointer copy): the next forward re-derives the kernel-side layouts."""
+        self._weights_version += 1
 
     def new_arena(self, slots):
         """Zero-initialised latent arena (the zero padding of bf16 slots is never rewritten)."""

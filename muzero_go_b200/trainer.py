@@ -148,6 +148,13 @@ class BatchedTrainer:
     def device(self):
         return next(self.net.parameters()).device
 
+    def _weights_changed(self):
+        # a replayed graph rewrites the parameters without bumping tensor._version: tell the network explicitly, so the
+        # next self-play / arena forward re-derives its kernel-side weight layouts (MuZeroNet.descriptor)
+        mark = getattr(self.net, "mark_weights_changed", None)
+        if mark is not None:
+            mark()
+
     def losses(self, batch):
         """Per-trajectory step_loss [B] (main.py:396-476) and the three weighted components [B] each."""
         cfg = self.cfg
@@ -179,6 +186,7 @@ class BatchedTrainer:
         per_traj.mean().backward()
         torch.nn.utils.clip_grad_norm_(self.net.parameters(), max_norm=self.cfg.max_grad_norm)
         self.optimizer.step()
+        self._weights_changed()
         return per_traj.detach(), {k: v.detach() for k, v in parts.items()}
 
     def _capture(self, batch):
@@ -188,7 +196,10 @@ class BatchedTrainer:
         fields = [f.name for f in dataclasses.fields(Batch)]
         static = Batch(**{k: getattr(batch, k).clone() for k in fields})
         net_state = copy.deepcopy(self.net.state_dict())
-        opt_state = copy.deepcopy(self.optimizer.state_dict())
+        # Adam's moments are restored IN PLACE: graphs captured earlier for other batch shapes hold the addresses of
+        # these very tensors (optimizer.load_state_dict would swap in new objects and leave them updating freed memory)
+        opt_saved = {p: {k: (v.clone() if torch.is_tensor(v) else v) for k, v in st.items()}
+                     for p, st in self.optimizer.state.items()}
         side = torch.cuda.Stream()
         side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(side):
@@ -196,16 +207,17 @@ class BatchedTrainer:
                 self._step_eager(static)
         torch.cuda.current_stream().wait_stream(side)
         self.net.load_state_dict(net_state)
-        if opt_state["state"]:
-            self.optimizer.load_state_dict(opt_state)
-            self.optimizer.param_groups[0]["lr"] = self._lr    # load_state_dict stores a copy: keep OUR tensor
-        else:
-            # a fresh optimizer: keep the moment buffers the warm-up created and zero them.  They must exist
-            # BEFORE the capture -- created inside it, their zero-fill would be replayed with every step.
-            for st in self.optimizer.state.values():
-                for v in st.values():
-                    if torch.is_tensor(v):
-                        v.zero_()
+        for p, st in self.optimizer.state.items():
+            saved = opt_saved.get(p)
+            for k, v in st.items():
+                if not torch.is_tensor(v):
+                    continue
+                if saved is not None and k in saved:
+                    v.copy_(saved[k])
+                else:
+                    # a fresh optimizer: keep the moment buffers the warm-up created and zero them.  They must exist
+                    # BEFORE the capture -- created inside it, their zero-fill would be replayed with every step.
+                    v.zero_()
         self.optimizer.zero_grad(set_to_none=True)
         graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(graph):
@@ -224,6 +236,7 @@ class BatchedTrainer:
         for f in dataclasses.fields(Batch):
             getattr(static, f.name).copy_(getattr(batch, f.name))
         graph.replay()
+        self._weights_changed()
         return per_traj.clone(), {k: v.clone() for k, v in parts.items()}
 
     def _schedule(self):

@@ -130,6 +130,19 @@ class Tree:
         _lib.check(_lib.load().mzgo_tree_expand_backup(self.desc, cfg.to_struct(), _lib.ptr(soft), _lib.ptr(reward),
                                                        _lib.ptr(value), _lib.stream_ptr()))
 
+    # ---- the fused per-simulation step the engine launches (mzgo_tree_step): expansion + backup of the leaf the
+    # previous step selected, then the next selection
+    def step(self, cfg, soft, reward, value, choice_stream=None, do_backup=True, do_select=True):
+        for t in (soft, reward, value):
+            assert t.dtype == torch.float32 and t.is_contiguous() and t.device == self.device
+        stride = 0
+        if choice_stream is not None:
+            assert choice_stream.dtype == torch.int32 and choice_stream.is_contiguous()
+            stride = choice_stream.shape[1]
+        _lib.check(_lib.load().mzgo_tree_step(self.desc, cfg.to_struct(), _lib.ptr(soft), _lib.ptr(reward),
+                                              _lib.ptr(value), _lib.ptr(choice_stream), stride, int(bool(do_backup)),
+                                              int(bool(do_select)), _lib.stream_ptr()))
+
     # ---- main.py:666-669
     def visit_counts(self):
         out = torch.empty((self.G, self.A), dtype=torch.int32, device=self.device)

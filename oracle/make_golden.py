@@ -38,7 +38,10 @@ def midgame_obs(n, plies, seed):
 
 
 # --------------------------------------------------------------------------- nets
-def make_nets(n, c, batch, seed):
+def make_nets(n, c, batch, seed, weight_scale=1.0, emb_scale=1.0, tag=""):
+    """weight_scale / emb_scale: every parameter times weight_scale, then the action embedding times emb_scale
+    (after the pass_logit fill).  The default init leaves latents and head outputs close to zero; the scaled
+    fixtures pin the kernels where activations are O(1)."""
     main = ref_loader.configure(ref_loader.load("main"), n)
     A = n * n + 1
     torch.manual_seed(seed)
@@ -46,6 +49,10 @@ def make_nets(n, c, batch, seed):
     # move biases / pass_logit / fc weights off their degenerate init so every term is exercised
     with torch.no_grad():
         net.prediction.pass_logit.fill_(0.37)
+        if weight_scale != 1.0 or emb_scale != 1.0:
+            for p in net.parameters():
+                p.mul_(weight_scale)
+            net.dynamics.action_embedding.weight.mul_(emb_scale)
     obs = np.stack([midgame_obs(n, 5 + 7 * i, seed + i) for i in range(batch)]).astype(np.float32)
     rng = np.random.default_rng(seed)
     actions = rng.integers(0, A, size=batch).astype(np.int64)
@@ -59,8 +66,8 @@ def make_nets(n, c, batch, seed):
     checksum = float(sum(v.double().sum() for v in sd.values()))
     abs_checksum = float(sum(v.double().abs().sum() for v in sd.values()))
     np.savez_compressed(
-        os.path.join(OUT, f"nets_N{n}_C{c}.npz"),
-        n=n, c=c, seed=seed, pass_logit=0.37, obs=obs, actions=actions,
+        os.path.join(OUT, f"nets_N{n}_C{c}{tag}.npz"),
+        n=n, c=c, seed=seed, pass_logit=0.37, weight_scale=weight_scale, emb_scale=emb_scale, obs=obs, actions=actions,
         weight_sum=checksum, weight_abs_sum=abs_checksum,
         latent=latent.numpy(), value=value.numpy(), logits=logits.numpy(),
         next_latent=nxt.numpy(), reward=reward.numpy(), value2=value2.numpy(), logits2=logits2.numpy(),
@@ -159,7 +166,7 @@ def run_reference_mcts(modname, n, sims, obs, net, noise, stream, c_puct=None):
                 dirichlet_epsilon=cfg.dirichlet_epsilon, pass_epsilon=cfg.pass_epsilon)
 
 
-def make_mcts(tag, modname, n, sims, seed, mode, plies, c=16, c_puct=None):
+def make_mcts(tag, modname, n, sims, seed, mode, plies, c=16, c_puct=None, logit_scale=2.0, value_scale=0.5):
     A = n * n + 1
     rng = np.random.default_rng(seed)
     obs = midgame_obs(n, plies, seed)
@@ -167,9 +174,9 @@ def make_mcts(tag, modname, n, sims, seed, mode, plies, c=16, c_puct=None):
     stream = rng.integers(0, 2 ** 32, size=sims + 8, dtype=np.uint64).astype(np.uint32)
     if mode == "table":
         init_logits = rng.normal(0, 1.5, A).astype(np.float32)
-        logits = rng.normal(0, 2.0, (sims, A)).astype(np.float32)
+        logits = rng.normal(0, logit_scale, (sims, A)).astype(np.float32)
         rewards = rng.normal(0, 0.1, sims).astype(np.float32)
-        values = rng.normal(0, 0.5, sims).astype(np.float32)
+        values = rng.normal(0, value_scale, sims).astype(np.float32)
         net = TableNet(init_logits, logits, rewards, values)
         res = run_reference_mcts(modname, n, sims, obs, net, noise, stream, c_puct)
     else:  # a real random-init reference net, outputs recorded
@@ -328,6 +335,8 @@ def main():
     make_nets(9, 128, 4, seed=0)
     make_nets(19, 128, 2, seed=1)
     make_nets(6, 32, 3, seed=2)
+    make_nets(9, 128, 3, seed=3, weight_scale=1.7, emb_scale=0.3, tag="_scaled")
+    make_nets(19, 128, 2, seed=4, weight_scale=1.7, emb_scale=0.3, tag="_scaled")
     make_mcts("main_N9_S50_table", "main", 9, 50, seed=10, mode="table", plies=12)
     make_mcts("main_N9_S800_table", "main", 9, 800, seed=11, mode="table", plies=30)
     make_mcts("main_N9_S400_net", "main", 9, 400, seed=12, mode="net", plies=8)
@@ -336,6 +345,11 @@ def main():
     make_mcts("main_N5_S300_endgame", "main", 5, 300, seed=15, mode="table", plies=40)
     make_mcts("play_N9_S300_table", "play", 9, 300, seed=16, mode="table", plies=20)
     make_mcts("selfplay_N9_S300_table", "self_play", 9, 300, seed=17, mode="table", plies=20)
+    # 19x19 below the root's children (k_tree_step<128>'s deeper-level loop at A = 362): a late position with few
+    # legal points and peaked policies
+    make_mcts("main_N19_S600_deep", "main", 19, 600, seed=18, mode="table", plies=300, logit_scale=4.0, value_scale=1.0)
+    make_mcts("selfplay_N19_S450_deep", "self_play", 19, 450, seed=19, mode="table", plies=280, logit_scale=4.0,
+              value_scale=1.0)
     make_train("N5_C16_mid", 5, 16, 30, start_index=4, seed=20)
     make_train("N5_C16_tail", 5, 16, 14, start_index=9, seed=21)     # unroll runs past the end of the game
     make_train("N6_C32_head", 6, 32, 40, start_index=0, seed=22)

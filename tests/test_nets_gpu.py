@@ -1,7 +1,17 @@
 """GPU: representation / dynamics / prediction networks through the C ABI against the golden outputs of
 the real reference MuZeroNet (tests/golden/nets_*.npz) and against the torch oracle on fresh inputs.
-Tolerances are north_star's: fp32 mode 1e-5, bf16 mode 1e-2 relative."""
+
+Tolerances (north_star: "within 1e-2 relative (bf16) and 1e-5 (fp32 mode)"), stated precisely:
+  fp32 mode  element-wise |got - want| <= 1e-5 * |want| + 1e-5                      (numpy assert_allclose)
+  bf16 mode  (a) tensor-max norm: max|got - want| <= 1e-2 * max|want|               (`rel_err`)
+             (b) element-wise:    |got - want| <= 1e-2 * |want| + 2^-4 * 1e-2 * max|want|      (`elem_excess` <= 1)
+             (b) bounds small entries too: an output that is a 1152-term bf16 dot product carries an absolute error
+             proportional to the tensor's scale, not to the entry, so a purely relative element-wise bound cannot hold
+             for entries near zero (ReLU outputs, logits crossing zero); 2^-4 of the tensor-level budget is the floor.
+The achieved errors of every fixture are appended to gpurun_out/nets_errors.json (copied to profiles/ per round).
+"""
 import glob
+import json
 import os
 
 import numpy as np
@@ -15,13 +25,17 @@ GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 FIXTURES = sorted(glob.glob(os.path.join(GOLDEN, "nets_*.npz")))
 
 
-def build_pair(n, c, seed, pass_logit, precision):
+def build_pair(n, c, seed, pass_logit, precision, weight_scale=1.0, emb_scale=1.0):
     import muzero_go_b200 as mz
     A = n * n + 1
     torch.manual_seed(seed)
     ref = MuZeroNetRef(c, A).eval()
     with torch.no_grad():
         ref.prediction.pass_logit.fill_(pass_logit)
+        if weight_scale != 1.0 or emb_scale != 1.0:      # the *_scaled fixtures (oracle/make_golden.py:make_nets)
+            for p in ref.parameters():
+                p.mul_(weight_scale)
+            ref.dynamics.action_embedding.weight.mul_(emb_scale)
     net = mz.MuZeroNet(c, A, precision=precision)
     net.load_state_dict(ref.state_dict())
     return ref, net.cuda().eval()
@@ -32,14 +46,45 @@ def close(got, want, rtol, atol, name):
 
 
 def rel_err(got, want):
+    """Tensor-max relative error: max|got - want| / max|want|."""
     got, want = got.detach().cpu().double().numpy(), np.asarray(want, dtype=np.float64)
     return float(np.abs(got - want).max() / (np.abs(want).max() + 1e-12))
+
+
+def elem_excess(got, want, rtol=1e-2, floor=2.0 ** -4):
+    """max over elements of |got - want| / (rtol * |want| + floor * rtol * max|want|); <= 1 passes."""
+    got, want = got.detach().cpu().double().numpy(), np.asarray(want, dtype=np.float64)
+    bound = rtol * np.abs(want) + floor * rtol * (np.abs(want).max() + 1e-12)
+    return float((np.abs(got - want) / bound).max())
+
+
+def fixture_pair(g, precision):
+    ws = float(g["weight_scale"]) if "weight_scale" in g else 1.0
+    es = float(g["emb_scale"]) if "emb_scale" in g else 1.0
+    return build_pair(int(g["n"]), int(g["c"]), int(g["seed"]), float(g["pass_logit"]), precision, ws, es)
+
+
+def record_errors(name, errs):
+    """Append the achieved errors to gpurun_out/nets_errors.json (scratch; summarised under profiles/)."""
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    path = os.environ.get("MZGO_NETS_ERRORS", os.path.join(root, "gpurun_out", "nets_errors.json"))
+    try:
+        os.makedirs(os.path.dirname(path), exist_ok=True)
+        data = {}
+        if os.path.exists(path):
+            with open(path) as fh:
+                data = json.load(fh)
+        data[name] = errs
+        with open(path, "w") as fh:
+            json.dump(data, fh, indent=1, sort_keys=True)
+    except OSError:
+        pass
 
 
 @pytest.mark.parametrize("path", FIXTURES, ids=os.path.basename)
 def test_fp32_mode_matches_reference_golden(path):
     g = np.load(path)
-    _, net = build_pair(int(g["n"]), int(g["c"]), int(g["seed"]), float(g["pass_logit"]), "fp32")
+    _, net = fixture_pair(g, "fp32")
     obs, actions = torch.from_numpy(g["obs"]).cuda(), torch.from_numpy(g["actions"]).cuda()
     latent, value, logits = net.initial_inference(obs)
     tol = dict(rtol=1e-5, atol=1e-5)
@@ -69,18 +114,20 @@ def test_fp32_mode_matches_reference_golden(path):
 @pytest.mark.parametrize("path", [p for p in FIXTURES if "_C128" in p], ids=os.path.basename)
 def test_bf16_mode_within_1e2_of_reference_golden(path):
     g = np.load(path)
-    _, net = build_pair(int(g["n"]), int(g["c"]), int(g["seed"]), float(g["pass_logit"]), "bf16")
+    _, net = fixture_pair(g, "bf16")
     obs, actions = torch.from_numpy(g["obs"]).cuda(), torch.from_numpy(g["actions"]).cuda()
     latent, value, logits = net.initial_inference(obs)
     nxt, reward, value2, logits2 = net.recurrent_inference(latent, actions)
     _, reward3, value3, logits3 = net.recurrent_inference(nxt, actions.flip(0))
-    errs = {"latent": rel_err(latent, g["latent"]), "value": rel_err(value, g["value"]),
-            "logits": rel_err(logits, g["logits"]), "next_latent": rel_err(nxt, g["next_latent"]),
-            "reward": rel_err(reward, g["reward"]), "value2": rel_err(value2, g["value2"]),
-            "logits2": rel_err(logits2, g["logits2"]), "reward3": rel_err(reward3, g["reward3"]),
-            "value3": rel_err(value3, g["value3"]), "logits3": rel_err(logits3, g["logits3"])}
-    print(errs)
-    assert max(errs.values()) < 1e-2, errs      # 1e-2 relative to the tensor's scale (north_star, bf16)
+    pairs = {"latent": latent, "value": value, "logits": logits, "next_latent": nxt, "reward": reward, "value2": value2,
+             "logits2": logits2, "reward3": reward3, "value3": value3, "logits3": logits3}
+    errs = {k: rel_err(v, g[k]) for k, v in pairs.items()}
+    excess = {k: elem_excess(v, g[k]) for k, v in pairs.items()}
+    print(errs, excess)
+    record_errors("bf16_golden/" + os.path.basename(path), {"tensor_max_rel": errs, "elementwise_excess": excess,
+                                                            "scale": {k: float(np.abs(g[k]).max()) for k in pairs}})
+    assert max(errs.values()) < 1e-2, errs          # (a) 1e-2 relative to the tensor's scale (north_star, bf16)
+    assert max(excess.values()) <= 1.0, excess      # (b) element-wise, see the module docstring
 
 
 @pytest.mark.parametrize("n,c,precision,tol", [(9, 128, "fp32", 1e-5), (19, 128, "fp32", 1e-5), (5, 16, "fp32", 1e-5),
@@ -108,4 +155,5 @@ def test_random_batches_match_torch_oracle(n, c, precision, tol):
             "next_latent": rel_err(nxt, rn), "reward": rel_err(reward, rr), "value2": rel_err(value2, rv2),
             "logits2": rel_err(logits2, rlog2)}
     print(precision, n, c, errs)
+    record_errors(f"random_batches/{precision}_N{n}_C{c}", {"tensor_max_rel": errs})
     assert max(errs.values()) < tol, errs

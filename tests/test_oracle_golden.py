@@ -19,6 +19,12 @@ def build_ref_net(g):
     net = MuZeroNetRef(int(g["c"]), int(g["n"]) ** 2 + 1).eval()
     with torch.no_grad():
         net.prediction.pass_logit.fill_(float(g["pass_logit"]))
+        ws = float(g["weight_scale"]) if "weight_scale" in g else 1.0
+        es = float(g["emb_scale"]) if "emb_scale" in g else 1.0
+        if ws != 1.0 or es != 1.0:               # the *_scaled fixtures (oracle/make_golden.py:make_nets)
+            for p in net.parameters():
+                p.mul_(ws)
+            net.dynamics.action_embedding.weight.mul_(es)
     return net
 
 

@@ -133,7 +133,8 @@ def test_engine_invariants(n, c, G, S, precision):
 
 @pytest.mark.parametrize("n,c,G,S,precision,variant", [(5, 16, 16, 10, "fp32", "main"), (5, 128, 16, 40, "bf16", "main"),
                                                        (9, 128, 150, 120, "bf16", "main"), (9, 128, 40, 100, "bf16", "self_play"),
-                                                       (13, 128, 9, 200, "bf16", "main"), (19, 128, 150, 24, "bf16", "main")])
+                                                       (13, 128, 9, 200, "bf16", "main"), (19, 128, 150, 24, "bf16", "main"),
+                                                       (19, 128, 5, 430, "bf16", "main")])
 def test_engine_equals_stepwise_api(n, c, G, S, precision, variant):
     """mzgo_selfplay_run is the composition of the exported pieces: same seed => same moves as driving
     net/tree/rules call by call from Python.  The engine runs the fused tree-step kernel and replays the search
@@ -146,6 +147,9 @@ def test_engine_equals_stepwise_api(n, c, G, S, precision, variant):
     eng = mz.SelfPlayEngine(net, n, G, S, search=cfg, traj_capacity=6, restart_finished=True)
     eng.run(6)
     torch.cuda.synchronize()
+    if S > n * n + 1:        # more simulations than root edges: the compared searches reach below the root's children
+        ctr = eng.read_counters()
+        assert ctr["leaf_depth_sum"] > ctr["simulations"] + 6 * G * 20, ctr
     # step by step
     A, M = n * n + 1, S + 1
     dev = torch.device("cuda")
@@ -205,7 +209,7 @@ def test_games_are_invariant_to_sharding_and_waves():
 
 @pytest.mark.parametrize("n,G,S,variant", [(5, 33, 30, "main"), (9, 300, 60, "main"), (9, 64, 60, "self_play"),
                                            (13, 20, 40, "main"), (19, 151, 12, "main"), (5, 2000, 6, "main"),
-                                           (13, 700, 5, "self_play")])
+                                           (13, 700, 5, "self_play"), (19, 6, 440, "main"), (19, 4, 420, "self_play")])
 def test_recurrent_tree_equals_separate_calls(n, G, S, variant):
     """mzgo_net_recurrent_tree (network + tree phase in one launch: a warp per game up to 9x9, 128 threads per
     game above; fewer games than SMs, more games per CTA than it has warps / 128-thread groups) leaves the same trees as
@@ -247,8 +251,76 @@ def test_recurrent_tree_equals_separate_calls(n, G, S, variant):
 
     ta, aa, pa, va = search(True)
     tb, ab, pb, vb = search(False)
+    if S > A:
+        assert int(ta.depth_sum.sum()) > int(ta.sims_done.sum()) + G * 20      # leaves below the root's children
     assert torch.equal(aa, ab) and torch.equal(pa, pb) and torch.equal(va, vb)
     for name in ("edge_visit", "edge_vsum", "child", "root_visit", "root_vsum", "n_nodes", "sims_done", "depth_sum"):
         assert torch.equal(getattr(ta, name), getattr(tb, name)), name
     # (node 0's float32 prior row is the fused step's path scratch: the root's priors are the float64 root_prior)
     assert torch.equal(ta.prior[:, 1:], tb.prior[:, 1:]) and torch.equal(ta.root_prior, tb.root_prior)
+
+
+@pytest.mark.parametrize("n,c,S,G,precision,variant", [
+    (19, 128, 450, 3, "bf16", "main"),        # k_tree_step<128> + k_tc_conv, two launches per simulation (the headline path)
+    (19, 128, 430, 2, "bf16", "self_play"),
+    (9, 128, 400, 3, "bf16", "main"),         # mzgo_net_recurrent_tree: the tree phase of the network kernel
+    (9, 128, 300, 2, "bf16", "self_play"),
+    (13, 128, 300, 2, "bf16", "main"),
+    (19, 32, 430, 2, "fp32", "main"),         # fp32 networks + k_tree_step<128>
+])
+def test_engine_search_matches_oracle_search_below_the_root(n, c, S, G, precision, variant):
+    """mzgo_search_run -- exactly what mzgo_selfplay_run enqueues for a move: the fused tree step / the network
+    kernel with its tree phase -- against the ORACLE search (oracle/mcts_ref.py, pinned to the real reference MCTS)
+    at simulation counts that take the leaves below the root's children (19x19 needs > 362 simulations for that).
+    Both sides consume identical float32 network outputs: the oracle's callbacks evaluate our network on the
+    single item (bf16 latents round-trip exactly through the float32 export), with injected Dirichlet noise and
+    random.choice streams.  G different positions in one batch.  Bit-exact: root priors, visit counts, value sums
+    of the root's children, leaf depths in order, dropped simulations, node counts."""
+    import muzero_go_b200 as mz
+    from muzero_go_b200 import _lib
+    from oracle.make_golden import midgame_obs
+    A = n * n + 1
+    dev = torch.device("cuda")
+    _, net = make_net(n, c, 31, precision)
+    cfg = mz.SearchConfig.for_variant(variant, seed=4)
+    rng = np.random.default_rng(n * 1000 + S)
+    obs = [midgame_obs(n, int(rng.integers(n * n // 3, n * n)), int(rng.integers(1 << 30))) for _ in range(G)]
+    noise = np.stack([rng.dirichlet([0.3] * A) for _ in range(G)])
+    streams = rng.integers(0, 2 ** 32, size=(G, S + 8), dtype=np.uint64).astype(np.uint32)
+    eng = mz.SelfPlayEngine(net, n, G, S, search=cfg, restart_finished=False, traj_capacity=1)
+    obs_t = torch.from_numpy(np.stack(obs).astype(np.float32)).to(dev)
+    eng.boards.load_planes(obs_t)
+    d = eng.descriptor()
+    L, s = _lib.load(), _lib.stream_ptr()
+    roots = (torch.arange(G, dtype=torch.int32, device=dev) * eng.M).contiguous()
+    eng.tree.active.fill_(1)
+    _lib.check(L.mzgo_net_initial(d.net, _lib.ptr(obs_t), None, _lib.ptr(eng.arena), _lib.ptr(roots),
+                                  _lib.ptr(eng.root_value_net), _lib.ptr(eng.root_policy), 1, G, s))
+    eng.tree.reset_roots(cfg, eng.root_policy, eng.boards, n, noise=noise, move_index=0)
+    stream_t = mz.Tree.stream_tensor(streams, dev)
+    _lib.check(L.mzgo_search_run(d, _lib.ptr(stream_t), stream_t.shape[1], s))
+    torch.cuda.synchronize()
+    t = eng.tree
+    vc = t.visit_counts().cpu().numpy()
+
+    def initial(o):
+        lat, v, p = net._run_initial(torch.from_numpy(np.asarray(o, dtype=np.float32))[None].cuda(), want_softmax=True)
+        return lat, v.cpu().numpy().reshape(-1)[0], p.cpu().numpy()[0]
+
+    def recurrent(lat, a):
+        nxt, r, v, p = net._run_recurrent(lat, torch.tensor([a]).cuda(), want_softmax=True)
+        return nxt, r.cpu().numpy().reshape(-1)[0], v.cpu().numpy().reshape(-1)[0], p.cpu().numpy()[0]
+
+    run_ref = mcts_ref.run_mcts_selfplay if variant == "self_play" else mcts_ref.run_mcts
+    deepest = 0
+    for k in range(G):
+        ref, mask = run_ref(obs[k], initial, recurrent, S, noise[k], streams[k], c_puct=cfg.c_puct, discount=cfg.discount,
+                            dirichlet_epsilon=cfg.dirichlet_epsilon, pass_epsilon=cfg.pass_epsilon)
+        assert np.array_equal(t.root_prior[k].cpu().numpy(), np.asarray(ref.prior[0], dtype=np.float64)), k
+        assert np.array_equal(vc[k], ref.root_visit_counts(mask)), k
+        assert np.array_equal(t.edge_vsum[k, 0].cpu().numpy(), ref.root_child_value_sums()), k
+        assert int(t.root_visit[k]) == ref.visit[0] and int(t.dropped[k]) == ref.dropped, k
+        assert int(t.n_nodes[k]) == len(ref.visit), k
+        assert int(t.depth_sum[k]) == sum(ref.depths) and int(t.sims_done[k]) == len(ref.depths), k
+        deepest = max(deepest, max(ref.depths))
+    assert deepest >= 3, deepest

@@ -131,3 +131,82 @@ def test_device_replay_batch_equals_host_batch():
     losses = [train_on_device(tr, dr, 8, gen) for _ in range(3)]
     assert all(np.isfinite(l) for l in losses)
     assert sorted(set(dr.priority[: len(dr)].tolist())) != [1.0]          # the losses were written back as priorities
+
+
+def _random_batch(g, B, K, n, A, dev):
+    from muzero_go_b200.trainer import Batch
+    pol = torch.rand(B, K + 1, A, generator=g)
+    return Batch((torch.rand(B, 6, n, n, generator=g) < 0.3).float().to(dev), torch.randint(0, A, (B, K), generator=g).to(dev),
+                 (torch.rand(B, K, generator=g) - 0.5).to(dev), (torch.rand(B, K + 1, generator=g) * 2 - 1).to(dev),
+                 (pol / pol.sum(-1, keepdim=True)).to(dev))
+
+
+def test_forward_follows_graph_replayed_training_steps():
+    """A replayed CUDA graph rewrites the parameters without touching tensor._version: after
+    several replay-only steps the libmzgo forward (prepared weight layouts, head constants, cached search graph)
+    must be the forward of the CURRENT parameters -- checked against the torch forward the trainer differentiates,
+    after every step, and through a SelfPlayEngine built before the steps."""
+    import muzero_go_b200 as mz
+    from muzero_go_b200 import trainer as T
+    n, c, B, K = 6, 32, 8, 10
+    A = n * n + 1
+    dev = torch.device("cuda")
+    torch.manual_seed(12)
+    net = mz.MuZeroNet(c, A).to(dev)
+    cfg = T.TrainConfig(learning_rate=3e-3)                     # large steps: stale weights show at once
+    tr = T.BatchedTrainer(net, A, cfg, cuda_graph=True)
+    eng = mz.SelfPlayEngine(net, n, 16, 8, search=mz.SearchConfig(seed=2), traj_capacity=4)
+    g = torch.Generator(device="cpu").manual_seed(5)
+    obs = (torch.rand(5, 6, n, n, generator=g) < 0.3).float().to(dev)
+    act = torch.randint(0, A, (5,), generator=g).to(dev)
+    prev = None
+    for step in range(5):
+        tr.train_step(_random_batch(g, B, K, n, A, dev))
+        assert len(tr._graphs) == 1
+        with torch.no_grad():
+            lat_t = T.representation(net, obs)
+            val_t, log_t = T.prediction(net, lat_t)
+            nxt_t, rew_t = T.dynamics(net, lat_t, act)
+            val2_t, log2_t = T.prediction(net, nxt_t)
+        lat, val, log = net.initial_inference(obs)
+        nxt, rew, val2, log2 = net.recurrent_inference(lat_t, act)
+        for got, want in ((lat, lat_t), (val, val_t), (log, log_t), (nxt, nxt_t), (rew, rew_t), (val2, val2_t), (log2, log2_t)):
+            assert torch.allclose(got, want, rtol=1e-4, atol=1e-5), step
+        if prev is not None:
+            assert not torch.allclose(lat, prev, rtol=1e-3, atol=1e-4)      # the steps do move the forward
+        prev = lat.clone()
+        # the engine (descriptor and search graph cached from earlier moves) searches with the new weights: its root
+        # value is the network's value of the position
+        eng.run(1)
+        torch.cuda.synchronize()
+    # root_value_net holds the initial-inference value the last move's search started from (position: traj row 0)
+    gb = mz.GoBoards(eng.G, n, dev)
+    gb.records.copy_(eng.traj_boards[0])
+    with torch.no_grad():
+        want_v, _ = T.prediction(net, T.representation(net, gb.planes(torch.float32)))
+    assert torch.allclose(eng.root_value_net, want_v.flatten(), rtol=1e-4, atol=1e-5)
+
+
+def test_second_batch_shape_keeps_earlier_graphs_valid():
+    """capturing a graph for a second batch shape must not move Adam's moment tensors from under
+    the first graph.  Alternating two shapes equals the eager trainer on the same batches."""
+    import copy
+    import muzero_go_b200 as mz
+    from muzero_go_b200.trainer import BatchedTrainer, TrainConfig
+    n, c, K = 5, 16, 10
+    A = n * n + 1
+    dev = torch.device("cuda")
+    torch.manual_seed(3)
+    net_a = mz.MuZeroNet(c, A).to(dev)
+    net_b = copy.deepcopy(net_a)
+    cfg = TrainConfig()
+    eager, graphed = BatchedTrainer(net_a, A, cfg, cuda_graph=False), BatchedTrainer(net_b, A, cfg, cuda_graph=True)
+    g = torch.Generator(device="cpu").manual_seed(9)
+    for step, B in enumerate([8, 8, 4, 8, 4, 4, 8]):
+        b = _random_batch(g, B, K, n, A, dev)
+        la, _ = eager.train_step(b)
+        lb, _ = graphed.train_step(b)
+        assert torch.allclose(la, lb, rtol=1e-5, atol=1e-6), step
+        for p, q in zip(net_a.parameters(), net_b.parameters()):
+            assert torch.allclose(p, q, rtol=0, atol=3e-6), step
+    assert len(graphed._graphs) == 2

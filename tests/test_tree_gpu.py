@@ -15,9 +15,17 @@ GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 MAIN_LIKE = sorted(glob.glob(os.path.join(GOLDEN, "mcts_*.npz")))   # main.py, play.py and self_play.py fixtures
 
 
-def run_gpu_search(n, obs_list, init_soft, soft, rewards, values, noise, streams, sims, cfg):
+DRIVERS = ["standalone", "step"]
+
+
+def run_gpu_search(n, obs_list, init_soft, soft, rewards, values, noise, streams, sims, cfg, driver="standalone"):
     """G independent searches in lock step; soft/rewards/values are per-game call-indexed tables
-    ([G][sims][A], [G][sims], [G][sims]), consumed in the order each game's simulations complete."""
+    ([G][sims][A], [G][sims], [G][sims]), consumed in the order each game's simulations complete.
+
+    driver "standalone": mzgo_tree_select + mzgo_tree_expand_backup (k_tree_select / k_tree_expand_backup).
+    driver "step": mzgo_tree_step(do_backup, do_select) -- k_tree_step<32> (A <= 96) / k_tree_step<128>, the kernel
+    mzgo_search_run launches once per simulation (and the code of the network kernel's tree phase), with the table
+    row of the leaf it selected written into the output buffers before the step that backs it up."""
     import muzero_go_b200 as mz
     G, A = len(obs_list), n * n + 1
     dev = torch.device("cuda")
@@ -31,15 +39,23 @@ def run_gpu_search(n, obs_list, init_soft, soft, rewards, values, noise, streams
     calls = torch.zeros(G, dtype=torch.int64, device=dev)
     gi = torch.arange(G, device=dev)
     depths = [[] for _ in range(G)]
-    for _ in range(sims):
-        tree.select(cfg, stream_t)
+    zs, zr = torch.zeros((G, A), device=dev), torch.zeros(G, device=dev)
+    if driver == "step":
+        tree.step(cfg, zs, zr, zr, stream_t, do_backup=False, do_select=True)
+    for s in range(sims):
+        if driver == "standalone":
+            tree.select(cfg, stream_t)
         live = tree.leaf_action >= 0
         idx = calls.clamp(max=sims - 1)
-        tree.expand_backup(cfg, soft_t[gi, idx].contiguous(), rew_t[gi, idx].contiguous(), val_t[gi, idx].contiguous())
-        calls += live.long()
         d = tree.leaf_depth.cpu().numpy()
         for g in np.nonzero(live.cpu().numpy())[0]:
             depths[g].append(int(d[g]))
+        out = (soft_t[gi, idx].contiguous(), rew_t[gi, idx].contiguous(), val_t[gi, idx].contiguous())
+        if driver == "standalone":
+            tree.expand_backup(cfg, *out)
+        else:
+            tree.step(cfg, *out, stream_t, do_backup=True, do_select=s + 1 < sims)
+        calls += live.long()
     return tree, depths
 
 
@@ -51,14 +67,17 @@ def cfg_from_fixture(g):
                            variant="self_play" if str(g["variant"]) == "self_play" else "main")
 
 
+@pytest.mark.parametrize("driver", DRIVERS)
 @pytest.mark.parametrize("path", MAIN_LIKE, ids=os.path.basename)
-def test_visit_counts_bit_exact_vs_reference_fixture(path):
+def test_visit_counts_bit_exact_vs_reference_fixture(path, driver):
     g = np.load(path)
     n, sims = int(g["n"]), int(g["sims"])
     cfg = cfg_from_fixture(g)
     # two copies of the same game in one batch: lock-step batching must not couple games
     tree, depths = run_gpu_search(n, [g["obs"]] * 2, [g["init_soft"]] * 2, [g["soft"]] * 2, [g["rewards"]] * 2,
-                                  [g["values"]] * 2, [g["noise"]] * 2, [g["stream"]] * 2, sims, cfg)
+                                  [g["values"]] * 2, [g["noise"]] * 2, [g["stream"]] * 2, sims, cfg, driver)
+    if sims >= 400 and n >= 9:
+        assert max(depths[0]) >= 2          # the fixture reaches below the root's children (19x19/800: depth 2, 9x9/800: 3)
     for k in range(2):
         assert np.array_equal(tree.root_prior[k].cpu().numpy(), g["root_prior"]), "root priors (float64) differ"
         assert np.array_equal(tree.edge_visit[k, 0].cpu().numpy().astype(np.int64), g["visit"])
@@ -73,7 +92,8 @@ def test_visit_counts_bit_exact_vs_reference_fixture(path):
 @pytest.mark.parametrize("n,sims,G,c_puct,variant", [(5, 120, 6, 2, "main"), (9, 260, 4, 2, "main"), (9, 150, 3, 10.0, "main"),
                                                      (19, 500, 2, 2, "main"), (5, 150, 6, 2.5, "self_play"),
                                                      (9, 260, 4, 2.5, "self_play"), (19, 450, 2, 2.5, "self_play")])
-def test_batched_search_matches_oracle_on_random_tables(n, sims, G, c_puct, variant):
+@pytest.mark.parametrize("driver", DRIVERS)
+def test_batched_search_matches_oracle_on_random_tables(n, sims, G, c_puct, variant, driver):
     """Different positions / tables per game; also exercises games whose simulations get dropped
     (main.py) or end in a terminal leaf (self_play.py)."""
     import muzero_go_b200 as mz
@@ -107,7 +127,9 @@ def test_batched_search_matches_oracle_on_random_tables(n, sims, G, c_puct, vari
         t, mask = run_ref(o, lambda ob, k=k: (None, np.float32(0), init_soft[k]), recurrent, sims, noise[k],
                           streams[k], c_puct=c_puct, discount=0.99, dirichlet_epsilon=0.25, pass_epsilon=0.05)
         trees.append((t, mask))
-    tree, depths = run_gpu_search(n, obs, init_soft, soft, rew, val, noise, streams, sims, cfg)
+    tree, depths = run_gpu_search(n, obs, init_soft, soft, rew, val, noise, streams, sims, cfg, driver)
+    if n == 19:
+        assert max(max(d) for d in depths if d) >= 2     # deeper levels of k_tree_step<128> at A = 362
     vc = tree.visit_counts().cpu().numpy()
     for k, (t, mask) in enumerate(trees):
         assert np.array_equal(tree.root_prior[k].cpu().numpy(), np.asarray(t.prior[0], dtype=np.float64))
