@@ -155,3 +155,69 @@ def test_pack_expand_round_trip_and_env():
         assert np.array_equal(i1["invalid_moves"], i2["invalid_moves"])
         done = d1
     assert env.winner() == ref.winner()
+
+
+@pytest.mark.parametrize("n,boards,T", [(5, 512, 75), (9, 512, 243), (19, 192, 722)])
+def test_playout_equals_textbook_rules_engine(n, boards, T):
+    """The kernels against the THIRD checker directly (oracle/go_textbook.c: place the stone, remove dead opponent
+    groups, suicide test, simple ko, two passes, region-flood area score -- no liberty-count formula in it): same
+    actions, same six planes after every ply (state hashes), same final planes and areas."""
+    import muzero_go_b200 as mz
+    from oracle import go_textbook
+    R = philox_table(700 + n, (boards, T))
+    want = go_textbook.playout(n, R)
+    gb = mz.GoBoards(boards, n).reset()
+    acts, hsh, _ = gb.playout(R, want_hash=True)
+    assert np.array_equal(acts.cpu().numpy(), want["actions"])
+    assert np.array_equal(hsh.cpu().numpy().view(np.uint64), want["hashes"])
+    assert np.array_equal(gb.planes(torch.uint8).cpu().numpy(), want["planes"])
+    areas, winner = gb.score(0.0)
+    assert np.array_equal(areas.cpu().numpy(), want["areas"])
+    assert np.array_equal(winner.cpu().numpy(), np.sign(want["areas"][:, 0] - want["areas"][:, 1]))
+
+
+def test_known_answer_positions_on_the_kernels():
+    """The hand-derived positions of tests/test_rules_textbook.py (ko in the corner / on the edge / in the centre,
+    two stones at once, recapture that is not ko, multi-stone suicide, snapback, eyes, tiny boards) played on the
+    GPU: planes after every move equal the textbook engine's, illegal moves are refused with status -1."""
+    import muzero_go_b200 as mz
+    from oracle.go_textbook import TextbookGo
+    cases = [
+        (["O.O..", "XO...", ".....", ".....", "....."], "b", [(0, 1), "x00", (4, 4), (4, 0), (0, 0), "x01"]),
+        (["XO.O.", ".XO..", ".....", ".....", "....."], "b", [(0, 2), "x01", (3, 3), (0, 1)]),
+        ([".XO..", "XO.O.", ".XO..", ".....", "....."], "b", [(1, 2), "x11", None, (4, 4), (1, 1), "x12"]),
+        (["O.OX.", "XOX..", ".....", ".....", "....."], "b", [(0, 1), "x00", "x02", None, (4, 4), "x00"]),
+        (["X.OX.", "OOX..", ".....", ".....", "....."], "b", [(0, 1), (0, 2), (0, 1)]),
+        (["X.XO.", "OOO..", ".....", ".....", "....."], "b", ["x01", None, (0, 1)]),
+        (["..OX.", "OOOX.", "XXX..", ".....", "....."], "b", [(0, 1), (0, 0), (0, 1)]),
+        ([".....", ".XO..", "XO.O.", ".XO..", "....."], "b", [(2, 2), "x21", (0, 0), (4, 4), (2, 1)]),
+        (["X.X.X", "XXXXX", "OOOOO", ".....", "....."], "w", ["x01", "x03", None, (0, 1), (0, 3)]),
+        (["XXX.X", "XXXXX", "OOOOO", ".....", "....."], "b", ["x03", None, (0, 3)]),
+        (["XO", ".."], "b", [(1, 1), "x01", "x10", None, (0, 1)]),
+        (["X.", ".O"], "w", [(0, 1), (1, 0), None, None]),
+        (["X.X", ".X.", "X.X"], "w", ["x01", "x10", "x12", "x21", None, (0, 1)]),
+    ]
+    for rows, to_move, script in cases:
+        n = len(rows)
+        ref = TextbookGo(n)
+        ref.to_move = 0 if to_move == "b" else 1
+        for r, line in enumerate(rows):
+            for c, ch in enumerate(line):
+                if ch in "XO":
+                    ref.stones[(r, c)] = 0 if ch == "X" else 1
+        gb = mz.GoBoards(1, n).load_planes(ref.planes()[None].astype(np.float32))
+        for step in script:
+            if isinstance(step, str):                  # "xRC": the move must be refused, board untouched
+                r, c = int(step[1]), int(step[2])
+                before = gb.records.clone()
+                assert ref.try_move((r, c)) is None, (rows, step)
+                status = gb.step(torch.tensor([r * n + c], dtype=torch.int32))
+                assert int(status[0]) == -1 and torch.equal(before, gb.records), (rows, step)
+                continue
+            a = n * n if step is None else step[0] * n + step[1]
+            ref.play(a)
+            status = gb.step(torch.tensor([a], dtype=torch.int32))
+            assert int(status[0]) == 0, (rows, step)
+            assert np.array_equal(gb.planes(torch.uint8).cpu().numpy()[0], ref.planes()), (rows, step)
+        areas, _ = gb.score(0.0)
+        assert tuple(areas[0].tolist()) == ref.areas(), rows
