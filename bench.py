@@ -4,6 +4,9 @@
     python bench.py --gpus N --steps K --warmup W            # our arm: CUDA hot path through the C ABI
     python bench.py --impl reference ...                      # CPU arm: the oracle port of the reference
 
+Default workload: BASELINE.json configs[3] (19x19, 2048 games, 800 sims/move, bf16), the north-star configuration;
+the configs[1] figures (9x9, 1024 games, 50 sims) ride in the same line under "secondary".
+
 A step = one lock-step move of every concurrent game: initial inference, root preparation,
 `sims` x (select -> recurrent inference -> expand/backup), action choice, rules step, trajectory row.
 Prints ONE JSON line (rank 0).  See DESIGN.md "Measurement" for the definitions used here.
@@ -25,10 +28,6 @@ WORKLOADS = {
     "19x19": dict(n=19, games=2048, sims=800, name="19x19 Go batched self-play, 2048 games, 800 sims/move"),
 }
 LATENT = 128
-# dram__bytes_read.sum + dram__bytes_write.sum per unit from the ncu --set full captures summarised in
-# profiles/r01/ncu_full_{9x9,19x19}_v8_raw.csv (writes are partly still in the 126 MB L2 when the kernel ends)
-NCU_TRAFFIC = {"rec_bytes_per_leaf": {9: 30.0e3, 19: 183.1e3}, "tree_bytes_per_game": {9: 3.19e3, 19: 12.24e3},
-               "source": "profiles/r01/ncu_full_*_v8_raw.csv (v9 captures agree: 33.4 KB per fused 9x9 launch and leaf, 183.2 KB at 19x19)"}
 
 
 def flops_recurrent(n, c=LATENT):
@@ -84,21 +83,23 @@ class ClockSampler:
         except subprocess.TimeoutExpired:
             self.proc.kill()
         time.sleep(0.2)
-        sm, mx, reasons = [], None, set()
+        sm, pw, mx, reasons = [], [], None, set()
         for t, r in self.rows:
             if len(r) < 7 or t < since:
                 continue
             try:
                 sm.append(float(r[0]))
                 mx = float(r[1])
+                pw.append(float(r[2]))
             except ValueError:
                 continue
             for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
                 if v.lower().startswith("active"):
                     reasons.add(name)
         sm.sort()
+        pw.sort()
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
-                "samples": len(sm)}
+                "samples": len(sm), "power_w_median": pw[len(pw) // 2] if pw else None}
 
 
 # ------------------------------------------------------------------------------------------------ CPU arm
@@ -118,6 +119,13 @@ def _cpu_worker(args):
     A = n * n + 1
     env = gymgo.GoEnv(n)
     obs = env.reset()
+    # mixed game phases like the GPU arm (config "positions"): a random 0-60 % of the move cap, untimed
+    for _ in range(int(rng.integers(0, int(0.6 * 1.5 * n * n) + 1))):
+        v = np.nonzero(env.valid_moves())[0]
+        obs, _, done, _ = env.step(int(v[rng.integers(len(v) - 1)]) if len(v) > 1 else int(v[0]))
+        if done:
+            obs = env.reset()
+            break
     sims_done = moves = 0
     t0 = time.perf_counter()
     while time.perf_counter() - t0 < budget:
@@ -150,7 +158,7 @@ def run_reference(args, wl):
     if rank != 0:
         return
     procs = os.cpu_count() or 1
-    n, sims = wl["n"], wl["sims"]
+    n, sims = wl["n"], args.sims or wl["sims"]
     per_step = max(4.0, min(20.0, 120.0 / max(1, args.steps + args.warmup)))
     for _ in range(args.warmup):
         cpu_arm(n, sims, min(2.0, per_step), procs)
@@ -166,7 +174,7 @@ def run_reference(args, wl):
     line = {"impl": "reference", "metric": "mcts_simulations_per_sec", "value": v, "unit": "sims/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1000.0 * t_total / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": wl["name"], "board": n, "sims_per_move": sims, "latent_dim": LATENT},
+            "config": config_dict(wl, args.games or wl["games"], sims, args.precision),
             "moves_per_sec": sum(mvals) / len(mvals),
             "cpu_baseline": {"value": v, "unit": "sims/s", "cores": procs, "kind": "port", "sample": sample},
             "e2e": {"value": v, "unit": "sims/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
@@ -174,25 +182,98 @@ def run_reference(args, wl):
 
 
 # ------------------------------------------------------------------------------------------------ GPU arm
-def run_ours(args, wl):
-    import numpy as np
+def config_dict(wl, games, sims, precision):
+    """The same dict in both arms (the CPU arm runs this workload's per-game loop on the host cores)."""
+    return {"workload": wl["name"], "board": wl["n"], "games_per_gpu": games, "sims_per_move": sims, "latent_dim": LATENT,
+            "weights": "random-init (torch.manual_seed(0))", "precision": precision,
+            "positions": "every game advanced a random 0-60 % of the move cap by random legal moves before the warm-up",
+            "cache": "inputs larger than L2 (the latent arena is > 1 GB per GPU and every simulation reads and writes fresh slots)",
+            "parallelism": "games sharded over the GPUs, no collective inside the search"}
+
+
+def ncu_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum per unit from the newest committed ncu --set full capture
+    (profiles/<round>/ncu_traffic.json, written by tools/summarise_ncu.py).  None when there is no capture."""
+    import glob
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*", "ncu_traffic.json")))
+    if not files:
+        return None
+    with open(files[-1]) as fh:
+        d = json.load(fh)
+    d["file"] = os.path.relpath(files[-1], ROOT)
+    return d
+
+
+def advance_games(mz, torch, group, n, seed):
+    """Mixed game phases: every game is advanced by a random 0-60 % of the move cap with random legal moves (the
+    configs[2] playout kernel), so the timed region sees openings, middle games and endgames side by side -- the steady
+    state of a long self-play job -- instead of 2048 empty boards."""
+    gen = torch.Generator(device="cpu").manual_seed(seed)
+    buckets = 8
+    for e in group.engines:
+        cap = e.max_game_moves
+        which = torch.randint(0, buckets, (e.G,), generator=gen)
+        for b in range(1, buckets):
+            idx = torch.nonzero(which == b).flatten().to(e.device)
+            plies = int(0.6 * cap * b / (buckets - 1))
+            if idx.numel() == 0 or plies == 0:
+                continue
+            tmp = mz.GoBoards(int(idx.numel()), n, e.device).reset()
+            R = torch.randint(0, 2 ** 31 - 1, (int(idx.numel()), plies), dtype=torch.int32, generator=gen)
+            tmp.playout(R, want_actions=False)
+            e.boards.records[idx] = tmp.records
+            e.move_count[idx] = tmp.records[:, 62]
+            e.pass_streak[idx] = tmp.records[:, 61] & 1
+    torch.cuda.synchronize()
+
+
+class TrajectoryExchange:
+    """The trajectory gather of north_star (4), off the search's critical path: every step's rows are packed with
+    slice copies into a ring of `depth` fixed-stride rows (no allocation), and every `depth` steps the ring is
+    all-gathered on a side stream ordered behind the compute stream by an event ("batched per K moves so
+    messages are >= 1 MB").  With one rank the rows are only packed."""
+
+    def __init__(self, torch, dist, mzdist, group, A, world, depth):
+        self.torch, self.mzdist, self.world, self.depth = torch, mzdist, world, depth
+        self.ring = mzdist.RowRing(group.G, A, depth, group.device)
+        self.side = torch.cuda.Stream()
+        self.out = (torch.empty((world,) + tuple(self.ring.buf.shape), dtype=torch.uint8, device=group.device)
+                    if world > 1 else None)
+        self.filled = 0
+        self.bytes_gathered = 0
+
+    def push(self, rows_per_engine):
+        self.ring.write(self.filled, rows_per_engine)
+        self.filled += 1
+        if self.filled == self.depth:
+            self.flush()
+
+    def flush(self):
+        if self.filled and self.world > 1:
+            torch = self.torch
+            ev = torch.cuda.Event()
+            ev.record()
+            with torch.cuda.stream(self.side):
+                self.side.wait_event(ev)
+                self.mzdist.all_gather_rows(self.out, self.ring.buf)
+            # the ring is rewritten by the next step: order that step behind the gather
+            torch.cuda.current_stream().wait_stream(self.side)
+            self.bytes_gathered += self.ring.buf.numel() * self.world
+        self.filled = 0
+
+
+def measure(args, wl, G, S, K, W, rank, world, dev, primary):
+    """One workload on this rank: whole-step throughput (device timed), end to end with host buffers, and -- for the
+    primary workload -- the three kernel families timed alone."""
     import torch
     import torch.distributed as dist
     import muzero_go_b200 as mz
     from muzero_go_b200 import _lib
     from muzero_go_b200 import dist as mzdist
 
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
-    n, G, S = wl["n"], args.games or wl["games"], args.sims or wl["sims"]
+    n = wl["n"]
     A = n * n + 1
-    K, W = args.steps, args.warmup
-
+    local = dev.index
     torch.manual_seed(0)                                    # random-init weights of the reference architecture
     net = mz.MuZeroNet(LATENT, A, precision=args.precision).to(dev).eval()
     bytes_bcast = mzdist.broadcast_weights(net, src=0)       # weight version 0 from the learner rank
@@ -204,12 +285,14 @@ def run_ours(args, wl):
     waves = 1
     while (G // waves) * per_game > 0.90 * free_b or G % waves:
         waves += 1
-    T = 2
-    group = mz.WaveGroup(net, n, G, S, waves=waves, search=mz.SearchConfig(seed=1000, game_base=rank * G), traj_capacity=T,
+    group = mz.WaveGroup(net, n, G, S, waves=waves, search=mz.SearchConfig(seed=1000, game_base=rank * G), traj_capacity=2,
                          restart_finished=True)
     eng = group.engines[0]          # the single-kernel timings below run on one wave's buffers
     GW = G // waves
     lib = _lib.load()
+    advance_games(mz, torch, group, n, seed=77 + rank)
+    exch_depth = max(1, min(64, (1 << 20) // max(1, G * mzdist.row_stride(A)) + 1))
+    exch = TrajectoryExchange(torch, dist, mzdist, group, A, world, exch_depth)
 
     def barrier():
         if world > 1:
@@ -218,16 +301,15 @@ def run_ours(args, wl):
 
     def step(row=0):
         group.run(1, traj_offset=row)
-        rows = group.trajectory_rows(row, row + 1)
-        if world > 1:                                        # trajectory gather to the replay side, outside the search
-            mzdist.gather_trajectories(rows, A)
-        return rows
+        exch.push([e.trajectory_rows(row, row + 1) for e in group.engines])
 
-    sampler = ClockSampler(local)
-    sampler.start()                 # nvidia-smi takes longer to start than a short timed region lasts: start it first
+    sampler = ClockSampler(local) if primary else None
+    if sampler:
+        sampler.start()             # nvidia-smi takes longer to start than a short timed region lasts: start it first
     t_load = time.perf_counter()
     for _ in range(W):
         step()
+    exch.flush()
     barrier()
     lib.mzgo_launch_count(1)
     c0 = group.read_counters()
@@ -236,31 +318,33 @@ def run_ours(args, wl):
     e0.record()
     for _ in range(K):
         step()
+    exch.flush()
     e1.record()
     barrier()
     ms = e0.elapsed_time(e1)
     launches = int(lib.mzgo_launch_count(0))
     c1 = group.read_counters()
-    # the same steps keep running, untimed, until nvidia-smi has delivered a few samples under this load (a 9x9 timed
-    # region is ~20 ms, the sampling period 100 ms); the samples span warm-up, the timed steps and these
-    # (the count is a function of the max-over-ranks time so that every rank runs the same number of gathers)
-    ms_all = torch.tensor([ms], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(ms_all, op=dist.ReduceOp.MAX)
-    ms_max = float(ms_all.item())
-    extra = 0 if ms_max >= 600.0 or os.environ.get("MZGO_BENCH_NO_EXTRA") else min(2000, int((600.0 - ms_max) / max(ms_max / K, 1e-3)) + 1)
-    # (and the games are put back where the timed region left them, so that everything measured below sees the same
-    # phase of the games as the timed region: openings, the state BASELINE's configs start from)
-    saved = [(e.boards.records.clone(), e.move_count.clone(), e.pass_streak.clone(), e.game_temperature.clone(),
-              e.moves_enqueued) for e in group.engines]
-    for _ in range(extra):
-        step()
-    torch.cuda.synchronize()
-    clocks = sampler.stop(t_load + 0.05)
-    for e, sv in zip(group.engines, saved):
-        e.boards.records.copy_(sv[0]); e.move_count.copy_(sv[1]); e.pass_streak.copy_(sv[2])
-        e.game_temperature.copy_(sv[3]); e.moves_enqueued = sv[4]
-    del saved
+    clocks = None
+    if sampler:
+        # a short timed region (9x9: a few ms per step) ends before nvidia-smi's 100 ms sampler has seen it: the same
+        # steps keep running, untimed, until 0.6 s of load have been sampled (a function of the max-over-ranks time, so
+        # that every rank runs the same number of gathers); the games are put back afterwards
+        ms_all = torch.tensor([ms], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(ms_all, op=dist.ReduceOp.MAX)
+        ms_max = float(ms_all.item())
+        extra = 0 if ms_max >= 600.0 or os.environ.get("MZGO_BENCH_NO_EXTRA") else min(2000, int((600.0 - ms_max) / max(ms_max / K, 1e-3)) + 1)
+        saved = [(e.boards.records.clone(), e.move_count.clone(), e.pass_streak.clone(), e.game_temperature.clone(),
+                  e.moves_enqueued) for e in group.engines]
+        for _ in range(extra):
+            step()
+        exch.flush()
+        torch.cuda.synchronize()
+        clocks = sampler.stop(t_load + 0.05)
+        for e, sv in zip(group.engines, saved):
+            e.boards.records.copy_(sv[0]); e.move_count.copy_(sv[1]); e.pass_streak.copy_(sv[2])
+            e.game_temperature.copy_(sv[3]); e.moves_enqueued = sv[4]
+        del saved
     barrier()
     sims_done = c1["simulations"] - c0["simulations"]
     moves_done = c1["moves"] - c0["moves"]
@@ -279,12 +363,14 @@ def run_ours(args, wl):
             host_boards[w * GW:(w + 1) * GW].copy_(rec, non_blocking=non_blocking)
 
     boards_down()
-    row_bytes = mzdist.pack_rows(group.trajectory_rows(0, 1))
-    host_row = torch.empty(row_bytes.shape, dtype=torch.uint8).pin_memory()
+    row_ring = mzdist.RowRing(G, A, 1, dev)
+    host_row = torch.empty(row_ring.buf.shape, dtype=torch.uint8).pin_memory()
+
     def e2e_step():
         boards_up()
-        rows = step()
-        host_row.copy_(mzdist.pack_rows(rows), non_blocking=True)
+        step()
+        row_ring.write(0, [e.trajectory_rows(0, 1) for e in group.engines])
+        host_row.copy_(row_ring.buf, non_blocking=True)
         boards_down(non_blocking=True)                       # next step's input comes from the host again
         torch.cuda.synchronize()                             # both read-backs have landed in pinned memory
 
@@ -295,13 +381,19 @@ def run_ours(args, wl):
     t0 = time.perf_counter()
     for _ in range(K):
         e2e_step()
+    exch.flush()
     barrier()
     e2e_s = time.perf_counter() - t0
     c2 = group.read_counters()
     e2e_sims = c2["simulations"] - c1e["simulations"]
     if os.environ.get("MZGO_BENCH_DEBUG"):
-        print(f"[bench debug] rank {rank}: timed {ms:.3f} ms / {sims_done} sims, extra steps {extra}, "
-              f"e2e {e2e_s * 1e3:.3f} ms / {e2e_sims} sims", file=sys.stderr)
+        print(f"[bench debug] rank {rank}: timed {ms:.3f} ms / {sims_done} sims, e2e {e2e_s * 1e3:.3f} ms / {e2e_sims} sims",
+              file=sys.stderr)
+    res = dict(ms=ms, e2e_ms=e2e_s * 1000.0, sims=sims_done, moves=moves_done, e2e_sims=e2e_sims, launches=launches, G=G,
+               depth=depth, waves=waves, GW=GW, clocks=clocks, bytes_bcast=bytes_bcast, arena_gb=eng.arena.numel() / 1e9,
+               h2d=G * 256, d2h=int(row_ring.buf.numel()) + G * 256, graph_replays=int(lib.mzgo_graph_replays()),
+               exchange={"rows_per_gather": exch_depth, "bytes_per_gather_per_rank": int(exch.ring.buf.numel()),
+                         "stream": "side stream, event-ordered"})
 
     # ---- dominant kernel (recurrent inference of one leaf batch), timed alone with CUDA events
     d = eng.descriptor()
@@ -333,11 +425,34 @@ def run_ours(args, wl):
         torch.cuda.synchronize()
         return k0.elapsed_time(k1) / (replays * count)
 
-    kern_ms = graph_time(lambda st: _lib.check(lib.mzgo_net_recurrent(*args_rec[:-1], st)), reps)
+    rec_fn = lambda st: _lib.check(lib.mzgo_net_recurrent(*args_rec[:-1], st))
+    kern_ms = graph_time(rec_fn, reps)
+    # ... and back to back for about a second (primary workload): the same kernel under the power cap, the way it runs
+    # inside a seconds-long step -- this is the figure to hold against the SUSTAINED cuBLAS peak
+    kern_ms_sustained = graph_time(rec_fn, reps, replays=max(3, int(1000.0 / (reps * kern_ms)))) if primary else None
     live = int((eng.tree.leaf_action >= 0).sum())
     peaks = measured_peaks()
     achieved = live * flops_recurrent(n) / (kern_ms * 1e-3) / 1e12
-    peak_tf = peaks["bf16_sustained"]
+    traffic = ncu_traffic()
+    tkey = f"rec_bytes_per_leaf_{n}"
+    res["roofline"] = {
+        "bound": "tensor", "kernel": "mzgo_net_recurrent (dynamics conv3x3 + heads, one leaf batch), timed alone: "
+                                     f"CUDA-graph replay of {reps} launches between CUDA events",
+        "achieved": achieved, "peak": peaks["bf16_burst"], "unit": "TFLOP/s", "frac": achieved / peaks["bf16_burst"],
+        "peak_source": peaks["source"] + " bf16 burst (the kernel is timed in isolation)",
+        "frac_of_sustained": achieved / peaks["bf16_sustained"],
+        "traffic": (traffic[tkey] * live if traffic and tkey in traffic else None),
+        "traffic_unit": "bytes per launch (ncu dram read+write per leaf x leaves)",
+        "traffic_source": traffic["file"] if traffic and tkey in traffic else None,
+        "algorithmic_bytes": 2 * LATENT * n * n * 2 * live, "launch_ms": kern_ms, "leaves_per_launch": live}
+    if kern_ms_sustained:
+        sus = live * flops_recurrent(n) / (kern_ms_sustained * 1e-3) / 1e12
+        res["roofline"]["sustained"] = {"launch_ms": kern_ms_sustained, "achieved": sus, "peak": peaks["bf16_sustained"],
+                                        "frac": sus / peaks["bf16_sustained"],
+                                        "what": "the same launches back to back for ~1 s (power cap reached), against the "
+                                                "measured sustained bf16 peak"}
+    if not primary:
+        return res
 
     # ---- tree step (HBM bound): expand + backup + next selection of all G trees, late in a search
     def bytes_tree(depth_mean):
@@ -369,6 +484,14 @@ def run_ours(args, wl):
     tree_depth = (int(eng.tree.depth_sum.sum()) - dsum0) / max(1, tree_sims)
     tree_bytes = tree_sims / tree_reps * bytes_tree(tree_depth)
     tree_gbs = tree_bytes / (tree_ms * 1e-3) / 1e9
+    tkey = f"tree_bytes_per_game_{n}"
+    res["roofline_tree"] = {
+        "bound": "hbm", "kernel": "k_tree_step (expand + backup + select, all trees of a wave), timed alone",
+        "achieved": tree_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": tree_gbs / peaks["hbm_gbs"],
+        "traffic": (traffic[tkey] * tree_sims / tree_reps if traffic and tkey in traffic else None),
+        "traffic_source": traffic["file"] if traffic and tkey in traffic else None, "launch_ms": tree_ms,
+        "bytes_per_sim": bytes_tree(tree_depth), "mean_leaf_depth": tree_depth, "sims_per_launch": tree_sims / tree_reps,
+        "state": f"simulations {S - tree_reps}..{S} of a search"}
 
     # ---- rules step (HBM bound nominally, 324 B per ply at 19x19 / 108 B at 9x9): 2^20 mid-game boards, one
     # random legal move each per launch (the configs[2] playout kernel with T = 1)
@@ -395,58 +518,106 @@ def run_ours(args, wl):
     rules_bytes = NB * (2 * (3 * 4 * ((n * n + 31) // 32) + 16) + 4)
     rules_gbs = rules_bytes / (rules_ms * 1e-3) / 1e9
     del rb, Rnd, acts
+    tkey = f"rules_bytes_per_ply_{n}"
+    res["roofline_rules"] = {
+        "bound": "hbm", "kernel": "k_rules_playout, T=1 (one random legal move on each of 2^20 mid-game boards)",
+        "achieved": rules_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": rules_gbs / peaks["hbm_gbs"],
+        "traffic": (traffic[tkey] * NB if traffic and tkey in traffic else None),
+        "traffic_source": traffic["file"] if traffic and tkey in traffic else None,
+        "launch_ms": rules_ms, "bytes_per_ply": rules_bytes / NB, "plies_per_sec": NB / (rules_ms * 1e-3)}
+    return res
 
-    t = torch.tensor([ms, e2e_s * 1000.0], dtype=torch.float64, device=dev)
-    tot = torch.tensor([sims_done, moves_done, e2e_sims, launches, G], dtype=torch.float64, device=dev)
+
+def rules_cpu_baseline(n):
+    """BASELINE.md section 3, rules-only CPU point: the C restatement of GymGo (oracle/gymgo_c.c, one host thread) on
+    configs[2]'s move table, a bounded sample of boards."""
+    import numpy as np
+    from oracle import gymgo_fast
+    boards, T = (64, 2 * n * n) if n > 9 else (1024, 2 * n * n)
+    R = np.random.Generator(np.random.Philox(0)).integers(0, 2 ** 32, size=(boards, T), dtype=np.uint64).astype(np.uint32)
+    st = gymgo_fast.init_states(boards, n)
+    gymgo_fast.lib()
+    t0 = time.perf_counter()
+    plies = gymgo_fast.playout(st, R)[0]
+    dt = time.perf_counter() - t0
+    return {"value": plies / dt, "unit": "plies/s", "cores": 1, "kind": "port",
+            "sample": f"oracle/gymgo_c.c, {boards} boards x up to {T} plies of the configs[2] playout ({n}x{n}), one thread, {dt:.1f} s"}
+
+
+def run_ours(args, wl):
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
     if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
-    ms, e2e_ms = t.tolist()
-    sims_all, moves_all, e2e_sims_all, launches_all, G_all = tot.tolist()
+        dist.init_process_group("nccl", device_id=dev)
+    G, S = args.games or wl["games"], args.sims or wl["sims"]
+    K, W = args.steps, args.warmup
+    r = measure(args, wl, G, S, K, W, rank, world, dev, primary=True)
+    second = None
+    if args.workload == "19x19" and not args.no_secondary and not args.games and not args.sims:
+        # BASELINE configs[1] beside it (extra key, same line): the 9x9 / 1024 games / 50 sims workload, whose steps
+        # are ~2 ms -- timed over enough steps for half a second of device time
+        torch.cuda.empty_cache()
+        wl9 = WORKLOADS["9x9"]
+        r9 = measure(args, wl9, wl9["games"], wl9["sims"], max(K, 250), max(W, 5), rank, world, dev, primary=False)
+        second = (wl9, r9)
 
+    def reduce(res):
+        t = torch.tensor([res["ms"], res["e2e_ms"]], dtype=torch.float64, device=dev)
+        tot = torch.tensor([res["sims"], res["moves"], res["e2e_sims"], res["launches"], res["G"]], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+        return t.tolist(), tot.tolist()
+
+    (ms, e2e_ms), (sims_all, moves_all, e2e_sims_all, launches_all, G_all) = reduce(r)
+    red9 = reduce(second[1]) if second else None
     if rank == 0:
+        n = wl["n"]
+        peaks = measured_peaks()
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
             procs = os.cpu_count() or 1
             s, m, wall = cpu_arm(n, S, 12.0, procs)
             cpu = {"value": s, "unit": "sims/s", "cores": procs, "kind": "port", "moves_per_sec": m,
                    "sample": f"{procs} single-thread processes x 12 s of the oracle port of main.py's self-play loop "
-                             f"({n}x{n}, {S} sims/move, C={LATENT})"}
-        row_b = int(row_bytes.numel())
-        line = {"metric": "mcts_simulations_per_sec", "value": sims_all / (ms * 1e-3), "unit": "sims/s", "n_gpus": world,
+                             f"({n}x{n}, {S} sims/move, C={LATENT}); calibration of the port against the real "
+                             "main.MCTS.run: BASELINE.md section 3"}
+            r["roofline_rules"]["cpu_baseline"] = rules_cpu_baseline(n)
+        value = sims_all / (ms * 1e-3)
+        cfg = config_dict(wl, G, S, args.precision)
+        line = {"metric": "mcts_simulations_per_sec", "value": value, "unit": "sims/s", "n_gpus": world,
                 "steps": K, "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "bf16" if args.precision == "bf16" else "f32", "data": "synthetic",
-                "config": {"workload": wl["name"], "board": n, "games_per_gpu": G, "games_total": int(G_all), "waves": waves,
-                           "games_per_wave": GW,
-                           "sims_per_move": S, "latent_dim": LATENT, "weights": "random-init (torch.manual_seed(0))",
-                           "cache": "inputs larger than L2 (latent arena %.1f GB per GPU)" % (eng.arena.numel() / 1e9),
-                           "parallelism": f"games sharded over {world} GPU(s), no collective inside the search"},
-                "moves_per_sec": moves_all / (ms * 1e-3), "mean_leaf_depth": depth,
-                "e2e": {"value": e2e_sims_all / (e2e_ms * 1e-3), "unit": "sims/s", "h2d_bytes_per_step": G * 256,
-                        "d2h_bytes_per_step": row_b + G * 256},
-                "gpu_launches": int(launches_all), "search_graph_replays": int(lib.mzgo_graph_replays()),
-                "roofline": {"bound": "tensor", "kernel": "mzgo_net_recurrent (dynamics conv3x3 + heads, one leaf batch)",
-                             "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved / peak_tf,
-                             "traffic": (NCU_TRAFFIC["rec_bytes_per_leaf"][n] * live if n in NCU_TRAFFIC["rec_bytes_per_leaf"] else None),
-                             "traffic_unit": "bytes per launch (ncu dram read+write per leaf x leaves)",
-                             "algorithmic_bytes": 2 * LATENT * n * n * 2 * live, "peak_source": peaks["source"] + " bf16 sustained",
-                             "launch_ms": kern_ms, "leaves_per_launch": live},
-                "roofline_tree": {"bound": "hbm", "kernel": "k_tree_step (expand + backup + select, all trees)",
-                                  "achieved": tree_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                                  "frac": tree_gbs / peaks["hbm_gbs"],
-                                  "traffic": (NCU_TRAFFIC["tree_bytes_per_game"][n] * tree_sims / tree_reps
-                                              if n in NCU_TRAFFIC["tree_bytes_per_game"] else None),
-                                  "traffic_note": "ncu capture at leaf depth 1; " + NCU_TRAFFIC["source"],
-                                  "launch_ms": tree_ms,
-                                  "bytes_per_sim": bytes_tree(tree_depth), "mean_leaf_depth": tree_depth,
-                                  "sims_per_launch": tree_sims / tree_reps,
-                                  "state": f"simulations {S - tree_reps}..{S} of a search"},
-                "roofline_rules": {"bound": "hbm", "kernel": "k_rules_playout, T=1 (one random legal move on each of 2^20 mid-game boards)",
-                                   "achieved": rules_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                                   "frac": rules_gbs / peaks["hbm_gbs"], "traffic": None, "launch_ms": rules_ms,
-                                   "bytes_per_ply": rules_bytes / NB, "plies_per_sec": NB / (rules_ms * 1e-3)},
-                "cpu_baseline": cpu, "clocks": clocks,
-                "weight_broadcast_bytes": bytes_bcast}
+                "config": cfg,
+                "run": {"games_total": int(G_all), "waves": r["waves"], "games_per_wave": r["GW"],
+                        "latent_arena_gb_per_gpu": r["arena_gb"], "trajectory_exchange": r["exchange"]},
+                "moves_per_sec": moves_all / (ms * 1e-3), "mean_leaf_depth": r["depth"],
+                "timed_region_s": ms * 1e-3,
+                "e2e": {"value": e2e_sims_all / (e2e_ms * 1e-3), "unit": "sims/s", "h2d_bytes_per_step": r["h2d"],
+                        "d2h_bytes_per_step": r["d2h"]},
+                "gpu_launches": int(launches_all), "search_graph_replays": r["graph_replays"],
+                "roofline": r["roofline"],
+                "frac_step": {"value": value / world * flops_recurrent(n) / 1e12 / peaks["bf16_sustained"],
+                              "what": "whole step as tensor work: sims/s per GPU x F_rec / measured SUSTAINED bf16 peak "
+                                      "(the step is seconds long)", "peak": peaks["bf16_sustained"], "unit": "TFLOP/s"},
+                "roofline_tree": r["roofline_tree"], "roofline_rules": r["roofline_rules"],
+                "cpu_baseline": cpu, "clocks": r["clocks"], "weight_broadcast_bytes": r["bytes_bcast"]}
+        if second:
+            wl9, r9 = second
+            (ms9, e2e9), (s9, m9, es9, _, _) = red9
+            line["secondary"] = {"config": config_dict(wl9, wl9["games"], wl9["sims"], args.precision),
+                                 "value": s9 / (ms9 * 1e-3), "unit": "sims/s", "moves_per_sec": m9 / (ms9 * 1e-3),
+                                 "steps": max(K, 250), "ms_per_step": ms9 / max(K, 250), "mean_leaf_depth": r9["depth"],
+                                 "e2e": {"value": es9 / (e2e9 * 1e-3), "unit": "sims/s", "h2d_bytes_per_step": r9["h2d"],
+                                         "d2h_bytes_per_step": r9["d2h"]},
+                                 "roofline": r9["roofline"],
+                                 "frac_step": s9 / (ms9 * 1e-3) / world * flops_recurrent(9) / 1e12 / peaks["bf16_sustained"]}
         emit(line)
     if world > 1:
         dist.destroy_process_group()
@@ -569,7 +740,9 @@ def main():
     ap.add_argument("--steps", type=int, default=4)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="9x9", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="19x19", choices=sorted(WORKLOADS),
+                    help="19x19 = BASELINE configs[3], the north-star configuration (default); 9x9 = configs[1]")
+    ap.add_argument("--no-secondary", action="store_true", help="skip the 9x9 figures printed beside the 19x19 line")
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--games", type=int, default=0)
     ap.add_argument("--sims", type=int, default=0)

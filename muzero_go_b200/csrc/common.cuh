@@ -47,27 +47,46 @@ __device__ __forceinline__ void griddep_launch() { asm volatile("griddepcontrol.
 bool mzgo_pdl_enabled();
 void mzgo_pdl_disable();
 
+// cluster_x > 1 launches thread-block clusters of that many CTAs along x (grid.x must be a multiple of it).
 template <typename... KArgs, typename... Args>
-static inline cudaError_t mzgo_launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
-                                          Args&&... args) {
+static inline cudaError_t mzgo_launch_pdl_cluster(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                                                  unsigned cluster_x, Args&&... args) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = grid;
     cfg.blockDim = block;
     cfg.dynamicSmemBytes = smem;
     cfg.stream = st;
-    cudaLaunchAttribute at[1];
-    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cudaLaunchAttribute at[2];
+    unsigned na = 0;
+    if (cluster_x > 1) {
+        at[na].id = cudaLaunchAttributeClusterDimension;
+        at[na].val.clusterDim.x = cluster_x;
+        at[na].val.clusterDim.y = 1;
+        at[na].val.clusterDim.z = 1;
+        na++;
+    }
+    const unsigned base = na;
+    if (mzgo_pdl_enabled()) {
+        at[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[na].val.programmaticStreamSerializationAllowed = 1;
+        na++;
+    }
     cfg.attrs = at;
-    cfg.numAttrs = mzgo_pdl_enabled() ? 1 : 0;
+    cfg.numAttrs = na;
     cudaError_t e = cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
-    if (e != cudaSuccess && cfg.numAttrs) {      // a driver / stream that refuses the attribute: plain launches from now on
+    if (e != cudaSuccess && na > base) {         // a driver / stream that refuses the attribute: plain launches from now on
         cudaGetLastError();
         mzgo_pdl_disable();
-        cfg.numAttrs = 0;
+        cfg.numAttrs = base;
         e = cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
     }
     return e;
+}
+
+template <typename... KArgs, typename... Args>
+static inline cudaError_t mzgo_launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                                          Args&&... args) {
+    return mzgo_launch_pdl_cluster(kernel, grid, block, smem, st, 1u, static_cast<Args&&>(args)...);
 }
 
 // ---- warp helpers ----

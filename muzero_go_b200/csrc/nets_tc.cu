@@ -17,12 +17,24 @@
 // The action embedding (main.py:98-100) is linear in the conv, so it is folded at weight-load time into
 // a per-action, per-border-class bias table [A][9][C] (border pixels see fewer taps).
 //
+// CTA pairs (cta_group::2).  One 128x128x16 MMA of a single CTA fetches 8 KB of operands per 64 cycles: exactly the
+// 128 B/clk of the shared-memory port at exactly the tensor-pipe rate (tools/mma_probe.cu), so every other shared-
+// memory byte -- weight ring refill, latent slabs, the epilogue's bias reads -- delayed the tensor pipe (88 cycles per
+// MMA measured in round 1).  The kernel therefore runs as clusters of two CTAs on the two SMs of a TPC: one thread of
+// the pair's leader issues tcgen05.mma.cta_group::2 (M = 256: 128 rows = one tile of positions from each CTA;
+// N = Cout), each CTA holds only ITS half of the output channels of every weight k-block (the tensor cores exchange
+// the halves), so operand fetch drops to 6 KB per MMA and the weight ring traffic per CTA halves
+// (tools/mma2_probe.cu: operand placement checked against a host matmul, and the cycles per MMA).  Every CTA still
+// owns its own images, TMEM accumulators, epilogue and finalisers; the pair walks its groups in lock step.
+//
 // Warp roles (384 threads): warp 0 TMA producer (latent slab in two 64-channel halves, weight k-blocks
-// through an mbarrier ring), warp 1 TMEM owner + MMA issuer (descriptors precomputed, ~4 instructions
-// per tcgen05.mma), warps 2-9 epilogue (tcgen05.ld -> bias/ReLU -> heads with the 1x1 weights read as
+// through an mbarrier ring), warp 1 TMEM owner + MMA issuer in the leader CTA (descriptors precomputed, ~4
+// instructions per tcgen05.mma) / relay in the other CTA (tells the leader's barriers that this CTA's operands have
+// landed), warps 2-9 epilogue (tcgen05.ld -> bias/ReLU -> heads with the 1x1 weights read as
 // kernel-parameter constants -> bf16 -> coalesced 16 B stores in the arena layout).
 #include <cuda_bf16.h>
 
+#include <algorithm>
 #include <mutex>
 #include <unordered_map>
 
@@ -34,7 +46,7 @@ namespace {
 constexpr int TC_C = 128;               // latent_dim of the tensor-core path
 constexpr int TC_THREADS = 384;         // producer, MMA issuer, 8 epilogue warps, 2 finalisers (384 x 168 registers)
 constexpr int TC_EPI_THREADS = 256;
-constexpr int TC_MAX_STAGES = 8;        // weight k-block ring (as many as fit)
+constexpr int TC_MAX_STAGES = 12;       // weight k-block ring (half a k-block per CTA and stage; as many as fit)
 constexpr int TC_SLOTS = 4;             // 4 x 128 TMEM columns
 constexpr int TC_SMEM_LIMIT = 232448;   // 227 KB
 
@@ -81,6 +93,25 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     while (!mbar_try_wait(bar, parity)) {
     }
 }
+// ---- CTA pair plumbing
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {        // every thread of both CTAs
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// shared::cluster address of the same shared-memory object in CTA `cta` of the cluster
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t saddr, uint32_t cta) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(cta));
+    return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
 __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
                      smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
@@ -118,11 +149,14 @@ __device__ __forceinline__ void st_global_v4_hint_if(void* ptr, uint4 v, uint64_
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
+// completion of all MMAs issued so far -> the barrier at this offset in BOTH CTAs of the pair
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
-                 : "memory");
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+                     smem_u32(bar)), "h"((uint16_t)3) : "memory");
 }
-// D[tmem] (+)= A[smem] * B[smem]^T, bf16 x bf16 -> fp32, M=128, N from idesc, K=16.
+// D[tmem] (+)= A[smem] * B[smem]^T for the CTA pair, bf16 x bf16 -> fp32, K=16: M = 256 (rows 0-127 from the leader's
+// shared memory into the leader's TMEM, rows 128-255 from / into the peer's), N from idesc with each CTA holding N/2
+// rows of B.  The descriptors address the same offsets in both CTAs' shared memory.
 // Descriptors are passed as (lo, hi) words: only lo (start address, LBO) changes between MMAs.
 __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi,
                                           uint32_t idesc, uint32_t acc) {
@@ -133,7 +167,7 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint32_t a_lo, uint32
         "mov.b64 da, {%1, %2};\n\t"
         "mov.b64 db, {%3, %4};\n\t"
         "setp.ne.b32 p, %6, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, p;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], da, db, %5, p;\n\t"
         "}" ::"r"(tmem_d), "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(acc) : "memory");
 }
 // K-major, SWIZZLE_NONE shared-memory matrix descriptor (cute::UMMA::SmemDescriptor bit layout):
@@ -143,9 +177,9 @@ __device__ __forceinline__ uint32_t desc_lo(uint32_t saddr, uint32_t lbo_bytes) 
     return ((saddr >> 4) & 0x3FFFu) | (((lbo_bytes >> 4) & 0x3FFFu) << 16);
 }
 __device__ __forceinline__ uint32_t desc_hi(uint32_t sbo_bytes) { return ((sbo_bytes >> 4) & 0x3FFFu) | (1u << 14); }
-// kind::f16 instruction descriptor: D fp32, A/B bf16, both K-major, M=128
+// kind::f16 instruction descriptor: D fp32, A/B bf16, both K-major, M=256 (the CTA pair)
 __host__ __device__ constexpr uint32_t tc_idesc(int n_cols) {
-    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n_cols >> 3) << 17) | ((128u >> 4) << 24);
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n_cols >> 3) << 17) | ((256u >> 4) << 24);
 }
 
 #define TMEM_LD_32X32B_X32(taddr, r)                                                                                  \
@@ -170,7 +204,7 @@ struct TcArgs {
     const int32_t* in_slot;      // optional (identity when NULL)
     const int32_t* out_slot;     // optional (identity when NULL); < 0 skips the item
     const int32_t* action;       // MODE_DYN: table row; < 0 skips the item.  Otherwise optional gate.
-    const __nv_bfloat16* wB;     // [9*CIN/64][8][COUT][8]
+    const __nv_bfloat16* wB;     // [9*CIN/64][2 CTAs][8][COUT/2][8]
     const float* tbl;            // MODE_DYN: [A][9][COUT] bias table; otherwise [COUT] bias
     float* reward;
     float* value;
@@ -201,7 +235,7 @@ __host__ __device__ inline TcSmemLayout tc_smem_layout(int n, int cin, int cout,
     const int images = tc_images_per_group(n);
     L.a_bytes = (uint32_t)images * (cin / 8) * tc_ps(n) * 16;
     L.b_off = (L.a_bytes + 127) / 128 * 128;
-    L.tbl_off = L.b_off + (uint32_t)stages * cout * 128;
+    L.tbl_off = L.b_off + (uint32_t)stages * cout * 64;            // a stage = this CTA's half of a weight k-block
     L.tbl_stride = mode_dyn ? (uint32_t)images * 9 * cout * 4 : 0u;                    // per group parity
     L.pol_off = L.tbl_off + (mode_dyn ? 2 * L.tbl_stride : (uint32_t)cout * 4);
     L.pol_stride = (uint32_t)images * 384 * 4;                    // [image][position] logits, per group parity
@@ -240,31 +274,55 @@ __device__ __forceinline__ bool elect_one() {
 }
 
 // CTA b owns the contiguous items [b*B/grid, (b+1)*B/grid) (balanced to within one item) and walks them in
-// groups of up to images_per_group: the group at `base` holds cnt = min(images_per_group, hi - base) items.
-__device__ __forceinline__ int tc_items_lo(const TcArgs& a) { return (int)((long long)blockIdx.x * a.B / gridDim.x); }
-__device__ __forceinline__ int tc_items_hi(const TcArgs& a) { return (int)((long long)(blockIdx.x + 1) * a.B / gridDim.x); }
+// groups of up to images_per_group.  The two CTAs of a pair walk their groups in LOCK STEP (one MMA covers tile j of
+// both): group gi of the pair holds items [lo + gi*images, ...) of each CTA, the pair runs max(groups) groups and a
+// group has max(cnt) x tiles_per_image accumulator tiles in both CTAs; a CTA with fewer images treats the rest as
+// dead tiles (never loaded, never stored).
+struct TcRange {
+    int lo, hi, plo, phi;      // this CTA's items, the peer's items
+    int ngroups;               // groups of the pair
+};
+__device__ __forceinline__ TcRange tc_range(const TcArgs& a) {
+    TcRange r;
+    const long long b = blockIdx.x, pb = blockIdx.x ^ 1u, grid = gridDim.x;
+    r.lo = (int)(b * a.B / grid); r.hi = (int)((b + 1) * a.B / grid);
+    r.plo = (int)(pb * a.B / grid); r.phi = (int)((pb + 1) * a.B / grid);
+    const int m = max(r.hi - r.lo, r.phi - r.plo);
+    r.ngroups = (m + a.images_per_group - 1) / a.images_per_group;
+    return r;
+}
+__device__ __forceinline__ int tc_group_cnt(const TcArgs& a, int lo, int hi, int gi) {
+    return max(0, min(a.images_per_group, hi - (lo + gi * a.images_per_group)));
+}
 
-// The item records of a group: lane i holds (action, input slot, output slot) of image i, -1 beyond the
-// group.  Every role loads them one group AHEAD (three independent loads, consumed an iteration later):
-// read at the top of the group they were three dependent L2 round trips on the way to the first bulk copy,
-// in front of every accumulator tile's first store, and in the launch's tail behind the last epilogue.
+// The item records of a group: lane i < 8 holds (action, input slot, output slot) of this CTA's image i, lane 8 + i
+// those of the PEER's image i (only their liveness is used), -1 beyond the group.  Every role loads them one group
+// AHEAD (three independent loads, consumed an iteration later): read at the top of the group they were three
+// dependent L2 round trips on the way to the first bulk copy, in front of every accumulator tile's first store, and
+// in the launch's tail behind the last epilogue.
 struct TcItems {
     int act, isl, osl;
 };
-__device__ __forceinline__ TcItems tc_load_items(const TcArgs& a, int base, int items_hi, int lane) {
+__device__ __forceinline__ TcItems tc_load_items(const TcArgs& a, const TcRange& rg, int gi, int lane) {
     TcItems r;
     r.act = r.isl = r.osl = -1;
-    const int item = base + lane;
-    if (lane < a.images_per_group && item < items_hi) {
+    const int side = lane >> 3, idx = lane & 7;
+    const int item = (side ? rg.plo : rg.lo) + gi * a.images_per_group + idx;
+    if (side < 2 && idx < a.images_per_group && gi < rg.ngroups && item < (side ? rg.phi : rg.hi)) {
         r.act = a.action ? __ldg(a.action + item) : 0;
         r.isl = a.in_slot ? __ldg(a.in_slot + item) : item;
         r.osl = a.out_slot ? __ldg(a.out_slot + item) : item;
     }
     return r;
 }
-// Which images of a group are live (bit i = image i): a ballot, so every role sees the same warp-uniform mask.
+// Which images of a group are live: bit i = this CTA's image i, bit 8 + i = the peer's image i.  A ballot, so every
+// role of BOTH CTAs sees the same pair-uniform "group is live" (mask != 0); `& 0xff` = this CTA's own images.
 __device__ __forceinline__ uint32_t tc_live_mask(const TcItems& t) {
     return __ballot_sync(FULL_MASK, (t.act | t.isl | t.osl) >= 0);
+}
+// accumulator tiles of group gi in each CTA of the pair
+__device__ __forceinline__ int tc_group_tiles(const TcArgs& a, const TcRange& rg, int gi) {
+    return max(tc_group_cnt(a, rg.lo, rg.hi, gi), tc_group_cnt(a, rg.plo, rg.phi, gi)) * a.tiles_per_image;
 }
 
 struct TcCtx {
@@ -273,7 +331,7 @@ struct TcCtx {
     float* s_part;         // [parity][tile][lane quarter][value, reward]
     uint32_t tbl_stride, pol_stride;
     uint64_t* acc_full;    // [TC_SLOTS]
-    uint64_t* acc_empty;   // [TC_SLOTS]
+    uint32_t acc_empty;    // shared::cluster address of the LEADER's acc_empty[0] (the MMA issuer waits there)
     uint64_t* tbl_full;    // [2]
     uint64_t* fin_full;    // [2] epilogue -> finaliser (and producer: bias table buffer free)
     uint64_t* fin_empty;   // [2] finaliser -> epilogue
@@ -292,8 +350,8 @@ __device__ __forceinline__ void tc_epilogue_role(const TcArgs& a, const TcCtx& c
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int wq = warp & 3, pi = (warp - 2) >> 2;
     const int n = a.n, ps = a.ps, q0 = n + 2;
-    const int tpi = a.tiles_per_image, images = a.images_per_group;
-    const int items_hi = tc_items_hi(a);
+    const int tpi = a.tiles_per_image;
+    const TcRange rg = tc_range(a);
     // geometry of this thread's row in tile tt of an image (tt < 3 for n <= 19): r | c << 5 | cls << 10 | valid << 14
     uint32_t geo[3];
 #pragma unroll
@@ -315,11 +373,11 @@ __device__ __forceinline__ void tc_epilogue_role(const TcArgs& a, const TcCtx& c
     // loop -- 128 accumulators per thread leave no registers to spare -- and travel during the wait for the
     // next accumulator)
     TcItems nx = first;
-    for (int base = tc_items_lo(a); base < items_hi; base += images, nx = tc_load_items(a, base, items_hi, lane)) {
-        const int cnt = min(images, items_hi - base), NT = cnt * tpi;
-        const uint32_t live = tc_live_mask(nx);
+    for (int gi = 0; gi < rg.ngroups; gi++, nx = tc_load_items(a, rg, gi, lane)) {
+        const int NT = tc_group_tiles(a, rg, gi);                  // tiles of this group in BOTH CTAs of the pair
+        const uint32_t live_pair = tc_live_mask(nx), live = live_pair & 0xffu;
         const int my_osl = nx.osl;
-        if (!live) continue;
+        if (!live_pair) continue;
         const uint32_t par = it & 1, use = it >> 1;
         if (MODE == MODE_DYN) mbar_wait(cx.tbl_full + par, use & 1);                 // bias tables of this group have landed
         if (MODE != MODE_PLAIN) mbar_wait(cx.fin_empty + par, (use & 1) ^ 1);        // finaliser is done with this parity's buffers
@@ -347,10 +405,10 @@ __device__ __forceinline__ void tc_epilogue_role(const TcArgs& a, const TcCtx& c
                 asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
             }
             if (warp == 2 && lane == 0 && it == 2) tc_stamp(a, 18);
-            // the accumulator now lives in registers: hand the TMEM slot back to the MMA warp at once
+            // the accumulator now lives in registers: hand the TMEM slot back to the pair's MMA issuer at once
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(cx.acc_empty + slot);
+            if (lane == 0) mbar_arrive_cluster(cx.acc_empty + slot * 8);
             if (!is_live) continue;
             const uint32_t g = tt == 0 ? geo[0] : (tt == 1 ? geo[1] : geo[2]);
             const int r = g & 31, cc = (g >> 5) & 31, cls = (g >> 10) & 15;
@@ -428,15 +486,16 @@ __device__ __forceinline__ void tc_finaliser_role(const TcArgs& a, const TcCtx& 
     const int lane = threadIdx.x & 31;
     const int n = a.n, np = n * n;
     const int tpi = a.tiles_per_image, images = a.images_per_group;
-    const int items_hi = tc_items_hi(a);
+    const TcRange rg = tc_range(a);
     const float pass_logit = a.sc.pass_logit;
     uint32_t it = 0;
     TcItems nx = first;
-    for (int base = tc_items_lo(a); base < items_hi; base += images) {
-        const int cnt = min(images, items_hi - base);
-        const uint32_t live = tc_live_mask(nx);
-        nx = tc_load_items(a, base + images, items_hi, lane);
-        if (!live) continue;
+    for (int gi = 0; gi < rg.ngroups; gi++) {
+        const int base = rg.lo + gi * images;
+        const int cnt = tc_group_cnt(a, rg.lo, rg.hi, gi);
+        const uint32_t live_pair = tc_live_mask(nx), live = live_pair & 0xffu;
+        nx = tc_load_items(a, rg, gi + 1, lane);
+        if (!live_pair) continue;
         const uint32_t par = it & 1, use = it >> 1;
         if (par != which) { it++; continue; }           // the other finaliser warp's group
         mbar_wait(cx.fin_full + par, use & 1);
@@ -570,16 +629,17 @@ struct TcMmaState {
     uint32_t a_lo[TC_SLOTS];     // descriptor of tile j of a group (image j / tpi, tile j % tpi), tap (0,0), chunk 0
 };
 
-// All MMAs of one group of NT tiles (NT = live images of the group x tiles per image).
+// All MMAs of one group of NT tiles per CTA (NT = images of the group x tiles per image; MMA j covers tile j of BOTH
+// CTAs of the pair).  Runs in the leader CTA only.
 template <int CIN, int COUT, int NT>
 __device__ __forceinline__ void tc_mma_group(const TcArgs& a, const TcMmaCtx& mx, TcMmaState& st) {
     constexpr int NH = CIN / 64;
-    constexpr uint32_t STAGE_BYTES = COUT * 128;
+    constexpr uint32_t STAGE_BYTES = COUT * 64;             // this CTA's half of a weight k-block: [8 chunks][COUT/2][8]
     constexpr uint32_t IDESC = tc_idesc(COUT);
     const int lane = threadIdx.x & 31;
     const int n = a.n, ps = a.ps;
     const uint32_t a_hi = desc_hi(128), b_hi = desc_hi(128);
-    const uint32_t b_lo0 = desc_lo(mx.sB, COUT * 16);
+    const uint32_t b_lo0 = desc_lo(mx.sB, (COUT / 2) * 16);
     const uint32_t ks_step = 2 * ps;
     const uint32_t tile_ctr = st.tile_ctr, it = st.it;
     uint32_t s = st.s, bph = st.bph;
@@ -609,15 +669,15 @@ __device__ __forceinline__ void tc_mma_group(const TcArgs& a, const TcMmaCtx& mx
                 for (int ks = 0; ks < 4; ks++) {
 #pragma unroll
                     for (int j = 0; j < NT; j++)
-                        umma_bf16(d_col[j], st.a_lo[j] + a_off + ks * ks_step, a_hi, b_lo + ks * (2 * COUT), b_hi, IDESC,
+                        umma_bf16(d_col[j], st.a_lo[j] + a_off + ks * ks_step, a_hi, b_lo + ks * COUT, b_hi, IDESC,
                                   ks == 0 ? acc0 : 1u);
                 }
-                umma_commit(mx.b_empty + s);          // frees the weight stage when these MMAs retire
+                umma_commit(mx.b_empty + s);          // frees the weight stage (in both CTAs) when these MMAs retire
             }
             __syncwarp();
             if (++s == (uint32_t)a.stages) { s = 0; bph ^= 1; }
         }
-        if (leader) umma_commit(mx.a_empty + h);      // this half of the input slab may be overwritten
+        if (leader) umma_commit(mx.a_empty + h);      // this half of the input slabs (both CTAs') may be overwritten
     }
     if (leader) {
 #pragma unroll
@@ -636,7 +696,7 @@ __device__ __forceinline__ void tc_mma_role(const TcArgs& a, const TcMmaCtx& mx,
     constexpr int KC_IN = CIN / 8;
     const int lane = threadIdx.x & 31;
     const int ps = a.ps, q0 = a.n + 2;
-    const int tpi = a.tiles_per_image, images = a.images_per_group;
+    const int tpi = a.tiles_per_image;
     const uint32_t slab_bytes = (uint32_t)KC_IN * ps * 16;
     TcMmaState st;
     st.it = st.s = st.bph = st.tile_ctr = 0;
@@ -646,14 +706,13 @@ __device__ __forceinline__ void tc_mma_role(const TcArgs& a, const TcMmaCtx& mx,
         const int img = j / tpi, tt = j - img * tpi;
         st.a_lo[j] = desc_lo(mx.sA + img * slab_bytes + (uint32_t)(q0 + tt * 128) * 16, ps * 16);
     }
-    const int items_hi = tc_items_hi(a);
+    const TcRange rg = tc_range(a);
     TcItems nx = first;
-    for (int base = tc_items_lo(a); base < items_hi; base += images) {
-        const int cnt = min(images, items_hi - base);
-        const uint32_t live = tc_live_mask(nx);
-        nx = tc_load_items(a, base + images, items_hi, lane);
-        if (!live) continue;
-        switch (cnt * tpi) {
+    for (int gi = 0; gi < rg.ngroups; gi++) {
+        const uint32_t live_pair = tc_live_mask(nx);
+        nx = tc_load_items(a, rg, gi + 1, lane);
+        if (!live_pair) continue;
+        switch (tc_group_tiles(a, rg, gi)) {
             case 1: tc_mma_group<CIN, COUT, 1>(a, mx, st); break;
             case 2: tc_mma_group<CIN, COUT, 2>(a, mx, st); break;
             default: tc_mma_group<CIN, COUT, 3>(a, mx, st); break;
@@ -661,13 +720,44 @@ __device__ __forceinline__ void tc_mma_role(const TcArgs& a, const TcMmaCtx& mx,
     }
 }
 
+// ---------------------------------------------------------------------------------------- relay role
+// Warp 1 of the pair's SECOND CTA.  The MMA issuer sits in the leader CTA and can only wait on its own barriers; a
+// bulk copy signals a barrier of the CTA it writes to.  So this warp waits, in the issuer's order, for this CTA's
+// slab halves and weight stages to land and passes each completion on to the leader's barrier of the same name (which
+// counts two arrivals per phase: the leader's own producer and this one).  It can never run a phase ahead: a stage is
+// only refilled after the leader's commit freed it, i.e. after the leader consumed the phase before.
+template <int CIN>
+__device__ __forceinline__ void tc_relay_role(const TcArgs& a, uint64_t* a_full, uint64_t* b_full, const TcItems& first) {
+    constexpr int NH = CIN / 64;
+    const int lane = threadIdx.x & 31;
+    const uint32_t ra_full = mapa_u32(smem_u32(a_full), 0), rb_full = mapa_u32(smem_u32(b_full), 0);
+    const TcRange rg = tc_range(a);
+    uint32_t it = 0, s = 0, bph = 0;
+    TcItems nx = first;
+    for (int gi = 0; gi < rg.ngroups; gi++) {
+        const uint32_t live_pair = tc_live_mask(nx);
+        nx = tc_load_items(a, rg, gi + 1, lane);
+        if (!live_pair) continue;
+        for (int h = 0; h < NH; h++) {
+            mbar_wait(a_full + h, it & 1);
+            if (lane == 0) mbar_arrive_cluster(ra_full + h * 8);
+            for (int tap = 0; tap < 9; tap++) {
+                mbar_wait(b_full + s, bph);
+                if (lane == 0) mbar_arrive_cluster(rb_full + s * 8);
+                if (++s == (uint32_t)a.stages) { s = 0; bph ^= 1; }
+            }
+        }
+        it++;
+    }
+}
+
 // ---------------------------------------------------------------------------------------- the fused kernel
+// Launched as clusters of two CTAs (launch_tc_conv): blockIdx.x ^ 1 is the peer, cluster rank 0 the pair's leader.
 template <int CIN, int COUT, int MODE>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 k_tc_conv(const __grid_constant__ TcArgs a) {
     constexpr int KC_IN = CIN / 8, NH = CIN / 64;
-    constexpr uint32_t STAGE_BYTES = COUT * 128;          // [8 chunks][COUT][8] bf16
-    constexpr uint32_t IDESC = tc_idesc(COUT);
+    constexpr uint32_t STAGE_BYTES = COUT * 64;           // this CTA's half of a weight k-block: [8 chunks][COUT/2][8] bf16
     extern __shared__ __align__(128) uint8_t smem[];
     const TcSmemLayout L = tc_smem_layout(a.n, CIN, COUT, a.stages, MODE == MODE_DYN);
     uint8_t* sA = smem;
@@ -676,7 +766,7 @@ k_tc_conv(const __grid_constant__ TcArgs a) {
     uint64_t* a_full = bars + 0;                    // [2] input slab halves
     uint64_t* a_empty = bars + 2;                   // [2]
     uint64_t* acc_full = bars + 4;                  // [TC_SLOTS]
-    uint64_t* acc_empty = bars + 4 + TC_SLOTS;      // [TC_SLOTS]
+    uint64_t* acc_empty = bars + 4 + TC_SLOTS;      // [TC_SLOTS] (the leader's are the ones in use)
     uint64_t* b_full = bars + 4 + 2 * TC_SLOTS;     // [TC_MAX_STAGES]
     uint64_t* b_empty = b_full + TC_MAX_STAGES;     // [TC_MAX_STAGES]
     uint64_t* tbl_full = b_empty + TC_MAX_STAGES;   // [2] per-action bias tables of a group (DYN)
@@ -685,53 +775,58 @@ k_tc_conv(const __grid_constant__ TcArgs a) {
     uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + TC_NUM_BARS);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int n = a.n, ps = a.ps;
-    const int images = a.images_per_group;
+    const int ps = a.ps;
     const uint32_t slab_bytes = (uint32_t)KC_IN * ps * 16;
     const uint32_t half_bytes = slab_bytes / NH;
-    const int q0 = n + 2;                           // flat position of pixel (0,0)
+    const uint32_t rank = cluster_ctarank();
+    const bool leader_cta = rank == 0;
 
     if (threadIdx.x == 0) {
-        for (int h = 0; h < 2; h++) { mbar_init(a_full + h, 1); mbar_init(a_empty + h, 1); }
-        for (int s = 0; s < TC_SLOTS; s++) { mbar_init(acc_full + s, 1); mbar_init(acc_empty + s, 4); }
-        for (int s = 0; s < TC_MAX_STAGES; s++) { mbar_init(b_full + s, 1); mbar_init(b_empty + s, 1); }
+        // "operands landed" barriers of the leader count two arrivals per phase: its own producer (with the bytes) and
+        // the peer's relay warp; the leader's acc_empty collect the epilogue warps of both CTAs
+        const uint32_t full_count = leader_cta ? 2 : 1;
+        for (int h = 0; h < 2; h++) { mbar_init(a_full + h, full_count); mbar_init(a_empty + h, 1); }
+        for (int s = 0; s < TC_SLOTS; s++) { mbar_init(acc_full + s, 1); mbar_init(acc_empty + s, 8); }
+        for (int s = 0; s < TC_MAX_STAGES; s++) { mbar_init(b_full + s, full_count); mbar_init(b_empty + s, 1); }
         for (int p = 0; p < 2; p++) { mbar_init(tbl_full + p, 1); mbar_init(fin_full + p, 8); mbar_init(fin_empty + p, 1); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 1) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(s_tmem)) : "memory");
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    if (warp == 1) {            // the same warp of both CTAs: accumulators at the same TMEM address in both SMs
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(s_tmem)) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
     }
-    // everything above is private to the CTA; what follows reads what the kernel before this one wrote (PDL, common.cuh)
+    // everything above is private to the pair; what follows reads what the kernel before this one wrote (PDL, common.cuh)
     griddep_wait();
     griddep_launch();
     if (threadIdx.x == 0) tc_stamp(a, 0);
-    // the first group's item records travel while the set-up above is published to the CTA
-    const TcItems first = tc_load_items(a, tc_items_lo(a), tc_items_hi(a), lane);
+    // the first group's item records travel while the set-up above is published to the pair
+    const TcRange rg = tc_range(a);
+    const TcItems first = tc_load_items(a, rg, 0, lane);
     tc_fence_before();
-    __syncthreads();
+    cluster_sync_all();         // both CTAs: barriers initialised, TMEM allocated, before any remote arrive / multicast commit
     tc_fence_after();
     const uint32_t tmem_base = *s_tmem;
     if (threadIdx.x == 0) tc_stamp(a, 1);
 
     if (warp == 0) {
         // ===================================================== TMA producer (lane 0 issues, the warp stays converged)
+        // own images' slabs and bias tables, and THIS CTA's half (output channels [rank*COUT/2, ...)) of every k-block
         uint32_t it = 0, s = 0, bph = 0;
         const uint64_t pol_stream = l2_policy_evict_first(), pol_keep = l2_policy_evict_last();
-        const int items_hi = tc_items_hi(a);
+        const uint8_t* w_half = reinterpret_cast<const uint8_t*>(a.wB) + (size_t)rank * STAGE_BYTES;
         TcItems nx = first;
-        for (int base = tc_items_lo(a); base < items_hi; base += images) {
+        for (int gi = 0; gi < rg.ngroups; gi++) {
             const TcItems cur = nx;
-            const uint32_t live = tc_live_mask(cur);
-            nx = tc_load_items(a, base + images, items_hi, lane);
-            if (!live) continue;
+            const uint32_t live_pair = tc_live_mask(cur), live = live_pair & 0xffu;
+            nx = tc_load_items(a, rg, gi + 1, lane);
+            if (!live_pair) continue;
             if (MODE == MODE_DYN) {
                 // per-action bias tables of this group -> s_tbl[parity] (free once the epilogue of group it-2 is through)
                 const uint32_t par = it & 1, use = it >> 1;
                 if (use > 0) mbar_wait(fin_full + par, (use - 1) & 1);
                 if (lane == 0) mbar_expect_tx(tbl_full + par, 9u * COUT * 4 * __popc(live));
                 __syncwarp();
-                if ((live >> lane) & 1u)
+                if (lane < 8 && ((live >> lane) & 1u))
                     bulk_g2s(smem + L.tbl_off + par * L.tbl_stride + (uint32_t)lane * 9 * COUT * 4,
                              a.tbl + (size_t)cur.act * 9 * COUT, 9u * COUT * 4, tbl_full + par);
             }
@@ -739,7 +834,7 @@ k_tc_conv(const __grid_constant__ TcArgs a) {
                 mbar_wait(a_empty + h, (it & 1) ^ 1);
                 if (lane == 0) mbar_expect_tx(a_full + h, half_bytes * __popc(live));
                 __syncwarp();
-                if ((live >> lane) & 1u) {
+                if (lane < 8 && ((live >> lane) & 1u)) {
                     const uint8_t* src = reinterpret_cast<const uint8_t*>(a.in) + (size_t)cur.isl * slab_bytes + (size_t)h * half_bytes;
                     if (MODE == MODE_DYN) bulk_g2s_hint(sA + (size_t)lane * slab_bytes + (size_t)h * half_bytes, src, half_bytes, a_full + h, pol_stream);
                     else bulk_g2s(sA + (size_t)lane * slab_bytes + (size_t)h * half_bytes, src, half_bytes, a_full + h);
@@ -748,8 +843,7 @@ k_tc_conv(const __grid_constant__ TcArgs a) {
                     mbar_wait(b_empty + s, bph ^ 1);
                     if (lane == 0) {
                         mbar_expect_tx(b_full + s, STAGE_BYTES);
-                        bulk_g2s_hint(sB + s * STAGE_BYTES,
-                                      reinterpret_cast<const uint8_t*>(a.wB) + (size_t)(h * 9 + tap) * STAGE_BYTES, STAGE_BYTES,
+                        bulk_g2s_hint(sB + s * STAGE_BYTES, w_half + (size_t)(h * 9 + tap) * 2 * STAGE_BYTES, STAGE_BYTES,
                                       b_full + s, pol_keep);
                     }
                     if (++s == (uint32_t)a.stages) { s = 0; bph ^= 1; }
@@ -758,13 +852,18 @@ k_tc_conv(const __grid_constant__ TcArgs a) {
             it++;
         }
     } else if (warp == 1) {
-        // ===================================================== MMA issuer
-        TcMmaCtx mx;
-        mx.sA = smem_u32(sA); mx.sB = smem_u32(sB);
-        mx.a_full = a_full; mx.a_empty = a_empty; mx.b_full = b_full; mx.b_empty = b_empty;
-        mx.acc_full = acc_full; mx.acc_empty = acc_empty;
-        mx.tmem_base = tmem_base;
-        tc_mma_role<CIN, COUT>(a, mx, first);
+        if (leader_cta) {
+            // ===================================================== MMA issuer of the pair
+            TcMmaCtx mx;
+            mx.sA = smem_u32(sA); mx.sB = smem_u32(sB);
+            mx.a_full = a_full; mx.a_empty = a_empty; mx.b_full = b_full; mx.b_empty = b_empty;
+            mx.acc_full = acc_full; mx.acc_empty = acc_empty;
+            mx.tmem_base = tmem_base;
+            tc_mma_role<CIN, COUT>(a, mx, first);
+        } else {
+            // ===================================================== relay: this CTA's landed operands -> the leader's barriers
+            tc_relay_role<CIN>(a, a_full, b_full, first);
+        }
     } else {
         TcCtx cx;
         cx.s_tbl = smem + L.tbl_off;
@@ -773,7 +872,7 @@ k_tc_conv(const __grid_constant__ TcArgs a) {
         cx.tbl_stride = L.tbl_stride;
         cx.pol_stride = L.pol_stride;
         cx.acc_full = acc_full;
-        cx.acc_empty = acc_empty;
+        cx.acc_empty = mapa_u32(smem_u32(acc_empty), 0);
         cx.tbl_full = tbl_full;
         cx.fin_full = fin_full;
         cx.fin_empty = fin_empty;
@@ -788,8 +887,9 @@ k_tc_conv(const __grid_constant__ TcArgs a) {
         // ===================================================== tree phase (tree_step.cuh, the code of k_tree_step)
         // Item i of the launch is game i's leaf, and a CTA's items are a contiguous range of games: what the
         // search does with the outputs is CTA-local.  The finalisers' value / reward / policy stores are ordered
-        // before these (L2) loads by the barrier above; the scratch aliases the input slabs, which are dead.
-        const int g_lo = tc_items_lo(a), g_hi = tc_items_hi(a);
+        // before these (L2) loads by the barrier above; the scratch aliases the input slabs, which are dead (this
+        // CTA's accumulators are complete, so the pair's MMAs have read both CTAs' slabs for the last time).
+        const int g_lo = rg.lo, g_hi = rg.hi;
         const int do_select = a.tree_mode == 1;
         const int sub128 = threadIdx.x >> 7;
         if (a.tree.A <= STEP_EPT * 32) {
@@ -805,18 +905,22 @@ k_tc_conv(const __grid_constant__ TcArgs a) {
         }
         if (threadIdx.x == 0) tc_stamp(a, 31);
     }
+    // nobody leaves, and the TMEM goes back, only when the peer is through with this CTA's barriers / shared memory too
+    cluster_sync_all();
     if (warp == 1) {
         tc_fence_after();
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem_base) : "memory");
+        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, 512;" ::"r"(tmem_base) : "memory");
     }
 }
 
 // ---------------------------------------------------------------------------------------- weight preparation
-// wB[kb = half*9 + tap][kc][co][e] = bf16(W[co][half*64 + kc*8 + e][tap])      (W = [Cout][Cin][3][3])
+// wB[kb = half*9 + tap][r][kc][j][e] = bf16(W[r*cout/2 + j][half*64 + kc*8 + e][tap])      (W = [Cout][Cin][3][3])
+// r = the CTA of the pair that stages this half of the output channels: each (kb, r) block is one contiguous bulk copy
 __global__ void k_tc_prep_w(const float* __restrict__ w, __nv_bfloat16* __restrict__ wB, int cin, int cout) {
-    const int total = 9 * cin * cout;
+    const int total = 9 * cin * cout, ch = cout / 2;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
-        const int e = i & 7, co = (i >> 3) % cout, kc = ((i >> 3) / cout) & 7, kb = (i >> 3) / (cout * 8);
+        const int e = i & 7, j = (i >> 3) % ch, kc = ((i >> 3) / ch) & 7, r = ((i >> 3) / (ch * 8)) & 1, kb = (i >> 3) / (cout * 8);
+        const int co = r * ch + j;
         const int half = kb / 9, tap = kb - half * 9;
         const int ci = half * 64 + kc * 8 + e;
         wB[i] = __float2bfloat16_rn(w[((size_t)co * cin + ci) * 9 + tap]);
@@ -1015,14 +1119,15 @@ int launch_tc_conv(TcArgs& a, int n, int B, cudaStream_t st) {
     a.images_per_group = tc_images_per_group(n);
     const int kblocks = 9 * CIN / 64;
     const TcSmemLayout L0 = tc_smem_layout(n, CIN, COUT, 0, MODE == MODE_DYN);
-    int stages = ((int)TC_SMEM_LIMIT - (int)L0.total) / (COUT * 128);
+    int stages = ((int)TC_SMEM_LIMIT - (int)L0.total) / (COUT * 64);
     if (stages > TC_MAX_STAGES) stages = TC_MAX_STAGES;
     if (stages > kblocks) stages = kblocks;
     MZGO_CHECK_ARG(stages >= 2, "shared memory layout of %u B leaves no room for the weight ring", L0.total);
     a.stages = stages;
     const TcSmemLayout L = tc_smem_layout(n, CIN, COUT, stages, MODE == MODE_DYN);
-    const int grid = B < num_sms() ? B : num_sms();
-    MZGO_CUDA(mzgo_launch_pdl(k_tc_conv<CIN, COUT, MODE>, dim3(grid), dim3(TC_THREADS), L.total, st, a));
+    // CTA pairs (clusters of two, the two SMs of a TPC): an even grid, at most one CTA per SM
+    const int pairs = std::max(1, std::min((B + 1) / 2, num_sms() / 2));
+    MZGO_CUDA(mzgo_launch_pdl_cluster(k_tc_conv<CIN, COUT, MODE>, dim3(2 * pairs), dim3(TC_THREADS), L.total, st, 2u, a));
     mzgo_count_launch();
     MZGO_LAUNCH_CHECK();
     return MZGO_OK;

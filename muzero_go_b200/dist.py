@@ -37,6 +37,65 @@ def broadcast_weights(module, src=0, group=None):
     return flat.numel() * flat.element_size()
 
 
+ROW_FIELDS = ("boards", "action", "policy", "root_value", "reward", "done", "winner")
+
+
+def row_field_bytes(action_size):
+    """Bytes of every field of one (move, game) trajectory record, in ROW_FIELDS order."""
+    return [256, 4, 4 * int(action_size), 4, 4, 1, 1]
+
+
+def row_stride(action_size):
+    return sum(row_field_bytes(action_size))
+
+
+class RowRing:
+    """`depth` trajectory rows of G games as ONE preallocated uint8 [depth, G, stride] buffer in the wire layout of
+    pack_rows / unpack_rows.  write() fills a row with slice copies straight from the engines' trajectory buffers
+    (no torch.cat, no allocation per step); the buffer is what gets all-gathered, `depth` moves at a time
+    ("batched per K moves so messages are >= 1 MB")."""
+
+    def __init__(self, num_games, action_size, depth, device):
+        self.G, self.A, self.depth = int(num_games), int(action_size), int(depth)
+        self.sizes = row_field_bytes(action_size)
+        self.buf = torch.zeros((self.depth, self.G, sum(self.sizes)), dtype=torch.uint8, device=device)
+
+    def write(self, t, rows_per_engine):
+        """rows_per_engine: one dict of [1, G_w, ...] tensors per engine (SelfPlayEngine.trajectory_rows(r, r + 1)),
+        engines in game order."""
+        g0 = 0
+        for rows in rows_per_engine:
+            gw = rows["action"].shape[1]
+            off = 0
+            for key, nbytes in zip(ROW_FIELDS, self.sizes):
+                src = rows[key][0]
+                self.buf[t, g0:g0 + gw, off:off + nbytes].copy_(src.contiguous().view(torch.uint8).reshape(gw, nbytes))
+                off += nbytes
+            g0 += gw
+        assert g0 == self.G
+
+    def rows(self, lo=0, hi=None):
+        """The ring's rows [lo, hi) as a dict of tensors (unpack_rows)."""
+        return unpack_rows(self.buf[lo:self.depth if hi is None else hi], self.A)
+
+
+def all_gather_rows(out, buf, group=None):
+    """out [world, ...] <- every rank's buf [...] in one collective (the per-rank slices of `out` are contiguous views
+    of one tensor, which NCCL gathers in place; works on gloo too)."""
+    dist.all_gather(list(out.unbind(0)), buf, group=group)
+
+
+def gather_ring(ring, group=None):
+    """all_gather of a whole RowRing: -> dict of [depth, sum G_r, ...] tensors on every rank."""
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return ring.rows(), ring.buf.numel()
+    world = dist.get_world_size(group)
+    out = torch.empty((world,) + tuple(ring.buf.shape), dtype=torch.uint8, device=ring.buf.device)
+    all_gather_rows(out, ring.buf, group)
+    merged = out.permute(1, 0, 2, 3).reshape(ring.depth, world * ring.G, -1)
+    return unpack_rows(merged.contiguous(), ring.A), out.numel()
+
+
 def pack_rows(rows):
     """Trajectory rows (dict of [T,G,...] tensors, SelfPlayEngine.trajectory_rows) -> one uint8 [T,G,stride]."""
     T, G = rows["action"].shape[:2]

@@ -41,6 +41,18 @@ def test_pack_unpack_round_trip():
         assert torch.equal(rows[k], back[k]), k
 
 
+def test_row_ring_equals_pack_rows():
+    A, depth, Gw = 82, 4, 3
+    waves = [fake_rows(depth, Gw, A, seed=s) for s in (1, 2)]
+    ring = mzdist.RowRing(2 * Gw, A, depth, "cpu")
+    for t in range(depth):
+        ring.write(t, [{k: v[t:t + 1] for k, v in w.items()} for w in waves])
+    want = mzdist.pack_rows({k: torch.cat([w[k] for w in waves], dim=1) for k in waves[0]})
+    assert ring.buf.shape[2] == mzdist.row_stride(A) and torch.equal(ring.buf, want)
+    back = ring.rows()
+    assert torch.equal(back["policy"][:, Gw:], waves[1]["policy"])
+
+
 def _worker(rank, world, port, out):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
@@ -62,7 +74,20 @@ def _worker(rank, world, port, out):
             ref = fake_rows(2, 3, 26, seed=r)
             for k in ref:
                 ok_gather &= torch.equal(gathered[k][:, 3 * r:3 * r + 3], ref[k])
-        out[rank] = bool(ok_bcast and ok_gather)
+        # the ring: `depth` moves of two waves packed with slice copies, gathered in one collective
+        depth, Gw = 3, 2
+        ring = mzdist.RowRing(2 * Gw, 26, depth, "cpu")
+        for t in range(depth):
+            ring.write(t, [{k: v[t:t + 1] for k, v in fake_rows(depth, Gw, 26, seed=10 * rank + w).items()} for w in range(2)])
+        merged, nbytes_ring = mzdist.gather_ring(ring)
+        ok_ring = nbytes_ring == world * depth * 2 * Gw * mzdist.row_stride(26)
+        for r in range(world):
+            for w in range(2):
+                ref = fake_rows(depth, Gw, 26, seed=10 * r + w)
+                lo = r * 2 * Gw + w * Gw
+                for k in ref:
+                    ok_ring &= torch.equal(merged[k][:, lo:lo + Gw], ref[k])
+        out[rank] = bool(ok_bcast and ok_gather and ok_ring)
     finally:
         dist.destroy_process_group()
 

@@ -1,0 +1,2 @@
+mkdir -p gpurun_out/r02
+timeout 120 tools/bin/mma2_probe > gpurun_out/r02/mma2_probe.txt 2>&1; echo probe rc=$?; cat gpurun_out/r02/mma2_probe.txt
