@@ -282,11 +282,14 @@ def measure(args, wl, G, S, K, W, rank, world, dev, primary):
     # take turns on one set of search buffers (muzero_go_b200.WaveGroup): still G games, one move each per step.
     free_b, _ = torch.cuda.mem_get_info()
     per_game = (S + 1) * (net.slot_bytes() + A * 18 + 8) + 64 * 1024
-    waves = 1
-    while (G // waves) * per_game > 0.90 * free_b or G % waves:
-        waves += 1
-    group = mz.WaveGroup(net, n, G, S, waves=waves, search=mz.SearchConfig(seed=1000, game_base=rank * G), traj_capacity=2,
-                         restart_finished=True)
+    # `streams` sets of search buffers are alive at once (waves on different streams overlap: one wave's tree step
+    # under another wave's network kernel, muzero_go_b200.WaveGroup)
+    streams = max(1, args.streams)
+    waves = streams
+    while streams * (G // waves) * per_game > 0.90 * free_b or G % waves:
+        waves += streams
+    group = mz.WaveGroup(net, n, G, S, waves=waves, streams=streams, search=mz.SearchConfig(seed=1000, game_base=rank * G),
+                         traj_capacity=2, restart_finished=True)
     eng = group.engines[0]          # the single-kernel timings below run on one wave's buffers
     GW = G // waves
     lib = _lib.load()
@@ -390,7 +393,7 @@ def measure(args, wl, G, S, K, W, rank, world, dev, primary):
         print(f"[bench debug] rank {rank}: timed {ms:.3f} ms / {sims_done} sims, e2e {e2e_s * 1e3:.3f} ms / {e2e_sims} sims",
               file=sys.stderr)
     res = dict(ms=ms, e2e_ms=e2e_s * 1000.0, sims=sims_done, moves=moves_done, e2e_sims=e2e_sims, launches=launches, G=G,
-               depth=depth, waves=waves, GW=GW, clocks=clocks, bytes_bcast=bytes_bcast, arena_gb=eng.arena.numel() / 1e9,
+               depth=depth, waves=waves, GW=GW, streams=streams, clocks=clocks, bytes_bcast=bytes_bcast, arena_gb=eng.arena.numel() / 1e9,
                h2d=G * 256, d2h=int(row_ring.buf.numel()) + G * 256, graph_replays=int(lib.mzgo_graph_replays()),
                exchange={"rows_per_gather": exch_depth, "bytes_per_gather_per_rank": int(exch.ring.buf.numel()),
                          "stream": "side stream, event-ordered"})
@@ -595,7 +598,7 @@ def run_ours(args, wl):
                 "steps": K, "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "bf16" if args.precision == "bf16" else "f32", "data": "synthetic",
                 "config": cfg,
-                "run": {"games_total": int(G_all), "waves": r["waves"], "games_per_wave": r["GW"],
+                "run": {"games_total": int(G_all), "waves": r["waves"], "games_per_wave": r["GW"], "streams": r["streams"],
                         "latent_arena_gb_per_gpu": r["arena_gb"], "trajectory_exchange": r["exchange"]},
                 "moves_per_sec": moves_all / (ms * 1e-3), "mean_leaf_depth": r["depth"],
                 "timed_region_s": ms * 1e-3,
@@ -744,6 +747,8 @@ def main():
                     help="19x19 = BASELINE configs[3], the north-star configuration (default); 9x9 = configs[1]")
     ap.add_argument("--no-secondary", action="store_true", help="skip the 9x9 figures printed beside the 19x19 line")
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--streams", type=int, default=1,
+                    help="CUDA streams (sets of search buffers) the waves of games are spread over; 1 = one wave at a time")
     ap.add_argument("--games", type=int, default=0)
     ap.add_argument("--sims", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")

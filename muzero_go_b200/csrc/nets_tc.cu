@@ -44,7 +44,7 @@
 namespace {
 
 constexpr int TC_C = 128;               // latent_dim of the tensor-core path
-constexpr int TC_THREADS = 384;         // producer, MMA issuer, 8 epilogue warps, 2 finalisers (384 x 168 registers)
+constexpr int TC_THREADS = 384;         // producer, MMA issuer / relay, 8 epilogue warps, 2 finalisers (384 x 168 registers)
 constexpr int TC_EPI_THREADS = 256;
 constexpr int TC_MAX_STAGES = 12;       // weight k-block ring (half a k-block per CTA and stage; as many as fit)
 constexpr int TC_SLOTS = 4;             // 4 x 128 TMEM columns

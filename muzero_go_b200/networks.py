@@ -83,10 +83,8 @@ class MuZeroNet(nn.Module):
         self.prediction = PredictionNetwork(latent_dim)
         for m in (self.representation, self.dynamics, self.prediction):
             m._owner = [self]          # a list keeps the owner out of the module tree
-        self._ws = None
-        self._ws_key = None
+        self._ws = None            # {ws_key: {"ws": tensor, "key": (max_batch, precision, device), "prepared": key}}
         self._desc = None
-        self._prepared_key = None
         self._weights_version = 0
 
     # ------------------------------------------------------------------ descriptor / workspace
@@ -105,9 +103,13 @@ class MuZeroNet(nn.Module):
     def slot_bytes(self):
         return int(_lib.load().mzgo_net_slot_bytes(self.board_size, self.latent_dim, PRECISIONS[self.precision]))
 
-    def descriptor(self, max_batch):
+    def descriptor(self, max_batch, ws_key=0):
         """mzgo_net_t for the current parameters; (re)derives the kernel-side weight layouts when the
-        parameters changed (load_state_dict, optimizer step, broadcast)."""
+        parameters changed (load_state_dict, optimizer step, broadcast).
+
+        ws_key names the workspace: the workspace holds the prepared weight layouts AND the representation network's
+        scratch activations, so callers that evaluate the network concurrently on different CUDA streams
+        (WaveGroup(streams=2)) must use different keys."""
         _lib.require_device()
         params = self._params_in_abi_order()
         dev = params[0].device
@@ -117,24 +119,27 @@ class MuZeroNet(nn.Module):
             if t.dtype != torch.float32 or not t.is_contiguous() or t.device != dev:
                 raise _lib.MzgoError("MuZeroNet parameters must be contiguous float32 tensors on one device")
         prec = PRECISIONS[self.precision]
-        ws_key = (int(max_batch), prec, dev)
-        if self._ws is None or self._ws_key is None or self._ws_key[0] < max_batch or self._ws_key[1:] != ws_key[1:]:
+        if self._ws is None:
+            self._ws = {}
+        slot = self._ws.get(ws_key)
+        want = (int(max_batch), prec, dev)
+        if slot is None or slot["key"][0] < max_batch or slot["key"][1:] != want[1:]:
             nbytes = int(_lib.load().mzgo_net_workspace_bytes(self.board_size, self.latent_dim, prec, int(max_batch)))
-            self._ws = torch.zeros(nbytes, dtype=torch.uint8, device=dev)
-            self._ws_key = ws_key
-            self._prepared_key = None
+            slot = {"ws": torch.zeros(nbytes, dtype=torch.uint8, device=dev), "key": want, "prepared": None}
+            self._ws[ws_key] = slot
+        ws = slot["ws"]
         d = _lib.NetDesc()
         d.n, d.C, d.A, d.precision = self.board_size, self.latent_dim, self.action_size, prec
-        d.max_batch = self._ws_key[0]
+        d.max_batch = slot["key"][0]
         for name, t in zip(_lib.NET_PARAM_FIELDS, params):
             setattr(d, name, t.data_ptr())
-        d.workspace, d.workspace_bytes = self._ws.data_ptr(), self._ws.numel()
+        d.workspace, d.workspace_bytes = ws.data_ptr(), ws.numel()
         # tensor._version catches eager in-place updates (optimizer.step, load_state_dict, broadcast); a replayed
         # CUDA graph updates the parameters WITHOUT touching it, hence the explicit counter (mark_weights_changed)
-        key = tuple((t.data_ptr(), t._version) for t in params) + (self._ws.data_ptr(), self._weights_version)
-        if key != self._prepared_key:
+        key = tuple((t.data_ptr(), t._version) for t in params) + (ws.data_ptr(), self._weights_version)
+        if key != slot["prepared"]:
             _lib.check(_lib.load().mzgo_net_prepare(d, _lib.stream_ptr()))
-            self._prepared_key = key
+            slot["prepared"] = key
         self._desc = d
         return d
 

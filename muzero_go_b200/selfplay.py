@@ -22,7 +22,7 @@ COUNTER_NAMES = ["moves", "simulations", "games_finished", "dropped_simulations"
 class SelfPlayEngine:
     def __init__(self, net, board_size, num_games, num_simulations, search=None, max_game_moves=None,
                  temperature=0.0, temperature_moves=0, komi=0.0, restart_finished=True, traj_capacity=8,
-                 device=None, share_search_buffers_with=None):
+                 device=None, share_search_buffers_with=None, ws_key=0):
         _lib.require_device()
         self.net = net
         self.n = int(board_size)
@@ -32,6 +32,7 @@ class SelfPlayEngine:
         self.A = self.n * self.n + 1
         self.M = self.S + 1
         self.search = search or SearchConfig()
+        self.ws_key = ws_key          # which network workspace (weight layouts + scratch) this engine evaluates with
         dev = self.device = _lib.norm_device(device if device is not None else net.prediction.pass_logit.device)
         self.max_game_moves = int(self.n * self.n * 1.5) if max_game_moves is None else int(max_game_moves)  # main.py:53
         self.temperature, self.temperature_moves = float(temperature), int(temperature_moves)
@@ -85,7 +86,7 @@ class SelfPlayEngine:
         d = _lib.SelfPlayDesc()
         d.tree = self.tree.desc
         d.params = self.search.to_struct()
-        d.net = self.net.descriptor(self.G)
+        d.net = self.net.descriptor(self.G, self.ws_key)
         d.n, d.num_simulations, d.max_game_moves = self.n, self.S, self.max_game_moves
         d.temperature_moves, d.temperature, d.komi = self.temperature_moves, self.temperature, self.komi
         d.restart_finished, d.traj_capacity = int(self.restart_finished), self.T
@@ -118,31 +119,60 @@ class SelfPlayEngine:
 
 
 class WaveGroup:
-    """`waves` engines of num_games / waves games each that take turns on ONE set of search buffers: every
-    call of run(k) plays k moves of every game, wave after wave.  This is how a game count whose latent arena
-    would not fit the HBM runs on one GPU (19x19, 800 simulations: 2048 games need 177 GB of latents at once,
-    two waves of 1024 need 89 GB); throughput is unchanged because the games are independent and a wave of
-    1024 leaves already fills the persistent network kernel (6.9 leaves per SM)."""
+    """`waves` engines of num_games / waves games each.  Every call of run(k) plays k moves of every game.
 
-    def __init__(self, net, board_size, num_games, num_simulations, waves=1, search=None, **kw):
+    Waves that run on the same stream take turns on ONE set of search buffers (trees, latent arena, scratch): a search
+    only lives for one move.  This is how a game count whose latent arena would not fit the HBM runs on one GPU
+    (19x19, 800 simulations: 2048 games need 177 GB of latents at once).
+
+    `streams` > 1 runs the waves round-robin on that many CUDA streams, each with its own set of search buffers, so
+    that the kernels of different waves overlap: the per-simulation loop of a wave is a chain [tree step -> network
+    kernel -> tree step ...] in which the latency-bound tree step (three dependent memory phases, ~15 % of a 19x19
+    simulation) leaves the SMs idle; with two waves in flight one wave's tree step runs under the other wave's
+    network kernel (SURVEY section 7 hard part 4).  The games are independent and the RNG is keyed
+    by the global game id, so the moves do not depend on how the games are cut into waves or streams."""
+
+    def __init__(self, net, board_size, num_games, num_simulations, waves=1, search=None, streams=1, **kw):
         if num_games % waves:
             raise ValueError("num_games must be a multiple of waves")
+        streams = max(1, min(int(streams), waves))
+        if waves % streams:
+            raise ValueError("waves must be a multiple of streams")
         per = num_games // waves
         self.engines = []
         for w in range(waves):
             # one RNG key space for the whole group: wave w owns the global game ids [base + w*per, base + (w+1)*per)
             base_cfg = search if search is not None else SearchConfig()
             cfg = dataclasses.replace(base_cfg, game_base=base_cfg.game_base + w * per)
+            owner = self.engines[w % streams] if w >= streams else None      # the first wave of this wave's stream
             self.engines.append(SelfPlayEngine(net, board_size, per, num_simulations, search=cfg,
-                                               share_search_buffers_with=self.engines[0] if w else None, **kw))
+                                               share_search_buffers_with=owner, ws_key=w % streams, **kw))
         e0 = self.engines[0]
         self.G, self.S, self.A, self.n, self.M = num_games, e0.S, e0.A, e0.n, e0.M
         self.arena, self.tree, self.device = e0.arena, e0.tree, e0.device
+        self.streams = [torch.cuda.Stream(device=self.device) for _ in range(streams)] if streams > 1 else []
+
+    def memory_bytes(self):
+        return sum(e.memory_bytes() for e in self.engines[:max(1, len(self.streams))])
 
     def run(self, num_moves, traj_offset=0):
-        for m in range(int(num_moves)):
-            for e in self.engines:
-                e.run(1, traj_offset=traj_offset + m)
+        if not self.streams:
+            for m in range(int(num_moves)):
+                for e in self.engines:
+                    e.run(1, traj_offset=traj_offset + m)
+            return
+        # fork: every side stream starts behind the caller's stream; join: the caller's stream continues behind all
+        main = torch.cuda.current_stream(self.device)
+        start = torch.cuda.Event()
+        start.record(main)
+        ns = len(self.streams)
+        for k, st in enumerate(self.streams):
+            st.wait_event(start)
+            with torch.cuda.stream(st):
+                for m in range(int(num_moves)):
+                    for e in self.engines[k::ns]:
+                        e.run(1, traj_offset=traj_offset + m)
+            main.wait_stream(st)
 
     def read_counters(self):
         tot = dict.fromkeys(COUNTER_NAMES, 0)

@@ -198,6 +198,16 @@ def test_games_are_invariant_to_sharding_and_waves():
     assert torch.equal(rows["action"], whole.traj_action)
     assert torch.equal(rows["policy"], whole.traj_policy)
     assert torch.equal(rows["boards"], whole.traj_boards)
+    # the same waves spread over two CUDA streams (two sets of search buffers, two network workspaces), whose kernels
+    # overlap: still the same games, move for move, and the same trajectory rows
+    both = mz.WaveGroup(net, n, G, S, waves=4, streams=2, search=cfg, traj_capacity=T)
+    both.run(T)
+    torch.cuda.synchronize()
+    rows2 = both.trajectory_rows(0, T)
+    assert both.engines[2].arena.data_ptr() == both.engines[0].arena.data_ptr() != both.engines[1].arena.data_ptr()
+    assert both.read_counters()["moves"] == G * T
+    for k in ("action", "policy", "boards", "root_value", "reward", "done", "winner"):
+        assert torch.equal(rows2[k], rows[k]), k
     for r in range(2):                               # two "ranks" of 6 games each
         shard = mz.SelfPlayEngine(net, n, G // 2, S, search=dataclasses.replace(cfg, game_base=r * (G // 2)), traj_capacity=T)
         shard.run(T)
