@@ -110,7 +110,9 @@ def load():
     if _lib is not None:
         return _lib
     path = so_path()
-    if not os.path.exists(path) or (os.path.isdir(os.path.join(_HERE, "csrc")) and not _build.up_to_date()):
+    # MZGO_KEEP_SO=1: use the library as built (the checked build of `python -m muzero_go_b200.build --checked`)
+    stale = os.path.isdir(os.path.join(_HERE, "csrc")) and not _build.up_to_date() and not os.environ.get("MZGO_KEEP_SO")
+    if not os.path.exists(path) or stale:
         try:
             _build.build()
         except Exception as e:  # no nvcc on the box: use the shipped .so if there is one

@@ -33,6 +33,9 @@ def _digest():
     return h.hexdigest()
 
 
+CHECKED_FLAG = "-DMZGO_CHECKED"     # device-side bounds assertions (csrc/common.cuh, MZGO_DCHECK)
+
+
 def up_to_date():
     """Content hash of the sources (not mtimes: the tree is copied to the GPU box by gpurun)."""
     if not (os.path.exists(SO) and os.path.exists(SO + ".hash")):
@@ -41,8 +44,10 @@ def up_to_date():
         return fh.read().strip() == _digest()
 
 
-def build(force=False, verbose=False):
-    if not force and up_to_date():
+def build(force=False, verbose=False, checked=False):
+    """checked=True: the same library with MZGO_DCHECK assertions compiled in (always rebuilt, and the recorded hash is
+    left stale on purpose so that the next plain build() rebuilds the normal library)."""
+    if not force and not checked and up_to_date():
         return SO
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
     objdir = os.path.join(HERE, "build")
@@ -52,16 +57,16 @@ def build(force=False, verbose=False):
     for src in sources():
         obj = os.path.join(objdir, os.path.basename(src)[:-3] + ".o")
         objs.append(obj)
-        cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", src, "-o", obj]
+        cmd = [nvcc] + NVCC_FLAGS + ([CHECKED_FLAG] if checked else []) + (["-Xptxas", "-v"] if verbose else []) + ["-c", src, "-o", obj]
         procs.append((cmd, subprocess.Popen(cmd)))
     for cmd, p in procs:
         if p.wait() != 0:
             raise RuntimeError("nvcc failed: " + " ".join(cmd))
     subprocess.check_call([nvcc, "-shared", "-o", SO] + objs)
     with open(SO + ".hash", "w") as fh:
-        fh.write(_digest())
+        fh.write(_digest() + ("-checked" if checked else ""))
     return SO
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv, checked="--checked" in sys.argv))

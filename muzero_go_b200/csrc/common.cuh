@@ -34,6 +34,17 @@ void mzgo_set_error(const char* fmt, ...);
 
 static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 
+// ---- checked build (python -m muzero_go_b200.build --checked): device-side bounds assertions on every node / edge /
+// slot / item index the kernels compute.  compute-sanitizer is closed on this GPU pool (profiles/r02/NOTES.md); the
+// whole GPU test suite run against this build (a failed assertion prints file:line and traps the kernel) is the
+// substitute.  No code in the normal build.
+#ifdef MZGO_CHECKED
+#include <assert.h>
+#define MZGO_DCHECK(cond) assert(cond)
+#else
+#define MZGO_DCHECK(cond) ((void)0)
+#endif
+
 // ---- programmatic dependent launch (PDL) ----
 // The kernels of the search loop (tree step, network) run back to back, each consuming what the one before wrote.
 // Launched with the programmatic-serialisation attribute, the next kernel's blocks are scheduled as soon as every

@@ -309,6 +309,7 @@ __device__ __forceinline__ TcItems tc_load_items(const TcArgs& a, const TcRange&
     const int side = lane >> 3, idx = lane & 7;
     const int item = (side ? rg.plo : rg.lo) + gi * a.images_per_group + idx;
     if (side < 2 && idx < a.images_per_group && gi < rg.ngroups && item < (side ? rg.phi : rg.hi)) {
+        MZGO_DCHECK(item >= 0 && item < a.B);
         r.act = a.action ? __ldg(a.action + item) : 0;
         r.isl = a.in_slot ? __ldg(a.in_slot + item) : item;
         r.osl = a.out_slot ? __ldg(a.out_slot + item) : item;
@@ -417,6 +418,7 @@ __device__ __forceinline__ void tc_epilogue_role(const TcArgs& a, const TcCtx& c
             const bool store_ok = q < ps;
             const float* tb = (MODE == MODE_DYN) ? s_tbl + (img * 9 + cls) * COUT : s_tbl;
             const int oslot = __shfl_sync(FULL_MASK, my_osl, img);
+            MZGO_DCHECK(oslot >= 0 && img < tc_group_cnt(a, rg.lo, rg.hi, gi) && slot < TC_SLOTS);
             uint4* dst = reinterpret_cast<uint4*>(a.out) + (size_t)oslot * KC_OUT * ps + q;
             float pol = 0.f, val = 0.f, rew = 0.f;
             const uint32_t keep = valid ? 0xffffffffu : 0u;

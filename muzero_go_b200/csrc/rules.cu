@@ -151,6 +151,7 @@ __device__ int board_move(Board& b, int r, int c, int n, int lane) {
         if (b.pass) b.done = 1;
         b.pass = 1;
     } else {
+        MZGO_DCHECK(r >= 0 && r < n && c >= 0 && c < n && n <= MZGO_MAX_N);
         const uint32_t stone = (lane == r) ? (1u << c) : 0u;
         if (__any_sync(FULL_MASK, (b.inv & stone) != 0u)) return -1;
         b.pass = 0;

@@ -261,7 +261,9 @@ k_tree_select(mzgo_tree_t t, mzgo_search_params_t p, const uint32_t* __restrict_
             if (take) { best = ob; best_a = oa; best_n = on; }
         }
         if (best_a < 0) break;   // only NaN / -inf scores: the reference falls out of the loop too
+        MZGO_DCHECK(best_a < A);
         node = (int)t.child[base + best_a];
+        MZGO_DCHECK(node < t.n_nodes[g]);
         npar = best_n;
         depth++;
     }
@@ -271,7 +273,9 @@ k_tree_select(mzgo_tree_t t, mzgo_search_params_t p, const uint32_t* __restrict_
             // terminal leaf: backpropagate(path, 0) -- a visit for every node on the path (self_play.py:188-190)
             int nd = node;
             while (nd != 0) {
+                MZGO_DCHECK(nd > 0 && nd < M);
                 const int pk = t.parent[(size_t)g * M + nd];
+                MZGO_DCHECK(pk >= 0 && (pk >> 9) < M && (pk & 511) < A);
                 t.edge_visit[((size_t)g * M + (pk >> 9)) * A + (pk & 511)] += 1;
                 nd = pk >> 9;
             }
@@ -301,6 +305,7 @@ k_tree_expand_backup(mzgo_tree_t t, mzgo_search_params_t p, const float* __restr
     const int A = t.A, M = t.M;
     const int par = t.leaf_parent[g];
     const int nw = t.leaf_node[g];
+    MZGO_DCHECK(act < A && par >= 0 && par < nw && nw < M && nw == t.n_nodes[g]);
     const size_t nbase = ((size_t)g * M + nw) * A;
     const float* mask = t.root_mask + (size_t)g * A;
     const bool v1 = p.variant == MZGO_VARIANT_SELFPLAY;
@@ -332,8 +337,10 @@ k_tree_expand_backup(mzgo_tree_t t, mzgo_search_params_t p, const float* __restr
         double sv = bv;                                      // self_play.py:340-343: +value at the new leaf, then alternating
         int node = nw;
         while (node != 0) {
+            MZGO_DCHECK(node > 0 && node < M);
             int pk = t.parent[(size_t)g * M + node];
             int pn = pk >> 9, pa = pk & 511;
+            MZGO_DCHECK(pk >= 0 && pn < M && pa < A);
             size_t e = ((size_t)g * M + pn) * A + pa;
             t.edge_visit[e] += 1;
             t.edge_vsum[e] = __dadd_rn(t.edge_vsum[e], sv);

@@ -168,6 +168,9 @@ __device__ __forceinline__ void tree_step_body(const mzgo_tree_t& t, const mzgo_
     const int root_visit0 = t.root_visit[g];
     const uint32_t ctr0 = t.choice_ctr[g];
     const int nn0 = t.n_nodes[g];
+    MZGO_DCHECK(g >= 0 && g < t.G && A <= STEP_EPT * TPG && nn0 >= 0 && nn0 <= M);
+    MZGO_DCHECK(act < A && (act < 0 || (par >= 0 && par < nn0 && nw == nn0 && nw < M && depth_b >= 1)));
+    MZGO_DCHECK(!(act >= 0 && depth_b <= A && tid < depth_b) || ((pk_raw >> 9) < nn0 && (pk_raw & 511) < A && pk_raw >= 0));
     const float* mask = t.root_mask + (size_t)g * A;
     float mk[STEP_EPT], sf[STEP_EPT];
     int nv_r[STEP_EPT], ch_r[STEP_EPT];
@@ -250,6 +253,7 @@ __device__ __forceinline__ void tree_step_body(const mzgo_tree_t& t, const mzgo_
             }
             for (int d = tid + TPG; d < depth; d += TPG) {
                 const int pk = path[d];
+                MZGO_DCHECK(pk >= 0 && (pk >> 9) < M && (pk & 511) < A);
                 const size_t e = ((size_t)g * M + (pk >> 9)) * A + (pk & 511);
                 t.edge_visit[e] += 1;
                 t.edge_vsum[e] = __dadd_rn(t.edge_vsum[e], (v1 && ((depth - 1 - d) & 1)) ? -bv : bv);
@@ -263,8 +267,10 @@ __device__ __forceinline__ void tree_step_body(const mzgo_tree_t& t, const mzgo_
                 int node = nw;
                 double sv = bv;
                 while (node != 0) {
+                    MZGO_DCHECK(node > 0 && node < M);
                     const int pk = t.parent[(size_t)g * M + node];
                     const int pn = pk >> 9, pa = pk & 511;
+                    MZGO_DCHECK(pk >= 0 && pn < M && pa < A);
                     const size_t e = ((size_t)g * M + pn) * A + pa;
                     t.edge_visit[e] += 1;
                     t.edge_vsum[e] = __dadd_rn(t.edge_vsum[e], sv);
@@ -316,6 +322,7 @@ __device__ __forceinline__ void tree_step_body(const mzgo_tree_t& t, const mzgo_
                                        (uint32_t)(g + p.game_base), move_index, &oa, &on, &oc);
         if (rc == 0) { sel_parent = node; sel_action = oa; break; }
         if (rc == 2 || oc <= 0) break;           // terminal leaf / dropped simulation (node keeps the leaf)
+        MZGO_DCHECK(oa >= 0 && oa < A && oc < M && oc < (act >= 0 ? nw + 1 : nn0));
         if (tid == 0 && depth <= A) path[depth - 1] = node * 512 + oa;
         node = oc; npar = on; depth++;
         step_sync<TPG, BAR>();                        // shared scratch is reused by the next level
@@ -346,7 +353,9 @@ __device__ __forceinline__ void tree_step_body(const mzgo_tree_t& t, const mzgo_
             // terminal leaf: backpropagate(path, 0) -- a visit for every node on the path (self_play.py:188-190)
             int nd = node;
             while (nd != 0) {
+                MZGO_DCHECK(nd > 0 && nd < M);
                 const int pk = t.parent[(size_t)g * M + nd];
+                MZGO_DCHECK(pk >= 0 && (pk >> 9) < M && (pk & 511) < A);
                 t.edge_visit[((size_t)g * M + (pk >> 9)) * A + (pk & 511)] += 1;
                 nd = pk >> 9;
             }
@@ -354,6 +363,7 @@ __device__ __forceinline__ void tree_step_body(const mzgo_tree_t& t, const mzgo_
         }
         if (sel_action >= 0) t.choice_ctr[g] = ctr0 + 1u;
         if (sel_action >= 0 && nn >= M) sel_action = -1;   // arena full: drop (cannot happen when M > simulations)
+        MZGO_DCHECK(sel_action < A && (sel_action < 0 || (sel_parent >= 0 && sel_parent < nn && nn < M)));
         if (sel_action >= 0 && depth <= A) path[depth - 1] = sel_parent * 512 + sel_action;
         t.leaf_parent[g] = sel_action >= 0 ? sel_parent : -1;
         t.leaf_action[g] = sel_action;
