@@ -182,11 +182,12 @@ def run_reference(args, wl):
 
 
 # ------------------------------------------------------------------------------------------------ GPU arm
-def config_dict(wl, games, sims, precision):
+def config_dict(wl, games, sims, precision, positions="mixed"):
     """The same dict in both arms (the CPU arm runs this workload's per-game loop on the host cores)."""
     return {"workload": wl["name"], "board": wl["n"], "games_per_gpu": games, "sims_per_move": sims, "latent_dim": LATENT,
             "weights": "random-init (torch.manual_seed(0))", "precision": precision,
-            "positions": "every game advanced a random 0-60 % of the move cap by random legal moves before the warm-up",
+            "positions": ("every game advanced a random 0-60 % of the move cap by random legal moves before the warm-up"
+                          if positions == "mixed" else "every game starts from the empty board (openings only)"),
             "cache": "inputs larger than L2 (the latent arena is > 1 GB per GPU and every simulation reads and writes fresh slots)",
             "parallelism": "games sharded over the GPUs, no collective inside the search"}
 
@@ -242,8 +243,8 @@ class TrajectoryExchange:
         self.filled = 0
         self.bytes_gathered = 0
 
-    def push(self, rows_per_engine):
-        self.ring.write(self.filled, rows_per_engine)
+    def push(self, group, row):
+        self.ring.write_from(self.filled, group, row)
         self.filled += 1
         if self.filled == self.depth:
             self.flush()
@@ -262,7 +263,7 @@ class TrajectoryExchange:
         self.filled = 0
 
 
-def measure(args, wl, G, S, K, W, rank, world, dev, primary):
+def measure(args, wl, G, S, K, W, rank, world, dev, primary, positions="mixed"):
     """One workload on this rank: whole-step throughput (device timed), end to end with host buffers, and -- for the
     primary workload -- the three kernel families timed alone."""
     import torch
@@ -293,7 +294,8 @@ def measure(args, wl, G, S, K, W, rank, world, dev, primary):
     eng = group.engines[0]          # the single-kernel timings below run on one wave's buffers
     GW = G // waves
     lib = _lib.load()
-    advance_games(mz, torch, group, n, seed=77 + rank)
+    if positions == "mixed":
+        advance_games(mz, torch, group, n, seed=77 + rank)
     exch_depth = max(1, min(64, (1 << 20) // max(1, G * mzdist.row_stride(A)) + 1))
     exch = TrajectoryExchange(torch, dist, mzdist, group, A, world, exch_depth)
 
@@ -304,7 +306,7 @@ def measure(args, wl, G, S, K, W, rank, world, dev, primary):
 
     def step(row=0):
         group.run(1, traj_offset=row)
-        exch.push([e.trajectory_rows(row, row + 1) for e in group.engines])
+        exch.push(group, row)
 
     sampler = ClockSampler(local) if primary else None
     if sampler:
@@ -372,7 +374,7 @@ def measure(args, wl, G, S, K, W, rank, world, dev, primary):
     def e2e_step():
         boards_up()
         step()
-        row_ring.write(0, [e.trajectory_rows(0, 1) for e in group.engines])
+        row_ring.write_from(0, group, 0)
         host_row.copy_(row_ring.buf, non_blocking=True)
         boards_down(non_blocking=True)                       # next step's input comes from the host again
         torch.cuda.synchronize()                             # both read-backs have landed in pinned memory
@@ -568,7 +570,11 @@ def run_ours(args, wl):
         torch.cuda.empty_cache()
         wl9 = WORKLOADS["9x9"]
         r9 = measure(args, wl9, wl9["games"], wl9["sims"], max(K, 250), max(W, 5), rank, world, dev, primary=False)
-        second = (wl9, r9)
+        # ... and from empty boards, the state round 1 measured (with 82 root edges and 50 simulations the search of an
+        # opening never leaves the root's children; the mixed figure above is the steady state of a long job)
+        r9o = measure(args, wl9, wl9["games"], wl9["sims"], max(K, 250), max(W, 5), rank, world, dev, primary=False,
+                      positions="openings")
+        second = (wl9, r9, r9o)
 
     def reduce(res):
         t = torch.tensor([res["ms"], res["e2e_ms"]], dtype=torch.float64, device=dev)
@@ -580,6 +586,7 @@ def run_ours(args, wl):
 
     (ms, e2e_ms), (sims_all, moves_all, e2e_sims_all, launches_all, G_all) = reduce(r)
     red9 = reduce(second[1]) if second else None
+    red9o = reduce(second[2]) if second else None
     if rank == 0:
         n = wl["n"]
         peaks = measured_peaks()
@@ -612,15 +619,20 @@ def run_ours(args, wl):
                 "roofline_tree": r["roofline_tree"], "roofline_rules": r["roofline_rules"],
                 "cpu_baseline": cpu, "clocks": r["clocks"], "weight_broadcast_bytes": r["bytes_bcast"]}
         if second:
-            wl9, r9 = second
+            wl9, r9, r9o = second
             (ms9, e2e9), (s9, m9, es9, _, _) = red9
+            (ms9o, e2e9o), (s9o, m9o, es9o, _, _) = red9o
             line["secondary"] = {"config": config_dict(wl9, wl9["games"], wl9["sims"], args.precision),
                                  "value": s9 / (ms9 * 1e-3), "unit": "sims/s", "moves_per_sec": m9 / (ms9 * 1e-3),
                                  "steps": max(K, 250), "ms_per_step": ms9 / max(K, 250), "mean_leaf_depth": r9["depth"],
                                  "e2e": {"value": es9 / (e2e9 * 1e-3), "unit": "sims/s", "h2d_bytes_per_step": r9["h2d"],
                                          "d2h_bytes_per_step": r9["d2h"]},
                                  "roofline": r9["roofline"],
-                                 "frac_step": s9 / (ms9 * 1e-3) / world * flops_recurrent(9) / 1e12 / peaks["bf16_sustained"]}
+                                 "frac_step": s9 / (ms9 * 1e-3) / world * flops_recurrent(9) / 1e12 / peaks["bf16_sustained"],
+                                 "openings": {"positions": "every game starts from the empty board (round 1's measurement)",
+                                              "value": s9o / (ms9o * 1e-3), "unit": "sims/s", "ms_per_step": ms9o / max(K, 250),
+                                              "mean_leaf_depth": r9o["depth"],
+                                              "e2e": {"value": es9o / (e2e9o * 1e-3), "unit": "sims/s"}}}
         emit(line)
     if world > 1:
         dist.destroy_process_group()

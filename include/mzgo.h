@@ -316,6 +316,14 @@ typedef struct mzgo_selfplay {
 int mzgo_selfplay_run(const mzgo_selfplay_t* sp, int num_moves, int traj_offset,
                       uint32_t first_move_index, void* stream);
 
+/* Trajectory rows [t0, t0 + nrows) of this engine in the wire layout of the trajectory gather (north_star (4): "a
+ * trajectory gather to the replay buffer"; SURVEY 8e: fixed-stride records): per (row, game) the bytes
+ *   board record 256 | action int32 | policy A x float32 | root value float32 | reward float32 | done uint8 | winner int8
+ * (stride 270 + 4A), written to out[r][g_offset + g], out = [nrows][G_total][stride] bytes (device, 2-byte aligned).
+ * The waves of a WaveGroup pack into one buffer with their game offsets; the buffer is what is all-gathered. */
+int mzgo_selfplay_pack_rows(const mzgo_selfplay_t* sp, int t0, int nrows, void* out /*device*/, int g_offset, int G_total,
+                            void* stream);
+
 /* One search only (the body of MCTS.run after the root is prepared): `num_simulations` rounds of
  * select -> recurrent inference -> expand/backup on sp->tree.  choice_stream as in mzgo_tree_select. */
 int mzgo_search_run(const mzgo_selfplay_t* sp, const uint32_t* choice_stream, int stride, void* stream);

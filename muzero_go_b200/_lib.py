@@ -95,6 +95,7 @@ _PROTOS = {
     "mzgo_net_import_latent": (i32, [C.POINTER(NetDesc), vp, vp, vp, i32, vp]),
     "mzgo_selfplay_run": (i32, [C.POINTER(SelfPlayDesc), i32, i32, u32, vp]),
     "mzgo_search_run": (i32, [C.POINTER(SelfPlayDesc), vp, i32, vp]),
+    "mzgo_selfplay_pack_rows": (i32, [C.POINTER(SelfPlayDesc), i32, i32, vp, i32, i32, vp]),
 }
 
 _lib = None

@@ -96,6 +96,34 @@ __global__ void k_sp_end_move(mzgo_selfplay_t sp, int t) {
     }
 }
 
+// Trajectory rows in the wire layout of the replay exchange (muzero_go_b200/dist.py, ROW_FIELDS): per (move, game)
+// a fixed-stride record {board 256 B, action i32, policy A x f32, root value f32, reward f32, done u8, winner i8}.
+// One warp per (row, game); out = [nrows][G_total][stride] bytes, this engine's games at [g_offset, g_offset + G).
+__global__ void k_sp_pack_rows(mzgo_selfplay_t sp, int t0, int nrows, uint8_t* out, int g_offset, int G_total) {
+    const int G = sp.tree.G, A = sp.tree.A;
+    const int w = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (w >= nrows * G) return;
+    const int r = w / G, g = w - r * G;
+    const size_t row = (size_t)(t0 + r) * G + g;
+    const size_t stride = 256 + 4 + 4 * (size_t)A + 4 + 4 + 1 + 1;
+    uint8_t* dst = out + ((size_t)r * G_total + g_offset + g) * stride;
+    // the stride is even but not a multiple of 4 in general: 16-bit stores keep every field at its byte offset
+    uint16_t* d16 = reinterpret_cast<uint16_t*>(dst);
+    const uint16_t* board = reinterpret_cast<const uint16_t*>(sp.traj_boards + row * MZGO_BOARD_WORDS);
+    for (int i = lane; i < 128; i += 32) d16[i] = board[i];
+    const uint16_t* pol = reinterpret_cast<const uint16_t*>(sp.traj_policy + row * A);
+    for (int i = lane; i < 2 * A; i += 32) d16[130 + i] = pol[i];
+    if (lane == 0) {
+        const uint32_t act = (uint32_t)sp.traj_action[row];
+        d16[128] = (uint16_t)act; d16[129] = (uint16_t)(act >> 16);
+        const uint32_t rv = __float_as_uint(sp.traj_root_value[row]), rw = __float_as_uint(sp.traj_reward[row]);
+        uint16_t* tail = d16 + 130 + 2 * A;
+        tail[0] = (uint16_t)rv; tail[1] = (uint16_t)(rv >> 16);
+        tail[2] = (uint16_t)rw; tail[3] = (uint16_t)(rw >> 16);
+        tail[4] = (uint16_t)sp.traj_done[row] | (uint16_t)((uint16_t)(uint8_t)sp.traj_winner[row] << 8);
+    }
+}
+
 int check_sp(const mzgo_selfplay_t* sp) {
     MZGO_CHECK_ARG(sp != nullptr, "selfplay is NULL");
     MZGO_CHECK_ARG(sp->n * sp->n + 1 == sp->tree.A && sp->net.n == sp->n, "board size mismatch");
@@ -209,6 +237,23 @@ static int search_run_cached(const mzgo_selfplay_t* sp, cudaStream_t st) {
 
 // Searches served by a replayed graph so far (bench.py reports it next to gpu_launches).
 extern "C" long long mzgo_graph_replays(void) { return g_graph_replays; }
+
+extern "C" int mzgo_selfplay_pack_rows(const mzgo_selfplay_t* sp, int t0, int nrows, void* out, int g_offset, int G_total,
+                                       void* stream) {
+    if (int e = check_sp(sp)) return e;
+    MZGO_CHECK_ARG(out != nullptr && nrows >= 0 && t0 >= 0 && t0 + nrows <= sp->traj_capacity, "rows [%d,%d) outside capacity %d",
+                   t0, t0 + nrows, sp->traj_capacity);
+    MZGO_CHECK_ARG(g_offset >= 0 && g_offset + sp->tree.G <= G_total, "games [%d,%d) outside the %d games of the buffer", g_offset,
+                   g_offset + sp->tree.G, G_total);
+    MZGO_CHECK_ARG(((uintptr_t)out & 1) == 0, "row buffer must be 2-byte aligned");
+    const int warps = nrows * sp->tree.G;
+    if (warps == 0) return MZGO_OK;
+    k_sp_pack_rows<<<ceil_div(warps, SP_THREADS / 32), SP_THREADS, 0, (cudaStream_t)stream>>>(*sp, t0, nrows, (uint8_t*)out, g_offset,
+                                                                                              G_total);
+    mzgo_count_launch();
+    MZGO_LAUNCH_CHECK();
+    return MZGO_OK;
+}
 
 extern "C" int mzgo_selfplay_run(const mzgo_selfplay_t* sp_in, int num_moves, int traj_offset,
                                  uint32_t first_move_index, void* stream) {

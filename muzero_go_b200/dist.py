@@ -74,6 +74,11 @@ class RowRing:
             g0 += gw
         assert g0 == self.G
 
+    def write_from(self, t, group, row):
+        """Row `row` of a SelfPlayEngine / WaveGroup into ring slot t with the engine's own packing kernel
+        (mzgo_selfplay_pack_rows): one launch per wave instead of seven slice copies."""
+        group.pack_rows(row, row + 1, self.buf[t:t + 1])
+
     def rows(self, lo=0, hi=None):
         """The ring's rows [lo, hi) as a dict of tensors (unpack_rows)."""
         return unpack_rows(self.buf[lo:self.depth if hi is None else hi], self.A)

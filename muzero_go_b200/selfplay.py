@@ -107,6 +107,16 @@ class SelfPlayEngine:
                                                  _lib.stream_ptr()))
         self.moves_enqueued += int(num_moves)
 
+    def pack_rows(self, lo, hi, out, g_offset=0):
+        """Trajectory rows [lo,hi) in the wire layout of the trajectory gather (dist.ROW_FIELDS) into
+        out[0:hi-lo, g_offset:g_offset+G, :], a uint8 [rows, G_total, stride] device tensor: ONE launch
+        (mzgo_selfplay_pack_rows), no torch.cat."""
+        assert out.dtype == torch.uint8 and out.is_contiguous() and out.dim() == 3 and out.shape[0] >= hi - lo
+        assert out.shape[2] == 270 + 4 * self.A
+        d = self._desc if self._desc is not None else self.descriptor()
+        _lib.check(_lib.load().mzgo_selfplay_pack_rows(d, int(lo), int(hi - lo), _lib.ptr(out), int(g_offset),
+                                                       int(out.shape[1]), _lib.stream_ptr()))
+
     def read_counters(self):
         """Synchronises.  -> dict of totals since construction."""
         return dict(zip(COUNTER_NAMES, self.counters.cpu().tolist()))
@@ -184,3 +194,10 @@ class WaveGroup:
     def trajectory_rows(self, lo, hi):
         rows = [e.trajectory_rows(lo, hi) for e in self.engines]
         return {k: torch.cat([r[k] for r in rows], dim=1) for k in rows[0]}
+
+    def pack_rows(self, lo, hi, out):
+        """All waves' rows [lo,hi) into out (uint8 [rows, num_games, stride], wire layout): one launch per wave."""
+        g0 = 0
+        for e in self.engines:
+            e.pack_rows(lo, hi, out, g_offset=g0)
+            g0 += e.G

@@ -208,6 +208,15 @@ def test_games_are_invariant_to_sharding_and_waves():
     assert both.read_counters()["moves"] == G * T
     for k in ("action", "policy", "boards", "root_value", "reward", "done", "winner"):
         assert torch.equal(rows2[k], rows[k]), k
+    # the engines' own row packing (mzgo_selfplay_pack_rows, one launch per wave) writes the wire layout of the
+    # trajectory gather byte for byte
+    from muzero_go_b200 import dist as mzdist
+    wire = torch.zeros((T, G, mzdist.row_stride(n * n + 1)), dtype=torch.uint8, device="cuda")
+    both.pack_rows(0, T, wire)
+    assert torch.equal(wire, mzdist.pack_rows(rows2))
+    ring = mzdist.RowRing(G, n * n + 1, 2, "cuda")
+    ring.write_from(1, both, 3)
+    assert torch.equal(ring.buf[1], wire[3]) and torch.equal(ring.rows(1, 2)["policy"][0], rows2["policy"][3])
     for r in range(2):                               # two "ranks" of 6 games each
         shard = mz.SelfPlayEngine(net, n, G // 2, S, search=dataclasses.replace(cfg, game_base=r * (G // 2)), traj_capacity=T)
         shard.run(T)
