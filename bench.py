@@ -724,7 +724,9 @@ def run_train(args):
                   "note": "train_on_device: sampling, batch assembly (gathers + rules-kernel planes), bootstrap forward and step "
                           "on the GPU, loss read back every step",
                   "host_assembly": B * args.steps / e2e_s},
-          "roofline": {"bound": "tensor", "kernel": "torch autograd forward + backward (cuDNN fp32/tf32 convolutions; library kernels)",
+          "roofline": {"bound": "tensor", "kernel": "csrc/train.cu: the 3x3 convolutions forward + data gradient + weight gradient in hand-written "
+                                                    "float32 CUDA-core kernels (the trainer's parity contract is float32, 1e-5), against the bf16 "
+                                                    "tensor peak for scale only",
                        "achieved": flops / (ms * 1e-3) / 1e12, "peak": peaks["bf16_sustained"], "unit": "TFLOP/s",
                        "frac": flops / (ms * 1e-3) / 1e12 / peaks["bf16_sustained"], "traffic": None},
           "cpu_baseline": cpu})

@@ -328,6 +328,30 @@ int mzgo_selfplay_pack_rows(const mzgo_selfplay_t* sp, int t0, int nrows, void* 
  * select -> recurrent inference -> expand/backup on sp->tree.  choice_stream as in mzgo_tree_select. */
 int mzgo_search_run(const mzgo_selfplay_t* sp, const uint32_t* choice_stream, int stride, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * 5. Training-side 3x3 convolutions (MuZeroAgent.train, main.py:381-501, whose forward and
+ *    backward run on nn.Conv2d / autograd in the reference -- main.py:75-77, :90).  Dense float32 NCHW batches,
+ *    padding 1; forward, data gradient and weight gradient; ReLU's backward mask is folded into the gradient
+ *    kernels' operand loads (y_gate = the layer's own output; NULL = no ReLU).  float32 on the CUDA cores: the
+ *    trainer's parity contract is 1e-5 against the real MuZeroAgent.train.  All launches asynchronous on `stream`,
+ *    CUDA-graph capturable.
+ * ------------------------------------------------------------------------------------------ */
+/* w [Cout][Cin][3][3] -> wT_fwd [Cin][9][Cout] (forward operand) and / or wT_bwd [Cout][9][Cin], taps flipped (data
+ * gradient operand); either may be NULL. */
+int mzgo_train_conv3x3_prep_w(const float* w /*device*/, float* wT_fwd /*device*/, float* wT_bwd /*device*/, int Cin,
+                              int Cout, void* stream);
+/* y [B][Cout][n][n] = conv3x3(x [B][Cin][n][n]) + bias (optional), then ReLU when relu != 0.  Cout % 8 == 0. */
+int mzgo_train_conv3x3_fwd(const float* x, const float* wT_fwd, const float* bias, float* y, int relu, int B, int Cin,
+                           int Cout, int n, void* stream);
+/* dx [B][Cin][n][n] = data gradient of the layer for dy [B][Cout][n][n] (masked by y_gate > 0 when given).  Cin % 8 == 0. */
+int mzgo_train_conv3x3_bwd_data(const float* dy, const float* y_gate, const float* wT_bwd, float* dx, int B, int Cin,
+                                int Cout, int n, void* stream);
+/* dw [Cout][Cin][3][3], db [Cout] (optional) = weight / bias gradient; scratch: mzgo_train_wgrad_scratch_floats floats.
+ * Deterministic (two passes, no atomics). */
+int64_t mzgo_train_wgrad_scratch_floats(int B, int Cin, int Cout);
+int mzgo_train_conv3x3_bwd_weight(const float* x, const float* dy, const float* y_gate, float* dw, float* db,
+                                  float* scratch, int B, int Cin, int Cout, int n, void* stream);
+
 /* Test / profiling hooks.  mzgo_debug_fastdiv_check: operand pairs on which the tree kernels' 5-operation
  * correctly rounded division differs from the generic IEEE division (must be 0; synchronous).
  * mzgo_debug_tc_trace: when buf != NULL every tensor-core conv launch stamps its role timeline into

@@ -95,6 +95,11 @@ _PROTOS = {
     "mzgo_net_import_latent": (i32, [C.POINTER(NetDesc), vp, vp, vp, i32, vp]),
     "mzgo_selfplay_run": (i32, [C.POINTER(SelfPlayDesc), i32, i32, u32, vp]),
     "mzgo_search_run": (i32, [C.POINTER(SelfPlayDesc), vp, i32, vp]),
+    "mzgo_train_conv3x3_prep_w": (i32, [vp, vp, vp, i32, i32, vp]),
+    "mzgo_train_conv3x3_fwd": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, i32, vp]),
+    "mzgo_train_conv3x3_bwd_data": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, vp]),
+    "mzgo_train_wgrad_scratch_floats": (i64, [i32, i32, i32]),
+    "mzgo_train_conv3x3_bwd_weight": (i32, [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, vp]),
     "mzgo_selfplay_pack_rows": (i32, [C.POINTER(SelfPlayDesc), i32, i32, vp, i32, i32, vp]),
 }
 

@@ -7,9 +7,11 @@ per-trajectory quantity (targets, the three losses, their weights) is the refere
 a step is the reference's step (tests/test_trainer.py pins the loss and the updated weights against the real
 `MuZeroAgent.train`, tests/golden/train_*.npz).
 
-Status: the differentiable forward and backward go through torch autograd on the parameter containers of
-`MuZeroNet` (cuDNN / cuBLAS on the GPU) -- library kernels.  The hand-written part of this repo is the self-play
-path; the trainer's own kernels (dgrad / wgrad on tcgen05) are the next step of this row, see DESIGN.md §7.
+Kernels: on a GPU the 3x3 convolutions of the representation and dynamics networks -- more than 99.9 % of a step's
+FLOPs -- run forward, data gradient and weight gradient in libmzgo.so's own float32 kernels (csrc/train.cu through
+muzero_go_b200/train_ops.py, one torch.autograd.Function per layer); torch's autograd keeps the bookkeeping around
+them (the 1x1 heads, the spatial means, the losses, clipping, Adam).  On CPU tensors (the host-logic parity tests)
+the same functions fall through to torch's own convolution.
 
   reward_value_transform      main.py:67-69
   n-step value target         main.py:503-522 (`compute_target_value`)
@@ -45,11 +47,19 @@ def reward_value_transform(x, epsilon=0.001):
 
 
 # ---- differentiable forward on the parameter containers of MuZeroNet (main.py:72-142) ---------------------------
+def conv3x3_relu(x, weight, bias):
+    """relu(conv2d(x, weight, bias, padding=1)): libmzgo.so's kernels on CUDA tensors, torch's on CPU tensors."""
+    if x.is_cuda:            # the product path: no library convolution, and a loud error rather than a silent one
+        from .train_ops import conv3x3_relu as native
+        return native(x, weight, bias)
+    return F.relu(F.conv2d(x, weight, bias, padding=1))
+
+
 def representation(net, obs):
     r = net.representation
-    x = F.relu(F.conv2d(obs, r.conv1.weight, r.conv1.bias, padding=1))
-    x = F.relu(F.conv2d(x, r.conv2.weight, r.conv2.bias, padding=1))
-    return F.relu(F.conv2d(x, r.conv3.weight, r.conv3.bias, padding=1))
+    x = conv3x3_relu(obs, r.conv1.weight, r.conv1.bias)
+    x = conv3x3_relu(x, r.conv2.weight, r.conv2.bias)
+    return conv3x3_relu(x, r.conv3.weight, r.conv3.bias)
 
 
 def prediction(net, latent):
@@ -64,7 +74,7 @@ def prediction(net, latent):
 def dynamics(net, latent, action):
     d = net.dynamics
     emb = F.embedding(action, d.action_embedding.weight)[:, :, None, None]
-    x = F.relu(F.conv2d(latent + emb, d.conv.weight, d.conv.bias, padding=1))
+    x = conv3x3_relu(latent + emb, d.conv.weight, d.conv.bias)
     r = F.conv2d(x, d.reward_conv.weight, d.reward_conv.bias).mean(dim=(2, 3))
     r = F.linear(F.relu(F.linear(r, d.fc_reward_hidden.weight, d.fc_reward_hidden.bias)), d.fc_reward_output.weight,
                  d.fc_reward_output.bias)

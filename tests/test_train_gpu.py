@@ -210,3 +210,54 @@ def test_second_batch_shape_keeps_earlier_graphs_valid():
         for p, q in zip(net_a.parameters(), net_b.parameters()):
             assert torch.allclose(p, q, rtol=0, atol=3e-6), step
     assert len(graphed._graphs) == 2
+
+
+@pytest.mark.parametrize("B,cin,cout,n", [(3, 6, 64, 6), (5, 64, 64, 9), (2, 64, 128, 19), (4, 128, 128, 6), (3, 16, 16, 5),
+                                          (20, 128, 128, 9), (1, 96, 96, 13)])
+def test_native_conv_kernels_match_float64_autograd(B, cin, cout, n):
+    """csrc/train.cu (forward, data gradient, weight / bias gradient with ReLU's mask folded in) through the C ABI
+    against torch autograd in float64: every output within 1e-5 of the tensor's scale (float32 accumulation order)."""
+    from muzero_go_b200.train_ops import conv3x3_relu
+    g = torch.Generator().manual_seed(B * 1000 + cin + n)
+    x = torch.randn(B, cin, n, n, generator=g)
+    w = torch.randn(cout, cin, 3, 3, generator=g) / (3.0 * cin ** 0.5)
+    b = torch.randn(cout, generator=g) * 0.1
+    dy = torch.randn(B, cout, n, n, generator=g)
+    need_dx = cin % 8 == 0            # the observation planes (6 channels) never need a gradient (main.py:397)
+    xr, wr, br = (t.double().requires_grad_(True) for t in (x, w, b))
+    yr = torch.relu(torch.nn.functional.conv2d(xr, wr, br, padding=1))
+    yr.backward(dy.double())
+    xg = x.cuda().requires_grad_(need_dx)
+    wg, bg = (t.cuda().requires_grad_(True) for t in (w, b))
+    y = conv3x3_relu(xg, wg, bg)
+    y.backward(dy.cuda())
+    checks = [(y, yr, "y"), (wg.grad, wr.grad, "dw"), (bg.grad, br.grad, "db")] + ([(xg.grad, xr.grad, "dx")] if need_dx else [])
+    for got, want, name in checks:
+        err = float((got.detach().cpu().double() - want.detach()).abs().max() / (want.detach().abs().max() + 1e-12))
+        assert err < 1e-5, (name, err)
+    assert float((y == 0).float().mean()) > 0.2          # the mask was exercised
+
+
+@pytest.mark.parametrize("name", ["N5_C16_mid", "N5_C16_tail", "N6_C32_head"])
+def test_reference_training_step_through_the_native_kernels(name):
+    """tests/golden/train_*.npz -- the REAL MuZeroAgent.train on a one-trajectory buffer -- with the network on the
+    GPU, where every 3x3 convolution runs forward and backward in csrc/train.cu: same loss (1e-5 relative) and same
+    weights after the clipped Adam step (2e-6 absolute), eager and as a replayed CUDA graph."""
+    import os
+    from muzero_go_b200.networks import MuZeroNet
+    from muzero_go_b200.trainer import BatchedTrainer, TrainConfig, build_batch
+    from tests.test_trainer import GOLDEN, load_case
+    z, n, c, traj, w0, w1 = load_case(os.path.join(GOLDEN, f"train_{name}.npz"))
+    A = n * n + 1
+    for graph in (False, True):
+        net = MuZeroNet(c, A)
+        net.load_state_dict(w0)
+        net = net.cuda()
+        tr = BatchedTrainer(net, A, TrainConfig(unroll_steps=int(z["unroll_steps"]), discount=float(z["discount"])),
+                            cuda_graph=graph)
+        batch = build_batch(net, [traj], [int(z["start_index"])], tr.cfg, A, torch.device("cuda"))
+        per_traj, _ = tr.train_step(batch)
+        assert abs(per_traj.item() - float(z["loss"])) <= 1e-5 * abs(float(z["loss"])), graph
+        sd = net.state_dict()
+        for k in w1:
+            assert torch.allclose(sd[k].cpu(), w1[k], rtol=0, atol=2e-6), (k, graph)
