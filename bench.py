@@ -570,8 +570,9 @@ def run_ours(args, wl):
         torch.cuda.empty_cache()
         wl9 = WORKLOADS["9x9"]
         r9 = measure(args, wl9, wl9["games"], wl9["sims"], max(K, 250), max(W, 5), rank, world, dev, primary=False)
-        # ... and from empty boards, the state round 1 measured (with 82 root edges and 50 simulations the search of an
-        # opening never leaves the root's children; the mixed figure above is the steady state of a long job)
+        # ... and started from empty boards and played on: over these hundreds of moves the games run through whole
+        # self-play games (cap 121 moves, restarted at once), i.e. the phases self-play itself produces with this
+        # random-init network (round 1 timed 20 moves from the empty board: openings only, 25 M sims/s)
         r9o = measure(args, wl9, wl9["games"], wl9["sims"], max(K, 250), max(W, 5), rank, world, dev, primary=False,
                       positions="openings")
         second = (wl9, r9, r9o)
@@ -629,7 +630,8 @@ def run_ours(args, wl):
                                          "d2h_bytes_per_step": r9["d2h"]},
                                  "roofline": r9["roofline"],
                                  "frac_step": s9 / (ms9 * 1e-3) / world * flops_recurrent(9) / 1e12 / peaks["bf16_sustained"],
-                                 "openings": {"positions": "every game starts from the empty board (round 1's measurement)",
+                                 "from_empty_boards": {"positions": "every game starts from the empty board and plays on through whole games "
+                                                                    "(self-play's own mix of phases)",
                                               "value": s9o / (ms9o * 1e-3), "unit": "sims/s", "ms_per_step": ms9o / max(K, 250),
                                               "mean_leaf_depth": r9o["depth"],
                                               "e2e": {"value": es9o / (e2e9o * 1e-3), "unit": "sims/s"}}}
