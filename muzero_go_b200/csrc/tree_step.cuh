@@ -157,6 +157,10 @@ __device__ __forceinline__ void tree_step_body(const mzgo_tree_t& t, const mzgo_
     const size_t rbase = (size_t)g * M * A;      // edges of the root
 
     // ---------------------------------------------------------------- round trip 1: every independent load
+    // (the network outputs of the leaf among them: both callers have them ready on entry -- the kernel before
+    // k_tree_step wrote them, the network kernel's tree phase starts behind a barrier -- and loading them
+    // unconditionally keeps them off the dependent chain leaf record -> outputs -> backup -> root selection)
+    wait_outputs();
     const int act = do_backup ? t.leaf_action[g] : -1;
     const int par = t.leaf_parent[g];
     const int nw = t.leaf_node[g];
@@ -168,19 +172,18 @@ __device__ __forceinline__ void tree_step_body(const mzgo_tree_t& t, const mzgo_
     const int root_visit0 = t.root_visit[g];
     const uint32_t ctr0 = t.choice_ctr[g];
     const int nn0 = t.n_nodes[g];
-    MZGO_DCHECK(g >= 0 && g < t.G && A <= STEP_EPT * TPG && nn0 >= 0 && nn0 <= M);
-    MZGO_DCHECK(act < A && (act < 0 || (par >= 0 && par < nn0 && nw == nn0 && nw < M && depth_b >= 1)));
-    MZGO_DCHECK(!(act >= 0 && depth_b <= A && tid < depth_b) || ((pk_raw >> 9) < nn0 && (pk_raw & 511) < A && pk_raw >= 0));
     const float* mask = t.root_mask + (size_t)g * A;
     float mk[STEP_EPT], sf[STEP_EPT];
     int nv_r[STEP_EPT], ch_r[STEP_EPT];
     double pr_r[STEP_EPT], vs_r[STEP_EPT];
+    const float rew_g = do_backup ? __ldcg(reward + g) : 0.f, val_g = do_backup ? __ldcg(value + g) : 0.f;
 #pragma unroll
     for (int e = 0; e < STEP_EPT; e++) {
         const int a = e * TPG + tid;
         mk[e] = 0.f; sf[e] = 0.f; nv_r[e] = 0; ch_r[e] = -1; pr_r[e] = 0.0; vs_r[e] = 0.0;
         if (a < A) {
             mk[e] = mask[a];
+            if (do_backup) sf[e] = __ldcg(soft + (size_t)g * A + a);
             if (do_select) {
                 nv_r[e] = t.edge_visit[rbase + a];
                 pr_r[e] = t.root_prior[(size_t)g * A + a];
@@ -189,8 +192,12 @@ __device__ __forceinline__ void tree_step_body(const mzgo_tree_t& t, const mzgo_
             }
         }
     }
+    MZGO_DCHECK(g >= 0 && g < t.G && A <= STEP_EPT * TPG && nn0 >= 0 && nn0 <= M);
+    MZGO_DCHECK(act < A && (act < 0 || (par >= 0 && par < nn0 && nw == nn0 && nw < M && depth_b >= 1)));
+    MZGO_DCHECK(!(act >= 0 && depth_b <= A && tid < depth_b) || ((pk_raw >> 9) < nn0 && (pk_raw & 511) < A && pk_raw >= 0));
 
-    // the statistics of the path edges this step backs up: a second, dependent batch, still before the wait
+    // the statistics of the path edges this step backs up: a second, dependent batch (needed by the backup's
+    // stores only, not by the selection below)
     const int pk_mine = (act >= 0 && depth_b <= A && tid < depth_b) ? pk_raw : -1;
     int ev_mine = 0;
     double es_mine = 0.0;
@@ -198,17 +205,6 @@ __device__ __forceinline__ void tree_step_body(const mzgo_tree_t& t, const mzgo_
         const size_t e = ((size_t)g * M + (pk_mine >> 9)) * A + (pk_mine & 511);
         ev_mine = t.edge_visit[e];
         es_mine = t.edge_vsum[e];
-    }
-
-    // ---------------------------------------------------------------- the network outputs of this game
-    wait_outputs();
-    const float rew_g = act >= 0 ? __ldcg(reward + g) : 0.f, val_g = act >= 0 ? __ldcg(value + g) : 0.f;
-    if (act >= 0) {
-#pragma unroll
-        for (int e = 0; e < STEP_EPT; e++) {
-            const int a = e * TPG + tid;
-            if (a < A) sf[e] = __ldcg(soft + (size_t)g * A + a);
-        }
     }
 
     // ---------------------------------------------------------------- expand + backup
