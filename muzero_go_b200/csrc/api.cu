@@ -1,5 +1,8 @@
 // Error plumbing, ABI version, device probe and launch accounting for libmzgo.so.
 #include <stdlib.h>
+#include <mutex>
+#include <unordered_map>
+
 #include "common.cuh"
 
 static thread_local char g_err[512] = "";
@@ -23,9 +26,19 @@ bool mzgo_pdl_enabled() {
 }
 void mzgo_pdl_disable() { g_pdl = 0; }
 
-static unsigned long long g_net_generation = 0;
-unsigned long long mzgo_net_generation() { return g_net_generation; }
-void mzgo_net_bump_generation() { g_net_generation++; }
+// weight generation per network workspace (the unit mzgo_net_prepare works on): preparing one network's weights
+// must not invalidate what was captured for another network (ArenaEvaluator's best_net) or another stream's workspace
+static std::mutex g_gen_mu;
+static std::unordered_map<const void*, unsigned long long> g_net_generation;
+unsigned long long mzgo_net_generation(const void* workspace) {
+    std::lock_guard<std::mutex> lk(g_gen_mu);
+    auto it = g_net_generation.find(workspace);
+    return it == g_net_generation.end() ? 0ull : it->second;
+}
+void mzgo_net_bump_generation(const void* workspace) {
+    std::lock_guard<std::mutex> lk(g_gen_mu);
+    g_net_generation[workspace]++;
+}
 
 extern "C" const char* mzgo_last_error(void) { return g_err; }
 

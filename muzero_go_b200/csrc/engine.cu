@@ -183,11 +183,20 @@ static int search_run_cached(const mzgo_selfplay_t* sp, cudaStream_t st) {
     key.tree.move_index = 0;
     int device = 0;
     MZGO_CUDA(cudaGetDevice(&device));
-    const unsigned long long gen = mzgo_net_generation();
+    const unsigned long long gen = mzgo_net_generation(sp->net.workspace);
     std::lock_guard<std::mutex> lk(g_graph_mu);
     SearchGraph* e = nullptr;
     for (auto& c : g_graphs)
-        if (c.device == device && c.generation == gen && memcmp(&c.key, &key, sizeof(key)) == 0) e = &c;
+        if (c.device == device && memcmp(&c.key, &key, sizeof(key)) == 0) e = &c;
+    if (e && e->generation != gen) {
+        // the same engine after a weight update (a training step, a broadcast): the old graph carries the old head
+        // constants.  Drop it and capture again on THIS call -- the kernels' attributes are set already, so a train /
+        // self-play loop pays one capture per weight version and never runs a move un-captured.
+        if (e->exec) cudaGraphExecDestroy(e->exec);
+        e->exec = nullptr;
+        e->generation = gen;
+        if (e->launches >= 0) e->launches = 0;
+    }
     if (!e) {
         if (g_graphs.size() >= MAX_GRAPHS) {
             if (g_graphs.front().exec) cudaGraphExecDestroy(g_graphs.front().exec);

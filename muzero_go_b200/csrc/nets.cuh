@@ -19,10 +19,10 @@ int mzgo_net_check(const mzgo_net_t* net);
 void mzgo_count_launch();
 void mzgo_count_launches(int k);
 int64_t mzgo_launch_count_peek();
-// bumped by every mzgo_net_prepare: kernel-argument constants derived from the weights (nets_tc.cu) are stale
-// in anything captured before (the search-loop graph cache of engine.cu keys on it)
-unsigned long long mzgo_net_generation();
-void mzgo_net_bump_generation();
+// bumped by every mzgo_net_prepare of that workspace: kernel-argument constants derived from the weights
+// (nets_tc.cu) are stale in anything captured before (the search-loop graph cache of engine.cu keys on it)
+unsigned long long mzgo_net_generation(const void* workspace);
+void mzgo_net_bump_generation(const void* workspace);
 
 int mzgo_net_prepare_fp32(const mzgo_net_t* net, cudaStream_t st);
 int mzgo_rep_fp32(const mzgo_net_t* net, const float* obs, const uint32_t* boards, float* out, const int32_t* out_idx,

@@ -6,7 +6,7 @@
 extern "C" int mzgo_net_prepare(const mzgo_net_t* net, void* stream) {
     if (int e = mzgo_net_check(net)) return e;
     cudaStream_t st = (cudaStream_t)stream;
-    mzgo_net_bump_generation();
+    mzgo_net_bump_generation(net->workspace);
     if (int e = mzgo_net_prepare_fp32(net, st)) return e;
     if (net->precision == 1) return mzgo_net_prepare_tc(net, st);
     return MZGO_OK;

@@ -249,6 +249,24 @@ class BatchedTrainer:
         self._weights_changed()
         return per_traj.clone(), {k: v.clone() for k, v in parts.items()}
 
+    def train_reference_order(self, trajectories, start_indices):
+        """The reference's update order for a batch of more than one trajectory (main.py:391-481), for parity runs:
+        zero_grad ONCE, then for every trajectory in turn -- targets bootstrapped with the weights as updated so far,
+        backward on gradients that keep accumulating, clip_grad_norm_ in place, an Adam step.  len(trajectories)
+        optimizer steps per call (where train_step takes one on the mean loss).  Eager, one trajectory at a time, like
+        the reference.  -> per-trajectory losses [B]."""
+        self.optimizer.zero_grad(set_to_none=True)
+        out = []
+        for traj, s in zip(trajectories, start_indices):
+            b = build_batch(self.net, [traj], [s], self.cfg, self.action_size, self.device)
+            per_traj, _ = self.losses(b)
+            per_traj.sum().backward()
+            torch.nn.utils.clip_grad_norm_(self.net.parameters(), max_norm=self.cfg.max_grad_norm)
+            self.optimizer.step()
+            self._weights_changed()
+            out.append(per_traj.detach())
+        return torch.cat(out)
+
     def _schedule(self):
         """StepLR(step_size, gamma) (main.py:379, :498)."""
         self._sched_calls += 1
@@ -262,16 +280,24 @@ class BatchedTrainer:
         lr = self.optimizer.param_groups[0]["lr"]
         return float(lr.item()) if torch.is_tensor(lr) else float(lr)
 
-    def train(self, replay_buffer, batch_size, rng=random):
+    def train(self, replay_buffer, batch_size, rng=random, reference_order=False):
         """main.py:381-501: sample, one random start index per trajectory, train, write the batch-average loss
         back as every sampled trajectory's priority, step the learning-rate schedule.  None if the buffer
-        cannot fill a batch."""
+        cannot fill a batch.
+
+        reference_order=False (default): ONE optimizer step on the mean of the per-trajectory losses.
+        reference_order=True: the reference's own order -- batch_size steps on accumulating gradients
+        (train_reference_order); slower, for runs that must be comparable with the reference update for update."""
         batch, indices = replay_buffer.sample(batch_size)
         if not batch or len(batch) < batch_size:
             return None
         starts = [rng.randint(0, len(t["actions"]) - 1) for t in batch]
-        b = build_batch(self.net, batch, starts, self.cfg, self.action_size, self.device)
-        per_traj, parts = self.train_step(b)
+        if reference_order:
+            per_traj = self.train_reference_order(batch, starts)
+            parts = {}
+        else:
+            b = build_batch(self.net, batch, starts, self.cfg, self.action_size, self.device)
+            per_traj, parts = self.train_step(b)
         avg_loss = float(per_traj.sum().item()) / batch_size
         if indices is not None:
             replay_buffer.update_priorities(indices, [avg_loss] * len(indices))

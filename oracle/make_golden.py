@@ -269,6 +269,68 @@ def make_train(tag, n, c, moves, start_index, seed):
     print(f"train_{tag}: T={len(traj['actions'])} start={start_index} loss={loss:.6f}")
 
 
+def make_train_batch(tag, n, c, moves, starts, seed):
+    """The REAL MuZeroAgent.train (main.py:381-501) with batch_size = len(starts) > 1: zero_grad ONCE (:391), then for
+    every sampled trajectory backward on gradients that keep accumulating, clip_grad_norm_ in place and an Adam step
+    (:478-480), the n-step bootstrap of each trajectory computed with the weights as updated so far.  The sampled
+    order is recorded (the buffer draws with np.random.choice), random.randint is patched to `starts` in call order."""
+    main = ref_loader.configure(ref_loader.load("main"), n)
+    A = n * n + 1
+    main.config.latent_dim = c
+    main.device = torch.device("cpu")
+    torch.manual_seed(seed)
+    agent = main.MuZeroAgent(n, c, A, 8)
+    with torch.no_grad():
+        agent.net.prediction.pass_logit.fill_(0.21)
+        agent.net.prediction.value_fc.weight.fill_(0.8)
+    before = {k: v.detach().clone().numpy() for k, v in agent.net.state_dict().items()}
+    B = len(starts)
+    trajs = [synthetic_trajectory(n, moves + 3 * i, seed + i) for i in range(B)]
+    for i, t in enumerate(trajs):
+        t["id"] = i
+    rb = main.MultiVersionReplayBuffer(8, 1, True)
+    for t in trajs:
+        rb.add(t)
+    order = []
+    real_sample = rb.sample
+
+    def recording_sample(k):
+        batch, idx = real_sample(k)
+        order.extend(int(t["id"]) for t in batch)
+        return batch, idx
+    rb.sample = recording_sample
+    calls = [0]
+
+    def fake_randint(lo, hi):
+        v = starts[calls[0]]
+        calls[0] += 1
+        assert lo <= v <= hi
+        return v
+    real_randint, real_wandb = main.random.randint, main.wandb
+    main.random.randint = fake_randint
+    main.wandb = type("NoWandb", (), {"log": staticmethod(lambda *a, **k: None)})
+    np.random.seed(seed)
+    agent.net.train()
+    try:
+        loss = agent.train(rb, B)
+    finally:
+        main.random.randint, main.wandb = real_randint, real_wandb
+    after = {k: v.detach().clone().numpy() for k, v in agent.net.state_dict().items()}
+    out = {"n": n, "c": c, "batch": B, "starts": np.asarray(starts, dtype=np.int64), "order": np.asarray(order, dtype=np.int64),
+           "loss": np.float64(loss), "unroll_steps": main.config.unroll_steps, "discount": main.config.discount}
+    for i, t in enumerate(trajs):
+        out[f"t{i}.observations"] = np.stack(t["observations"])
+        out[f"t{i}.actions"] = np.asarray(t["actions"], dtype=np.int64)
+        out[f"t{i}.rewards"] = np.asarray(t["rewards"], dtype=np.float64)
+        out[f"t{i}.policies"] = np.stack(t["policies"])
+    for k, v in before.items():
+        out["w0." + k] = v
+    for k, v in after.items():
+        out["w1." + k] = v
+    np.savez_compressed(os.path.join(OUT, f"trainbatch_{tag}.npz"), **out)
+    print(f"trainbatch_{tag}: order={order} starts={list(starts)} loss={loss:.6f}")
+
+
 def make_replay(seed):
     """Sampling order of the REAL replay buffers (main.py:158-244) under a fixed numpy seed: FIFO eviction,
     priority updates, multi-version mapping."""
@@ -353,6 +415,7 @@ def main():
     make_train("N5_C16_mid", 5, 16, 30, start_index=4, seed=20)
     make_train("N5_C16_tail", 5, 16, 14, start_index=9, seed=21)     # unroll runs past the end of the game
     make_train("N6_C32_head", 6, 32, 40, start_index=0, seed=22)
+    make_train_batch("N5_C16_B3", 5, 16, 16, starts=[2, 7, 0], seed=23)
     make_replay(seed=5)
     make_arena(seed=6)
 

@@ -261,3 +261,25 @@ def test_reference_training_step_through_the_native_kernels(name):
         sd = net.state_dict()
         for k in w1:
             assert torch.allclose(sd[k].cpu(), w1[k], rtol=0, atol=2e-6), (k, graph)
+
+
+def test_reference_order_batch_on_the_gpu():
+    """tests/golden/trainbatch_N5_C16_B3.npz (the REAL MuZeroAgent.train, batch of 3: three clipped Adam steps on
+    accumulating gradients) reproduced on the GPU through the native convolution kernels."""
+    import os
+    from muzero_go_b200.networks import MuZeroNet
+    from muzero_go_b200.trainer import BatchedTrainer, TrainConfig
+    from tests.test_trainer import GOLDEN, load_batch_case
+    z, trajs, w0, w1 = load_batch_case(os.path.join(GOLDEN, "trainbatch_N5_C16_B3.npz"))
+    n, c = int(z["n"]), int(z["c"])
+    A = n * n + 1
+    order, starts = [int(i) for i in z["order"]], [int(s) for s in z["starts"]]
+    net = MuZeroNet(c, A)
+    net.load_state_dict(w0)
+    net = net.cuda()
+    tr = BatchedTrainer(net, A, TrainConfig(unroll_steps=int(z["unroll_steps"]), discount=float(z["discount"])))
+    per_traj = tr.train_reference_order([trajs[i] for i in order], starts)
+    assert abs(float(per_traj.sum()) / len(order) - float(z["loss"])) <= 1e-5 * abs(float(z["loss"]))
+    sd = net.state_dict()
+    for k in w1:
+        assert torch.allclose(sd[k].cpu(), w1[k], rtol=0, atol=4e-6), k

@@ -150,3 +150,46 @@ def test_train_loop_priorities_and_schedule(tmp_path):
     assert calculate_returns([1.0, 2.0], 4.0, 0.5) == [1.0 + 0.5 * (2.0 + 0.5 * 4.0), 2.0 + 0.5 * 4.0]
     with open(path, "rb") as f:
         assert isinstance(pickle.load(f), list)
+
+
+def load_batch_case(path):
+    z = np.load(path)
+    B = int(z["batch"])
+    trajs = []
+    for i in range(B):
+        T = len(z[f"t{i}.actions"])
+        trajs.append({"observations": [z[f"t{i}.observations"][k] for k in range(T + 2)],
+                      "actions": [int(a) for a in z[f"t{i}.actions"]], "rewards": [float(r) for r in z[f"t{i}.rewards"]],
+                      "policies": [z[f"t{i}.policies"][k] for k in range(T)]})
+    w0 = {k[3:]: torch.from_numpy(z[k]) for k in z.files if k.startswith("w0.")}
+    w1 = {k[3:]: torch.from_numpy(z[k]) for k in z.files if k.startswith("w1.")}
+    return z, trajs, w0, w1
+
+
+def test_reference_order_reproduces_a_reference_batch():
+    """tests/golden/trainbatch_*.npz: the REAL MuZeroAgent.train with batch_size 3 -- zero_grad once, then per trajectory
+    backward on accumulating gradients, clip, Adam step, bootstraps with the weights as updated so far
+    (main.py:391-481).  `train_reference_order` reproduces the average loss and the weights after the three steps;
+    the default one-step-per-batch `train_step` on the same batch does NOT land on those weights (the documented
+    difference)."""
+    from muzero_go_b200.networks import MuZeroNet
+    from muzero_go_b200.trainer import BatchedTrainer, TrainConfig, build_batch
+    z, trajs, w0, w1 = load_batch_case(os.path.join(GOLDEN, "trainbatch_N5_C16_B3.npz"))
+    n, c = int(z["n"]), int(z["c"])
+    A = n * n + 1
+    order, starts = [int(i) for i in z["order"]], [int(s) for s in z["starts"]]
+    cfg = TrainConfig(unroll_steps=int(z["unroll_steps"]), discount=float(z["discount"]))
+    net = MuZeroNet(c, A)
+    net.load_state_dict(w0)
+    tr = BatchedTrainer(net, A, cfg)
+    per_traj = tr.train_reference_order([trajs[i] for i in order], starts)
+    assert abs(float(per_traj.sum()) / len(order) - float(z["loss"])) <= 1e-5 * abs(float(z["loss"]))
+    sd = net.state_dict()
+    for k in w1:
+        assert torch.allclose(sd[k], w1[k], rtol=0, atol=4e-6), k
+    net2 = MuZeroNet(c, A)
+    net2.load_state_dict(w0)
+    tr2 = BatchedTrainer(net2, A, cfg)
+    tr2.train_step(build_batch(net2, [trajs[i] for i in order], starts, cfg, A, torch.device("cpu")))
+    far = max(float((net2.state_dict()[k] - w1[k]).abs().max()) for k in w1)
+    assert far > 5e-5            # one step of 1e-4 against three
