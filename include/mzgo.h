@@ -359,6 +359,10 @@ int mzgo_train_conv3x3_bwd_weight(const float* x, const float* dy, const float* 
 long long mzgo_debug_fastdiv_check(unsigned long long seed, int blocks, long long per_thread);
 int mzgo_debug_tc_trace(void* buf /*device*/);
 
+/* Trace build only (python -m muzero_go_b200.build --define MZGO_TRACE_TREE): when buf != NULL every tree step stamps
+ * its phases per game into buf[G][16] (uint64 globaltimer values, tools/tree_trace.py); MZGO_ERR_UNSUPPORTED otherwise. */
+int mzgo_debug_tree_trace(void* buf /*device*/);
+
 /* mzgo_rules_step / mzgo_rules_playout run a warp per board below this many boards and a thread per board from
  * it on (board sizes 5, 6, 9, where it is the faster one on large batches; 13 and 19 only when the value is 0;
  * same results bit for bit).  Returns the previous value; a negative argument only reads it.  Default 32768. */

@@ -70,6 +70,7 @@ _PROTOS = {
     "mzgo_debug_fastdiv_check": (C.c_longlong, [C.c_ulonglong, i32, C.c_longlong]),
     "mzgo_debug_rules_tpb_min": (i32, [i32]),
     "mzgo_debug_tc_trace": (i32, [vp]),
+    "mzgo_debug_tree_trace": (i32, [vp]),
     "mzgo_sizeof": (i64, [i32]),
     "mzgo_rules_reset": (i32, [vp, i32, i32, vp]),
     "mzgo_rules_step": (i32, [vp, vp, vp, i32, i32, vp]),

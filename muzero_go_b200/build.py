@@ -44,9 +44,10 @@ def up_to_date():
         return fh.read().strip() == _digest()
 
 
-def build(force=False, verbose=False, checked=False):
+def build(force=False, verbose=False, checked=False, defines=()):
     """checked=True: the same library with MZGO_DCHECK assertions compiled in (always rebuilt, and the recorded hash is
     left stale on purpose so that the next plain build() rebuilds the normal library)."""
+    checked = checked or bool(defines)
     if not force and not checked and up_to_date():
         return SO
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
@@ -57,7 +58,7 @@ def build(force=False, verbose=False, checked=False):
     for src in sources():
         obj = os.path.join(objdir, os.path.basename(src)[:-3] + ".o")
         objs.append(obj)
-        cmd = [nvcc] + NVCC_FLAGS + ([CHECKED_FLAG] if checked else []) + (["-Xptxas", "-v"] if verbose else []) + ["-c", src, "-o", obj]
+        cmd = [nvcc] + NVCC_FLAGS + ([CHECKED_FLAG] if checked and not defines else []) + ["-D" + d for d in defines] + (["-Xptxas", "-v"] if verbose else []) + ["-c", src, "-o", obj]
         procs.append((cmd, subprocess.Popen(cmd)))
     for cmd, p in procs:
         if p.wait() != 0:
@@ -69,4 +70,5 @@ def build(force=False, verbose=False, checked=False):
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv, checked="--checked" in sys.argv))
+    _defs = [sys.argv[i + 1] for i, a in enumerate(sys.argv[:-1]) if a == "--define"]
+    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv, checked="--checked" in sys.argv, defines=_defs))

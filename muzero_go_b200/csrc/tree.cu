@@ -379,10 +379,15 @@ k_tree_step(mzgo_tree_t t, mzgo_search_params_t p, const float* soft, const floa
     __shared__ StepShared<TPG> sh;
     const int sub = threadIdx.x / TPG, tid = threadIdx.x % TPG;
     const int g = blockIdx.x * GPB + sub;
-    griddep_wait();                              // the network outputs of the launch before (PDL, common.cuh)
+#ifdef MZGO_TRACE_TREE
+    if (g < t.G) TSTAMP(0, 0);
+#endif
     griddep_launch();
-    if (g >= t.G) return;                        // TPG == 128: the whole block; TPG == 32: whole warps
-    tree_step_body<TPG, 0>(t, p, soft, reward, value, choice_stream, stride, do_backup, do_select, sh, sub, tid, g, [] {});
+    if (g >= t.G) { griddep_wait(); return; }    // TPG == 128: the whole block; TPG == 32: whole warps
+    // the grid-dependency wait (PDL, common.cuh) sits INSIDE the step, in front of the first read of what the kernel
+    // before this one wrote (the network outputs): the tree data is fetched while that kernel drains
+    tree_step_body<TPG, 0>(t, p, soft, reward, value, choice_stream, stride, do_backup, do_select, sh, sub, tid, g,
+                           [] { griddep_wait(); });
 }
 
 // main.py:666-669
@@ -617,6 +622,19 @@ extern "C" int mzgo_tree_step(const mzgo_tree_t* tree, const mzgo_search_params_
     mzgo_count_launch();
     MZGO_LAUNCH_CHECK();
     return MZGO_OK;
+}
+
+// Trace build only: arm / disarm the per-game stamps of the tree step (buf = device [G][16] uint64, or NULL).
+extern "C" int mzgo_debug_tree_trace(void* buf) {
+#ifdef MZGO_TRACE_TREE
+    unsigned long long* p = (unsigned long long*)buf;
+    MZGO_CUDA(cudaMemcpyToSymbol(g_tree_trace, &p, sizeof(p)));
+    return MZGO_OK;
+#else
+    (void)buf;
+    mzgo_set_error("mzgo_debug_tree_trace needs the trace build (python -m muzero_go_b200.build --define MZGO_TRACE_TREE)");
+    return MZGO_ERR_UNSUPPORTED;
+#endif
 }
 
 extern "C" int mzgo_tree_visit_counts(const mzgo_tree_t* tree, int32_t* out, void* stream) {

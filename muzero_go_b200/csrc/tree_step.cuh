@@ -5,6 +5,22 @@
 
 namespace {
 
+// Trace build (python -m muzero_go_b200.build --define MZGO_TRACE_TREE; tools/tree_trace.py): per-game globaltimer
+// stamps of the step's phases.  A stamp takes a loaded value as an operand, so it is taken when that value ARRIVES.
+#ifdef MZGO_TRACE_TREE
+__device__ unsigned long long* g_tree_trace = nullptr;     // [G][16]
+#define TSTAMP(slot, dep)                                                                          \
+    do {                                                                                           \
+        if (tid == 0 && do_select && g_tree_trace) {                                               \
+            unsigned long long _t;                                                                 \
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(_t) : "r"((int)(dep)) : "memory");   \
+            g_tree_trace[(size_t)g * 16 + (slot)] = _t;                                            \
+        }                                                                                          \
+    } while (0)
+#else
+#define TSTAMP(slot, dep) ((void)0)
+#endif
+
 constexpr int STEP_THREADS = 128;
 constexpr int STEP_EPT = 3;   // edges per thread: A <= 3 * TPG
 
@@ -156,11 +172,13 @@ __device__ __forceinline__ void tree_step_body(const mzgo_tree_t& t, const mzgo_
     int* path = reinterpret_cast<int*>(t.prior + (size_t)g * M * A);   // scratch row of the root (its priors are float64, elsewhere)
     const size_t rbase = (size_t)g * M * A;      // edges of the root
 
-    // ---------------------------------------------------------------- round trip 1: every independent load
-    // (the network outputs of the leaf among them: both callers have them ready on entry -- the kernel before
-    // k_tree_step wrote them, the network kernel's tree phase starts behind a barrier -- and loading them
-    // unconditionally keeps them off the dependent chain leaf record -> outputs -> backup -> root selection)
-    wait_outputs();
+    // ---------------------------------------------------------------- round trip 1: every load of TREE data
+    // Nothing here was written by the kernel before this one (the network kernel only writes latents and its
+    // outputs; the trees were last written by the previous tree step, which completed before the network kernel
+    // could start), so in the stand-alone kernel all of it is issued BEFORE the grid-dependency wait: the blocks
+    // become resident while the network kernel's last CTAs drain and spend that wait fetching.  (The FIRST step of
+    // a search, do_backup == 0, follows the root preparation, which does write tree data: it waits first.)
+    if (!do_backup) wait_outputs();
     const int act = do_backup ? t.leaf_action[g] : -1;
     const int par = t.leaf_parent[g];
     const int nw = t.leaf_node[g];
@@ -176,14 +194,12 @@ __device__ __forceinline__ void tree_step_body(const mzgo_tree_t& t, const mzgo_
     float mk[STEP_EPT], sf[STEP_EPT];
     int nv_r[STEP_EPT], ch_r[STEP_EPT];
     double pr_r[STEP_EPT], vs_r[STEP_EPT];
-    const float rew_g = do_backup ? __ldcg(reward + g) : 0.f, val_g = do_backup ? __ldcg(value + g) : 0.f;
 #pragma unroll
     for (int e = 0; e < STEP_EPT; e++) {
         const int a = e * TPG + tid;
         mk[e] = 0.f; sf[e] = 0.f; nv_r[e] = 0; ch_r[e] = -1; pr_r[e] = 0.0; vs_r[e] = 0.0;
         if (a < A) {
             mk[e] = mask[a];
-            if (do_backup) sf[e] = __ldcg(soft + (size_t)g * A + a);
             if (do_select) {
                 nv_r[e] = t.edge_visit[rbase + a];
                 pr_r[e] = t.root_prior[(size_t)g * A + a];
@@ -195,9 +211,9 @@ __device__ __forceinline__ void tree_step_body(const mzgo_tree_t& t, const mzgo_
     MZGO_DCHECK(g >= 0 && g < t.G && A <= STEP_EPT * TPG && nn0 >= 0 && nn0 <= M);
     MZGO_DCHECK(act < A && (act < 0 || (par >= 0 && par < nn0 && nw == nn0 && nw < M && depth_b >= 1)));
     MZGO_DCHECK(!(act >= 0 && depth_b <= A && tid < depth_b) || ((pk_raw >> 9) < nn0 && (pk_raw & 511) < A && pk_raw >= 0));
+    TSTAMP(2, act + nv_r[0] + ch_r[STEP_EPT - 1] + pk_raw);
 
-    // the statistics of the path edges this step backs up: a second, dependent batch (needed by the backup's
-    // stores only, not by the selection below)
+    // the statistics of the path edges this step backs up: a second, dependent batch of tree data
     const int pk_mine = (act >= 0 && depth_b <= A && tid < depth_b) ? pk_raw : -1;
     int ev_mine = 0;
     double es_mine = 0.0;
@@ -205,6 +221,21 @@ __device__ __forceinline__ void tree_step_body(const mzgo_tree_t& t, const mzgo_
         const size_t e = ((size_t)g * M + (pk_mine >> 9)) * A + (pk_mine & 511);
         ev_mine = t.edge_visit[e];
         es_mine = t.edge_vsum[e];
+    }
+    const double root_vsum0 = t.root_vsum[g];
+    const int sims_done0 = t.sims_done[g];
+    const long long depth_sum0 = t.depth_sum[g];
+
+    // ---------------------------------------------------------------- the network outputs of this game's leaf
+    if (do_backup) wait_outputs();
+    TSTAMP(1, 0);
+    const float rew_g = do_backup ? __ldcg(reward + g) : 0.f, val_g = do_backup ? __ldcg(value + g) : 0.f;
+    if (do_backup) {
+#pragma unroll
+        for (int e = 0; e < STEP_EPT; e++) {
+            const int a = e * TPG + tid;
+            if (a < A) sf[e] = __ldcg(soft + (size_t)g * A + a);
+        }
     }
 
     // ---------------------------------------------------------------- expand + backup
@@ -275,9 +306,9 @@ __device__ __forceinline__ void tree_step_body(const mzgo_tree_t& t, const mzgo_
                 }
             }
             t.root_visit[g] = root_visit0 + 1;
-            t.root_vsum[g] = __dadd_rn(t.root_vsum[g], (v1 && (depth & 1)) ? -bv : bv);
-            t.sims_done[g] += 1;
-            t.depth_sum[g] += depth;
+            t.root_vsum[g] = __dadd_rn(root_vsum0, (v1 && (depth & 1)) ? -bv : bv);
+            t.sims_done[g] = sims_done0 + 1;
+            t.depth_sum[g] = depth_sum0 + depth;
         }
         // the root level fetched above predates this backup: patch the one root edge on the path (the same
         // float64 addition the backup thread performs on the same operands) and the new child link
@@ -290,8 +321,10 @@ __device__ __forceinline__ void tree_step_body(const mzgo_tree_t& t, const mzgo_
             if (par == 0 && a == act) ch_r[e] = nw;
         }
     }
+    TSTAMP(3, ev_mine + __float_as_int(sf[0]));
     if (!do_select) return;
     step_sync<TPG, BAR>();                            // the statistics written above are read below by other threads
+    TSTAMP(4, 0);
 
     // ---------------------------------------------------------------- select
     if (!is_active) {
@@ -316,6 +349,7 @@ __device__ __forceinline__ void tree_step_body(const mzgo_tree_t& t, const mzgo_
         int oa = -1, on = 0, oc = -1;
         const int rc = step_level<TPG, BAR>(sh, sub, tid, nv_r, cp, vs_r, ch_r, pos, npar, v1, ctr0, choice_stream, stream_off, p,
                                        (uint32_t)(g + p.game_base), move_index, &oa, &on, &oc);
+        TSTAMP(min(5 + 2 * (depth - 1), 13), rc + oa);
         if (rc == 0) { sel_parent = node; sel_action = oa; break; }
         if (rc == 2 || oc <= 0) break;           // terminal leaf / dropped simulation (node keeps the leaf)
         MZGO_DCHECK(oa >= 0 && oa < A && oc < M && oc < (act >= 0 ? nw + 1 : nn0));
@@ -336,6 +370,7 @@ __device__ __forceinline__ void tree_step_body(const mzgo_tree_t& t, const mzgo_
                 ch_r[e] = (int)t.child[base + a];
             }
         }
+        TSTAMP(min(6 + 2 * (depth - 2), 14), nv_r[0] + ch_r[STEP_EPT - 1] + __float_as_int(prf[0]));
         pos = 0u;
 #pragma unroll
         for (int e = 0; e < STEP_EPT; e++) {
@@ -369,6 +404,7 @@ __device__ __forceinline__ void tree_step_body(const mzgo_tree_t& t, const mzgo_
         t.leaf_out_slot[g] = sel_action >= 0 ? g * M + nn : -1;
         if (sel_action < 0) t.dropped[g] += 1;
     }
+    TSTAMP(15, 0);
 }
 
 
