@@ -13,7 +13,7 @@ echo "launches 19 rc=$?"
 $C9 > $O/plain_9.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -s 150 -c 420 --csv --log-file $O/launches_9x9.csv $C9 > $O/ncu_l9.log 2>&1
 echo "launches 9 rc=$?"
-# --set full: 9x9 fused kernel, rules kernels (19x19 conv + tree step: tools/_ncu1.sh, same command as C19)
+# --set full: 9x9 fused kernel, rules kernels (19x19 conv + tree step: tools/ncu_19x19.sh, same command as C19)
 ncu --set full --clock-control none --import-source on -k regex:"k_tc_conv" -s 300 -c 2 -o $O/prof_9x9 $C9 > $O/ncu_f9.log 2>&1
 echo "full 9 rc=$?"
 ncu --set full --clock-control none --import-source on -k regex:"k_rules_playout" -c 12 -o $O/prof_rules19 $C19 > $O/ncu_fr.log 2>&1
