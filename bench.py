@@ -471,6 +471,9 @@ def measure(args, wl, G, S, K, W, rank, world, dev, primary, positions="mixed"):
     _lib.check(lib.mzgo_search_run(d_part, None, 0, _lib.stream_ptr()))
     step_args = (eng.tree.desc, p_struct, _lib.ptr(eng.leaf_policy), _lib.ptr(eng.leaf_reward), _lib.ptr(eng.leaf_value),
                  None, 0)
+    # mzgo_search_run ends with a backup-only step: select the next leaf first, so that every step below backs up a
+    # leaf that a selection really produced (with whatever network outputs are in the buffers) and selects the next
+    _lib.check(lib.mzgo_tree_step(*step_args, 0, 1, _lib.stream_ptr()))
     _lib.check(lib.mzgo_tree_step(*step_args, 1, 1, _lib.stream_ptr()))    # warm
     torch.cuda.synchronize()
     g_tree = torch.cuda.CUDAGraph()

@@ -160,16 +160,17 @@ extern "C" int mzgo_search_run(const mzgo_selfplay_t* sp, const uint32_t* choice
     }
     // per simulation: [expand/backup of the previous leaf + next selection] -> recurrent inference
     for (int s = 0; s < sp->num_simulations; s++) {
-        if (int e = mzgo_tree_step(t, &sp->params, sp->leaf_policy, sp->leaf_reward, sp->leaf_value, choice_stream, stride,
-                                   s > 0, 1, st))
+        // (from the second step on the kernel in front of the step is this loop's own network kernel)
+        if (int e = mzgo_tree_step_impl(t, &sp->params, sp->leaf_policy, sp->leaf_reward, sp->leaf_value, choice_stream, stride,
+                                        s > 0, 1, s > 0, st))
             return e;
         if (int e = mzgo_net_recurrent(&sp->net, sp->arena, t->leaf_in_slot, t->leaf_action, t->leaf_out_slot,
                                        sp->leaf_reward, sp->leaf_value, sp->leaf_policy, 1, t->G, stream))
             return e;
     }
     if (sp->num_simulations > 0)
-        if (int e = mzgo_tree_step(t, &sp->params, sp->leaf_policy, sp->leaf_reward, sp->leaf_value, choice_stream, stride,
-                                   1, 0, st))
+        if (int e = mzgo_tree_step_impl(t, &sp->params, sp->leaf_policy, sp->leaf_reward, sp->leaf_value, choice_stream, stride,
+                                        1, 0, 1, st))
             return e;
     return MZGO_OK;
 }

@@ -24,6 +24,11 @@ int64_t mzgo_launch_count_peek();
 unsigned long long mzgo_net_generation(const void* workspace);
 void mzgo_net_bump_generation(const void* workspace);
 
+// mzgo_tree_step with the caller's word that the kernel in front of it is the network kernel of the same search (tree.cu)
+int mzgo_tree_step_impl(const mzgo_tree_t* tree, const mzgo_search_params_t* p, const float* soft, const float* reward,
+                        const float* value, const uint32_t* choice_stream, int stride, int do_backup, int do_select,
+                        int after_network, void* stream);
+
 int mzgo_net_prepare_fp32(const mzgo_net_t* net, cudaStream_t st);
 int mzgo_rep_fp32(const mzgo_net_t* net, const float* obs, const uint32_t* boards, float* out, const int32_t* out_idx,
                   long out_stride, int B, cudaStream_t st);

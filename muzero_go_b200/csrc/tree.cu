@@ -374,7 +374,7 @@ k_tree_expand_backup(mzgo_tree_t t, mzgo_search_params_t p, const float* __restr
 template <int TPG>
 __global__ void __launch_bounds__(STEP_THREADS, 8)
 k_tree_step(mzgo_tree_t t, mzgo_search_params_t p, const float* soft, const float* reward, const float* value,
-            const uint32_t* __restrict__ choice_stream, int stride, int do_backup, int do_select) {
+            const uint32_t* __restrict__ choice_stream, int stride, int do_backup, int do_select, int early_loads) {
     constexpr int GPB = STEP_THREADS / TPG;     // games per block
     __shared__ StepShared<TPG> sh;
     const int sub = threadIdx.x / TPG, tid = threadIdx.x % TPG;
@@ -387,7 +387,7 @@ k_tree_step(mzgo_tree_t t, mzgo_search_params_t p, const float* soft, const floa
     // the grid-dependency wait (PDL, common.cuh) sits INSIDE the step, in front of the first read of what the kernel
     // before this one wrote (the network outputs): the tree data is fetched while that kernel drains
     tree_step_body<TPG, 0>(t, p, soft, reward, value, choice_stream, stride, do_backup, do_select, sh, sub, tid, g,
-                           [] { griddep_wait(); });
+                           [] { griddep_wait(); }, early_loads != 0);
 }
 
 // main.py:666-669
@@ -605,23 +605,32 @@ extern "C" int mzgo_tree_expand_backup(const mzgo_tree_t* tree, const mzgo_searc
 }
 
 // Fused simulation step (engine path): expand + backup of the previous leaf, then the next selection.
-extern "C" int mzgo_tree_step(const mzgo_tree_t* tree, const mzgo_search_params_t* p, const float* soft,
-                              const float* reward, const float* value, const uint32_t* choice_stream, int stride,
-                              int do_backup, int do_select, void* stream) {
+// after_network != 0: the caller enqueued the network kernel of the same search directly in front of this step (and the
+// tree step before that), so the step may fetch its tree data before the grid-dependency wait (tree_step.cuh).
+int mzgo_tree_step_impl(const mzgo_tree_t* tree, const mzgo_search_params_t* p, const float* soft, const float* reward,
+                        const float* value, const uint32_t* choice_stream, int stride, int do_backup, int do_select,
+                        int after_network, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
+    const int early = (after_network && do_backup) ? 1 : 0;
     if (int e = check_tree(tree)) return e;
     if (int e = ensure_rcp_table()) return e;
     MZGO_CHECK_ARG(p && (!do_backup || (soft && reward && value)), "NULL argument");
     if (tree->G == 0) return MZGO_OK;
     if (tree->A <= STEP_EPT * 32)
         MZGO_CUDA(mzgo_launch_pdl(k_tree_step<32>, dim3(ceil_div(tree->G, STEP_THREADS / 32)), dim3(STEP_THREADS), 0, st, *tree, *p,
-                                  soft, reward, value, choice_stream, stride, do_backup, do_select));
+                                  soft, reward, value, choice_stream, stride, do_backup, do_select, early));
     else
         MZGO_CUDA(mzgo_launch_pdl(k_tree_step<128>, dim3(tree->G), dim3(STEP_THREADS), 0, st, *tree, *p, soft, reward, value,
-                                  choice_stream, stride, do_backup, do_select));
+                                  choice_stream, stride, do_backup, do_select, early));
     mzgo_count_launch();
     MZGO_LAUNCH_CHECK();
     return MZGO_OK;
+}
+
+extern "C" int mzgo_tree_step(const mzgo_tree_t* tree, const mzgo_search_params_t* p, const float* soft,
+                              const float* reward, const float* value, const uint32_t* choice_stream, int stride,
+                              int do_backup, int do_select, void* stream) {
+    return mzgo_tree_step_impl(tree, p, soft, reward, value, choice_stream, stride, do_backup, do_select, 0, stream);
 }
 
 // Trace build only: arm / disarm the per-game stamps of the tree step (buf = device [G][16] uint64, or NULL).

@@ -166,7 +166,7 @@ template <int TPG, int BAR, class Wait>
 __device__ __forceinline__ void tree_step_body(const mzgo_tree_t& t, const mzgo_search_params_t& p, const float* soft,
                                                const float* reward, const float* value, const uint32_t* choice_stream,
                                                int stride, int do_backup, int do_select, StepShared<TPG>& sh, int sub,
-                                               int tid, int g, Wait wait_outputs) {
+                                               int tid, int g, Wait wait_outputs, bool early_loads = false) {
     const bool v1 = p.variant == MZGO_VARIANT_SELFPLAY;
     const int A = t.A, M = t.M;
     int* path = reinterpret_cast<int*>(t.prior + (size_t)g * M * A);   // scratch row of the root (its priors are float64, elsewhere)
@@ -176,9 +176,11 @@ __device__ __forceinline__ void tree_step_body(const mzgo_tree_t& t, const mzgo_
     // Nothing here was written by the kernel before this one (the network kernel only writes latents and its
     // outputs; the trees were last written by the previous tree step, which completed before the network kernel
     // could start), so in the stand-alone kernel all of it is issued BEFORE the grid-dependency wait: the blocks
-    // become resident while the network kernel's last CTAs drain and spend that wait fetching.  (The FIRST step of
-    // a search, do_backup == 0, follows the root preparation, which does write tree data: it waits first.)
-    if (!do_backup) wait_outputs();
+    // become resident while the network kernel's last CTAs drain and spend that wait fetching.  Only when the caller
+    // vouches for that order (early_loads: the steps mzgo_search_run enqueues behind a network kernel): the first step
+    // of a search follows the root preparation and a step called back to back with another one follows a tree step,
+    // both of which DO write tree data -- those wait first.
+    if (!early_loads) wait_outputs();
     const int act = do_backup ? t.leaf_action[g] : -1;
     const int par = t.leaf_parent[g];
     const int nw = t.leaf_node[g];
@@ -227,7 +229,7 @@ __device__ __forceinline__ void tree_step_body(const mzgo_tree_t& t, const mzgo_
     const long long depth_sum0 = t.depth_sum[g];
 
     // ---------------------------------------------------------------- the network outputs of this game's leaf
-    if (do_backup) wait_outputs();
+    if (early_loads) wait_outputs();
     TSTAMP(1, 0);
     const float rew_g = do_backup ? __ldcg(reward + g) : 0.f, val_g = do_backup ? __ldcg(value + g) : 0.f;
     if (do_backup) {

@@ -89,7 +89,8 @@ def test_agent_plays_a_legal_game_against_the_oracle_env():
     assert moves > 4
 
 
-@pytest.mark.parametrize("n,c,G,S,precision", [(5, 16, 64, 12, "fp32"), (9, 128, 32, 20, "fp32"), (9, 128, 32, 20, "bf16")])
+@pytest.mark.parametrize("n,c,G,S,precision", [(5, 16, 64, 12, "fp32"), (9, 128, 32, 20, "fp32"), (9, 128, 32, 20, "bf16"),
+                                               (13, 128, 6, 16, "bf16")])
 def test_engine_invariants(n, c, G, S, precision):
     import muzero_go_b200 as mz
     _, net = make_net(n, c, 5, precision)
