@@ -363,12 +363,14 @@ k_tree_expand_backup(mzgo_tree_t t, mzgo_search_params_t p, const float* __restr
 // Arithmetic is the same, operation for operation, as in k_tree_select / k_tree_expand_backup.
 //
 // Memory round trips (the kernel is latency bound: a few KB per game, dependent levels):
-//   1. everything that does not depend on another load is fetched at the top in one batch: the leaf record,
-//      the network outputs, the mask, the stored path AND the root level of the next selection (visits,
-//      priors, value sums, child links).  The root statistics this very step changes (one edge of the
-//      backup path, the child link when the leaf hangs off the root) are patched in registers;
-//   2. the backup read-modify-write of the path edges;
-//   3. one batch per level below the root (visits, priors, value sums and child links together).
+//   1. all TREE data that does not depend on another load is fetched at the top in one batch: the leaf record, the
+//      mask, the stored path, the per-game counters AND the root level of the next selection (visits, priors, value
+//      sums, child links); the root statistics this very step changes (one edge of the backup path, the child link
+//      when the leaf hangs off the root) are patched in registers.  Behind the engine's own network kernel this batch
+//      and the next are issued BEFORE the grid-dependency wait (the blocks are resident while that kernel drains);
+//   2. the statistics of the path edges to back up (needed by the backup's stores only);
+//   3. behind the wait: the network outputs of the leaf (value, reward, softmax);
+//   4. one batch per level below the root (visits, priors, value sums and child links together).
 // (the step itself lives in tree_step.cuh: the network kernel of nets_tc.cu runs the same code as a warp-group role)
 
 template <int TPG>
