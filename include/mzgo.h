@@ -351,6 +351,20 @@ int mzgo_train_conv3x3_bwd_data(const float* dy, const float* y_gate, const floa
 int64_t mzgo_train_wgrad_scratch_floats(int B, int Cin, int Cout);
 int mzgo_train_conv3x3_bwd_weight(const float* x, const float* dy, const float* y_gate, float* dw, float* db,
                                   float* scratch, int B, int Cin, int Cout, int n, void* stream);
+/* The same weight gradient for callers that cannot allocate (code under CUDA-graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same arguments and results as mzgo_train_conv3x3_bwd_weight (bit for bit: same kernels, same order of summation),
+ * minus `scratch`: the partial sums live in a device array built into the library, MZGO_TRAIN_WGRAD_STATIC_MAX_FLOATS
+ * floats (10 MiB, held by every GPU that loads the library until the process exits; enough for the reference's
+ * largest layer, 129 -> 128 channels, at any batch size).  Shapes with mzgo_train_wgrad_scratch_floats(B, Cin, Cout)
+ * beyond that are refused with MZGO_ERR_ARG and a message naming both numbers.  The call itself allocates nothing
+ * (no cudaMalloc / cudaFree / allocating library routine) and launches on `stream` without synchronising.  All calls
+ * on one device share the array: nothing in it needs to start at zero (each call writes every partial sum before
+ * it reads it), but calls that OVERLAP on the GPU -- two streams, two host threads -- race on it; serialise them. */
+#define MZGO_TRAIN_WGRAD_STATIC_MAX_FLOATS (10 * 1024 * 1024 / 4)
+int64_t mzgo_train_wgrad_static_max_floats(void);
+int mzgo_train_conv3x3_bwd_weight_static(const float* x, const float* dy, const float* y_gate, float* dw, float* db, int B,
+                                         int Cin, int Cout, int n, void* stream);
 
 /* Test / profiling hooks.  mzgo_debug_fastdiv_check: operand pairs on which the tree kernels' 5-operation
  * correctly rounded division differs from the generic IEEE division (must be 0; synchronous).

@@ -101,6 +101,8 @@ _PROTOS = {
     "mzgo_train_conv3x3_bwd_data": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, vp]),
     "mzgo_train_wgrad_scratch_floats": (i64, [i32, i32, i32]),
     "mzgo_train_conv3x3_bwd_weight": (i32, [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, vp]),
+    "mzgo_train_wgrad_static_max_floats": (i64, []),
+    "mzgo_train_conv3x3_bwd_weight_static": (i32, [vp, vp, vp, vp, vp, i32, i32, i32, i32, vp]),
     "mzgo_selfplay_pack_rows": (i32, [C.POINTER(SelfPlayDesc), i32, i32, vp, i32, i32, vp]),
 }
 

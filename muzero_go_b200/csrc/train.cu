@@ -14,6 +14,7 @@
 // ever written.  Everything is launched on the caller's stream without synchronisation (CUDA-graph capturable: the
 // trainer replays its whole step from one graph).
 #include <algorithm>
+#include <mutex>
 
 #include "common.cuh"
 #include "nets.cuh"
@@ -275,4 +276,52 @@ extern "C" int mzgo_train_conv3x3_bwd_weight(const float* x, const float* dy, co
     mzgo_count_launches(2);
     MZGO_LAUNCH_CHECK();
     return MZGO_OK;
+}
+
+// ---- weight gradient without any allocation (no counterpart in the reference):
+// for callers that cannot call cudaMalloc -- code under CUDA-graph capture, tight serving loops, harnesses
+// that forbid it.  The partial sums of the two-pass reduction live in a file-scope device array of a fixed maximum
+// size; every GPU that loads the library holds these 10 MiB until the process exits.
+//
+// g_wgrad_scratch, named in HOST code, is a host-side stand-in and not a device address: the kernels get the address
+// cudaGetSymbolAddress returns for the CURRENT device, resolved once per device below.
+//
+// Every call on a device shares the array.  Nothing in it has to start at zero: k_train_wgrad_partial writes every
+// partial sum k_train_wgrad_reduce reads (all z < Z, co < Cout, ci < Cin, nine taps; the bias partials whenever db is
+// given) before the reduction of the SAME call reads it, in stream order, so the contents an earlier call left behind
+// are never read.  Calls that overlap on the GPU (two streams, two host threads) race on the array: serialise them.
+constexpr int64_t WGRAD_STATIC_FLOATS = MZGO_TRAIN_WGRAD_STATIC_MAX_FLOATS;
+static __device__ __align__(256) float g_wgrad_scratch[WGRAD_STATIC_FLOATS];
+
+namespace {
+constexpr int MAX_DEVICES = 64;
+float* g_wgrad_scratch_ptr[MAX_DEVICES];   // device address of g_wgrad_scratch on device d (0 = not resolved yet)
+std::mutex g_wgrad_scratch_mu;
+}  // namespace
+
+extern "C" int64_t mzgo_train_wgrad_static_max_floats(void) { return WGRAD_STATIC_FLOATS; }
+
+extern "C" int mzgo_train_conv3x3_bwd_weight_static(const float* x, const float* dy, const float* y_gate, float* dw, float* db,
+                                                    int B, int Cin, int Cout, int n, void* stream) {
+    MZGO_CHECK_ARG(B >= 1 && Cin >= 1 && Cout >= 1, "bwd_weight_static: unsupported shape B=%d Cin=%d Cout=%d", B, Cin, Cout);
+    const int64_t need = mzgo_train_wgrad_scratch_floats(B, Cin, Cout);
+    MZGO_CHECK_ARG(need <= WGRAD_STATIC_FLOATS,
+                   "bwd_weight_static: B=%d Cin=%d Cout=%d needs %lld floats of scratch, the built-in array holds %lld "
+                   "(use mzgo_train_conv3x3_bwd_weight with a caller-owned buffer)",
+                   B, Cin, Cout, (long long)need, (long long)WGRAD_STATIC_FLOATS);
+    int dev = -1;
+    MZGO_CUDA(cudaGetDevice(&dev));
+    MZGO_CHECK_ARG(dev >= 0 && dev < MAX_DEVICES, "bwd_weight_static: device %d out of range", dev);
+    float* scratch;
+    {
+        std::lock_guard<std::mutex> lock(g_wgrad_scratch_mu);
+        if (!g_wgrad_scratch_ptr[dev]) {
+            float* p = nullptr;
+            MZGO_CUDA(cudaGetSymbolAddress((void**)&p, g_wgrad_scratch));     // with device `dev` current
+            MZGO_CHECK_ARG(p != nullptr, "bwd_weight_static: no device address for the scratch array on device %d", dev);
+            g_wgrad_scratch_ptr[dev] = p;
+        }
+        scratch = g_wgrad_scratch_ptr[dev];
+    }
+    return mzgo_train_conv3x3_bwd_weight(x, dy, y_gate, dw, db, scratch, B, Cin, Cout, n, stream);
 }
