@@ -374,7 +374,7 @@ k_tree_expand_backup(mzgo_tree_t t, mzgo_search_params_t p, const float* __restr
 // (the step itself lives in tree_step.cuh: the network kernel of nets_tc.cu runs the same code as a warp-group role)
 
 template <int TPG>
-__global__ void __launch_bounds__(STEP_THREADS, 8)
+__global__ void __launch_bounds__(STEP_THREADS, 7)
 k_tree_step(mzgo_tree_t t, mzgo_search_params_t p, const float* soft, const float* reward, const float* value,
             const uint32_t* __restrict__ choice_stream, int stride, int do_backup, int do_select, int early_loads) {
     constexpr int GPB = STEP_THREADS / TPG;     // games per block

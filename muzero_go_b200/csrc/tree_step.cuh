@@ -23,6 +23,7 @@ __device__ unsigned long long* g_tree_trace = nullptr;     // [G][16]
 
 constexpr int STEP_THREADS = 128;
 constexpr int STEP_EPT = 3;   // edges per thread: A <= 3 * TPG
+static_assert(STEP_EPT == 3, "the root-edge patch of tree_step_body selects among three register slots");
 
 __device__ __forceinline__ int npar_root_after(int root_visit0, int act) { return root_visit0 + (act >= 0 ? 1 : 0); }
 
@@ -40,49 +41,129 @@ struct StepShared {
     static constexpr int GPB = STEP_THREADS / TPG, WPG = TPG / 32, NW = STEP_EPT * WPG;
     uint32_t open[GPB][NW];      // ballot words per game (word w covers actions [32w, 32w+32))
     uint32_t live[GPB][WPG];
-    double qmin[GPB][WPG], qmax[GPB][WPG], best[GPB][WPG];
+    unsigned long long kmin[GPB][WPG], kmax[GPB][WPG], kbest[GPB][WPG];   // order-preserving keys of float64 values (dkey)
     int besta[GPB][WPG], bestn[GPB][WPG], bestc[GPB][WPG];
     float pri[GPB][STEP_EPT * TPG];   // self_play.py variant: masked child priors before the renormalisation
     float tot[GPB];
 };
 
-// One PUCT level (main.py:318-358) on register-resident edge data.  Returns 0: an unexpanded edge was drawn
-// (*out_a), 1: descend through *out_a into child *out_c (which has *out_n visits), 2: nothing selectable.
+// Order-preserving map of the non-NaN float64 values onto uint64: a < b <=> dkey(a) < dkey(b), -0.0 just below +0.0.
+// Minimum, maximum and argmax over a warp then take two 32-bit redux.sync operations (high word, then the low word
+// among the lanes that hold the winning high word) instead of five rounds of 64-bit shuffles and compares.
+__device__ __forceinline__ unsigned long long dkey(double x) {
+    const long long b = __double_as_longlong(x);
+    return (unsigned long long)(b ^ ((b >> 63) | (long long)0x8000000000000000ull));
+}
+__device__ __forceinline__ double dkey_inv(unsigned long long k) {
+    const long long b = (long long)k;
+    return __longlong_as_double(b < 0 ? (b ^ (long long)0x8000000000000000ull) : ~b);
+}
+__device__ __forceinline__ unsigned long long warp_max_u64(unsigned long long k) {
+    const uint32_t hi = (uint32_t)(k >> 32), lo = (uint32_t)k;
+    const uint32_t mh = __reduce_max_sync(FULL_MASK, hi);
+    const uint32_t ml = __reduce_max_sync(FULL_MASK, hi == mh ? lo : 0u);
+    return ((unsigned long long)mh << 32) | ml;
+}
+__device__ __forceinline__ unsigned long long warp_min_u64(unsigned long long k) {
+    const uint32_t hi = (uint32_t)(k >> 32), lo = (uint32_t)k;
+    const uint32_t mh = __reduce_min_sync(FULL_MASK, hi);
+    const uint32_t ml = __reduce_min_sync(FULL_MASK, hi == mh ? lo : 0xffffffffu);
+    return ((unsigned long long)mh << 32) | ml;
+}
+
+// position of the k-th (0-based) set bit of v; v has more than k set bits
+__device__ __forceinline__ int nth_set_bit(uint32_t v, int k) {
+    int pos = 0;
+#pragma unroll
+    for (int w = 16; w > 0; w >>= 1) {
+        const int c = __popc(v & ((1u << w) - 1u));
+        if (k >= c) { k -= c; pos += w; v >>= w; }
+    }
+    return pos;
+}
+
+// The terms of the PUCT score (main.py:328-358) of ONE edge that do not depend on the level's min-max normalisation:
+// q = value_sum / visits (0 for an unvisited edge) and u = c P sqrt(N) / (1 + n).  sq = sqrt(N) of the level.
+__device__ __forceinline__ void edge_terms(int nv, double cp, double vs, double sq, double* q, double* u) {
+    *q = 0.0;
+    if (nv > 0) *q = (fabs(vs) < 1e6) ? div_by_count(vs, nv) : __ddiv_rn(vs, (double)nv);
+    const double num = __dmul_rn(cp, sq);
+    *u = (num < 1e6) ? div_by_count(num, 1 + nv) : __ddiv_rn(num, (double)(1 + nv));
+}
+// sqrt(N) of a level whose parent has npar visits: main.py:354 / self_play.py:297-300
+__device__ __forceinline__ double level_sqrt(int npar, bool v1) { return __dsqrt_rn((double)(v1 ? max(1, npar) : npar + 1)); }
+
+template <int TPG>
+__device__ __forceinline__ void level_terms(const int (&nv)[STEP_EPT], const double (&cp)[STEP_EPT], const double (&vs)[STEP_EPT],
+                                            uint32_t pos, double sq, double (&q)[STEP_EPT], double (&u)[STEP_EPT]) {
+#pragma unroll
+    for (int e = 0; e < STEP_EPT; e++) {
+        q[e] = 0.0; u[e] = 0.0;
+        if ((pos >> e) & 1u) edge_terms(nv[e], cp[e], vs[e], sq, &q[e], &u[e]);
+    }
+}
+
+// One PUCT level (main.py:318-358) on register-resident edge data: visits nv, child links ch, the live set pos
+// (prior > 0) and the edge terms q / u of level_terms.  r = this step's random number (one unexpanded edge is drawn per
+// step at most).  Returns 0: an unexpanded edge was drawn (*out_a), 1: descend through *out_a into child *out_c (which
+// has *out_n visits), 2: nothing selectable.
+// TPG == 128: two block barriers per PUCT level (ballots + the warps' q range; the warps' best edges), one per level
+// that ends in a draw; no barrier between levels -- every scratch array is written before one barrier of a level and
+// read before the next one, so a warp that runs ahead into the next level cannot overwrite what another still reads.
 template <int TPG, int BAR>
 __device__ __forceinline__ int step_level(StepShared<TPG>& sh, int sub, int tid, const int (&nv)[STEP_EPT],
-                                          const double (&cp)[STEP_EPT], const double (&vs)[STEP_EPT],
-                                          const int (&ch)[STEP_EPT], uint32_t pos, int npar, bool v1, uint32_t rnd_or_ctr,
-                                          const uint32_t* choice_stream, size_t stream_off, const mzgo_search_params_t& p,
-                                          uint32_t g, uint32_t move_index, int* out_a, int* out_n, int* out_c) {
+                                          const double (&q)[STEP_EPT], const double (&u)[STEP_EPT],
+                                          const int (&ch)[STEP_EPT], uint32_t pos, uint32_t r, int* out_a, int* out_n,
+                                          int* out_c) {
     constexpr int WPG = TPG / 32, NW = STEP_EPT * WPG;
     const int wig = tid >> 5, lane = tid & 31;
+    uint32_t ow[NW];                             // TPG == 32: the ballots themselves; else filled from shared memory
+    uint32_t mine = 0u;
 #pragma unroll
     for (int e = 0; e < STEP_EPT; e++) {
         const bool opn = ((pos >> e) & 1u) && nv[e] == 0;
         const uint32_t b = __ballot_sync(FULL_MASK, opn);
-        if (lane == 0) sh.open[sub][e * WPG + wig] = b;
+        if (WPG == 1) ow[e] = b;
+        else if (lane == 0) sh.open[sub][e * WPG + wig] = b;
+        mine |= b;
     }
-    const uint32_t any_live = __ballot_sync(FULL_MASK, pos != 0u);
-    if (lane == 0) sh.live[sub][wig] = any_live;
-    step_sync<TPG, BAR>();
+    uint32_t all_live = __ballot_sync(FULL_MASK, pos != 0u);
+    // the range of q over the live edges (min-max normalisation set = prior > 0, main.py:328-339); a warp that holds
+    // an unexpanded edge knows that the level ends in a draw and skips it
+    unsigned long long kmin = dkey(INFINITY), kmax = dkey(-INFINITY);
+    if (mine == 0u) {
+        double qmin = INFINITY, qmax = -INFINITY;
+#pragma unroll
+        for (int e = 0; e < STEP_EPT; e++) {
+            if ((pos >> e) & 1u) { qmin = fmin(qmin, q[e]); qmax = fmax(qmax, q[e]); }
+        }
+        kmin = warp_min_u64(dkey(qmin));
+        kmax = warp_max_u64(dkey(qmax));
+    }
+    if (WPG > 1) {
+        if (lane == 0) { sh.live[sub][wig] = all_live; sh.kmin[sub][wig] = kmin; sh.kmax[sub][wig] = kmax; }
+        step_sync<TPG, BAR>();
+#pragma unroll
+        for (int w = 0; w < NW; w++) ow[w] = sh.open[sub][w];
+#pragma unroll
+        for (int w = 0; w < WPG; w++) {
+            all_live |= sh.live[sub][w];
+            kmin = min(kmin, sh.kmin[sub][w]);
+            kmax = max(kmax, sh.kmax[sub][w]);
+        }
+    }
     int n_open = 0;
-    uint32_t all_live = 0u;
 #pragma unroll
-    for (int w = 0; w < NW; w++) n_open += __popc(sh.open[sub][w]);
-#pragma unroll
-    for (int w = 0; w < WPG; w++) all_live |= sh.live[sub][w];
+    for (int w = 0; w < NW; w++) n_open += __popc(ow[w]);
     if (n_open > 0) {
         // random.choice(unexpanded), main.py:322-325
-        const uint32_t r = choice_stream ? choice_stream[stream_off + rnd_or_ctr]
-                                         : mzgo_rand_u32(p.seed, g, 0x20000u + move_index, rnd_or_ctr);
         int k = (int)(r % (uint32_t)n_open);
         int a_sel = -1;
 #pragma unroll
         for (int w = 0; w < NW; w++) {
-            const uint32_t b = sh.open[sub][w];
-            const int c = __popc(b);
+            const int c = __popc(ow[w]);
             if (a_sel < 0) {
-                if (k < c) a_sel = w * 32 + (int)__fns(b, 0, k + 1);
+                if (k < c) a_sel = w * 32 + nth_set_bit(ow[w], k);
                 else k -= c;
             }
         }
@@ -91,27 +172,7 @@ __device__ __forceinline__ int step_level(StepShared<TPG>& sh, int sub, int tid,
         return 0;
     }
     if (!all_live) return 2;                     // nothing selectable: simulation dropped / terminal leaf
-    // Q of every live edge, min-max normalisation set = prior > 0 (main.py:328-339)
-    double q[STEP_EPT];
-    double qmin = INFINITY, qmax = -INFINITY;
-#pragma unroll
-    for (int e = 0; e < STEP_EPT; e++) {
-        q[e] = 0.0;
-        if ((pos >> e) & 1u) {
-            if (nv[e] > 0) q[e] = (fabs(vs[e]) < 1e6) ? div_by_count(vs[e], nv[e]) : __ddiv_rn(vs[e], (double)nv[e]);
-            qmin = fmin(qmin, q[e]);
-            qmax = fmax(qmax, q[e]);
-        }
-    }
-    qmin = warp_min_d(qmin);
-    qmax = warp_max_d(qmax);
-    if (WPG > 1) {
-        if (lane == 0) { sh.qmin[sub][wig] = qmin; sh.qmax[sub][wig] = qmax; }
-        step_sync<TPG, BAR>();
-#pragma unroll
-        for (int w = 0; w < WPG; w++) { qmin = fmin(qmin, sh.qmin[sub][w]); qmax = fmax(qmax, sh.qmax[sub][w]); }
-    }
-    const double sq = __dsqrt_rn((double)(v1 ? max(1, npar) : npar + 1));   // main.py:354 / self_play.py:297-300
+    const double qmin = dkey_inv(kmin), qmax = dkey_inv(kmax);
     const bool norm = qmax > qmin;
     const double range = __dsub_rn(qmax, qmin);
     // 1/range once per level; a range outside the proven window of div_rn_with_rcp takes the generic division
@@ -124,31 +185,29 @@ __device__ __forceinline__ int step_level(StepShared<TPG>& sh, int sub, int tid,
         if ((pos >> e) & 1u) {
             const double dq = __dsub_rn(q[e], qmin);
             const double qn = norm ? (fast ? div_rn_with_rcp(dq, range, rrange) : __ddiv_rn(dq, range)) : q[e];
-            const double num = __dmul_rn(cp[e], sq);
-            const double u = (num < 1e6) ? div_by_count(num, 1 + nv[e]) : __ddiv_rn(num, (double)(1 + nv[e]));
-            const double score = __dadd_rn(qn, u);
+            const double score = __dadd_rn(qn, u[e]);
             if (score > best) { best = score; best_a = e * TPG + tid; best_n = nv[e]; best_c = ch[e]; }   // e ascending = action ascending
         }
     }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        const double ob = __shfl_xor_sync(FULL_MASK, best, o);
-        const int oa = __shfl_xor_sync(FULL_MASK, best_a, o);
-        const int on = __shfl_xor_sync(FULL_MASK, best_n, o);
-        const int oc = __shfl_xor_sync(FULL_MASK, best_c, o);
-        const bool take = (oa >= 0) && (best_a < 0 || ob > best || (ob == best && oa < best_a));
-        if (take) { best = ob; best_a = oa; best_n = on; best_c = oc; }
-    }
+    // argmax, ties to the lowest action: key 0 = no candidate (NaN and -inf scores never win, as in the reference's
+    // `score > best_score` with best_score = -inf); -0.0 + 0.0 = +0.0 makes equal scores equal keys
+    unsigned long long kb = best_a >= 0 ? dkey(__dadd_rn(best, 0.0)) : 0ull;
+    const unsigned long long kw = warp_max_u64(kb);
+    const uint32_t aw = __reduce_min_sync(FULL_MASK, (kb == kw && best_a >= 0) ? (uint32_t)best_a : 0xffffffffu);
+    best_a = (int)aw;                            // -1 when the warp has no candidate
+    best_n = __shfl_sync(FULL_MASK, best_n, (int)(aw & 31u));   // the winning edge e * TPG + wig * 32 + lane sits in lane aw % 32
+    best_c = __shfl_sync(FULL_MASK, best_c, (int)(aw & 31u));
+    kb = kw;
     if (WPG > 1) {
-        if (lane == 0) { sh.best[sub][wig] = best; sh.besta[sub][wig] = best_a; sh.bestn[sub][wig] = best_n; sh.bestc[sub][wig] = best_c; }
+        if (lane == 0) { sh.kbest[sub][wig] = kb; sh.besta[sub][wig] = best_a; sh.bestn[sub][wig] = best_n; sh.bestc[sub][wig] = best_c; }
         step_sync<TPG, BAR>();
-        best = sh.best[sub][0]; best_a = sh.besta[sub][0]; best_n = sh.bestn[sub][0]; best_c = sh.bestc[sub][0];
+        kb = sh.kbest[sub][0]; best_a = sh.besta[sub][0]; best_n = sh.bestn[sub][0]; best_c = sh.bestc[sub][0];
 #pragma unroll
         for (int w = 1; w < WPG; w++) {
-            const double ob = sh.best[sub][w];
+            const unsigned long long ok = sh.kbest[sub][w];
             const int oa = sh.besta[sub][w], on = sh.bestn[sub][w], oc = sh.bestc[sub][w];
-            const bool take = (oa >= 0) && (best_a < 0 || ob > best || (ob == best && oa < best_a));
-            if (take) { best = ob; best_a = oa; best_n = on; best_c = oc; }
+            const bool take = (oa >= 0) && (best_a < 0 || ok > kb || (ok == kb && oa < best_a));
+            if (take) { kb = ok; best_a = oa; best_n = on; best_c = oc; }
         }
     }
     if (best_a < 0) return 2;                    // only NaN / -inf scores: the reference falls out of the loop too
@@ -227,6 +286,29 @@ __device__ __forceinline__ void tree_step_body(const mzgo_tree_t& t, const mzgo_
     const double root_vsum0 = t.root_vsum[g];
     const int sims_done0 = t.sims_done[g];
     const long long depth_sum0 = t.depth_sum[g];
+
+    // ---------------------------------------------------------------- work that needs tree data only
+    // (behind the engine's network kernel it runs while that kernel drains, in front of the wait)
+    // the step's one random number: random.choice(unexpanded) ends the descent, main.py:322-325
+    const size_t stream_off = (size_t)g * stride;
+    uint32_t rnd = 0u;
+    if (do_select) rnd = choice_stream ? choice_stream[stream_off + ctr0]
+                                       : mzgo_rand_u32(p.seed, (uint32_t)(g + p.game_base), 0x20000u + move_index, ctr0);
+    // the root level's edge terms from the statistics as they are BEFORE this step's backup: the backup changes one
+    // root edge (the first edge of the path), whose terms are redone below from the patched statistics
+    int npar = root_visit0 + (act >= 0 ? 1 : 0);
+    double cp[STEP_EPT], q_r[STEP_EPT], u_r[STEP_EPT];
+    uint32_t pos = 0u;
+    double sq = 0.0;
+    if (do_select) {
+        sq = level_sqrt(npar, v1);
+#pragma unroll
+        for (int e = 0; e < STEP_EPT; e++) {
+            cp[e] = __dmul_rn(p.c_puct, pr_r[e]);    // root: float64 priors (main.py:276-282)
+            if (e * TPG + tid < A && pr_r[e] > 0.0) pos |= 1u << e;
+        }
+        level_terms<TPG>(nv_r, cp, vs_r, pos, sq, q_r, u_r);
+    }
 
     // ---------------------------------------------------------------- the network outputs of this game's leaf
     if (early_loads) wait_outputs();
@@ -316,11 +398,21 @@ __device__ __forceinline__ void tree_step_body(const mzgo_tree_t& t, const mzgo_
         // float64 addition the backup thread performs on the same operands) and the new child link
         const int a_first = pk0 & 511;           // stored paths always start with an edge of the root
         const double sv0 = (v1 && ((depth - 1) & 1)) ? -bv : bv;
+        if (do_select) {
+            const int e_first = a_first / TPG;
+            if (a_first - e_first * TPG == tid) {    // one thread of the game: its edge e_first is the path's root edge
+                const int nv1 = (e_first == 0 ? nv_r[0] : e_first == 1 ? nv_r[1] : nv_r[2]) + 1;
+                const double vs1 = __dadd_rn(e_first == 0 ? vs_r[0] : e_first == 1 ? vs_r[1] : vs_r[2], sv0);
+                const double cp1 = e_first == 0 ? cp[0] : e_first == 1 ? cp[1] : cp[2];
+                double q1 = 0.0, u1 = 0.0;
+                if ((pos >> e_first) & 1u) edge_terms(nv1, cp1, vs1, sq, &q1, &u1);
 #pragma unroll
-        for (int e = 0; e < STEP_EPT; e++) {
-            const int a = e * TPG + tid;
-            if (a == a_first) { nv_r[e] += 1; vs_r[e] = __dadd_rn(vs_r[e], sv0); }
-            if (par == 0 && a == act) ch_r[e] = nw;
+                for (int e = 0; e < STEP_EPT; e++)
+                    if (e == e_first) { nv_r[e] = nv1; q_r[e] = q1; u_r[e] = u1; }
+            }
+#pragma unroll
+            for (int e = 0; e < STEP_EPT; e++)
+                if (par == 0 && e * TPG + tid == act) ch_r[e] = nw;
         }
     }
     TSTAMP(3, ev_mine + __float_as_int(sf[0]));
@@ -334,33 +426,22 @@ __device__ __forceinline__ void tree_step_body(const mzgo_tree_t& t, const mzgo_
         return;
     }
     int node = 0, depth = 1;
-    int npar = root_visit0 + (act >= 0 ? 1 : 0);
     int sel_parent = -1, sel_action = -1;
-    const size_t stream_off = (size_t)g * stride;
-    // The level loop works on ONE set of register arrays (nv_r / vs_r / ch_r / cp): they hold the prefetched and
+    // The level loop works on ONE set of register arrays (nv_r / ch_r / q_r / u_r): they hold the prefetched and
     // patched root level on entry and are reloaded for every level below, so there is a single copy of the
     // level code (the kernel is instruction-cache sensitive).
-    double cp[STEP_EPT];
-    uint32_t pos = 0u;
-#pragma unroll
-    for (int e = 0; e < STEP_EPT; e++) {
-        cp[e] = __dmul_rn(p.c_puct, pr_r[e]);    // root: float64 priors (main.py:276-282)
-        if (e * TPG + tid < A && pr_r[e] > 0.0) pos |= 1u << e;
-    }
     while (true) {
         int oa = -1, on = 0, oc = -1;
-        const int rc = step_level<TPG, BAR>(sh, sub, tid, nv_r, cp, vs_r, ch_r, pos, npar, v1, ctr0, choice_stream, stream_off, p,
-                                       (uint32_t)(g + p.game_base), move_index, &oa, &on, &oc);
+        const int rc = step_level<TPG, BAR>(sh, sub, tid, nv_r, q_r, u_r, ch_r, pos, rnd, &oa, &on, &oc);
         TSTAMP(min(5 + 2 * (depth - 1), 13), rc + oa);
         if (rc == 0) { sel_parent = node; sel_action = oa; break; }
         if (rc == 2 || oc <= 0) break;           // terminal leaf / dropped simulation (node keeps the leaf)
         MZGO_DCHECK(oa >= 0 && oa < A && oc < M && oc < (act >= 0 ? nw + 1 : nn0));
         if (tid == 0 && depth <= A) path[depth - 1] = node * 512 + oa;
         node = oc; npar = on; depth++;
-        step_sync<TPG, BAR>();                        // shared scratch is reused by the next level
         const size_t base = ((size_t)g * M + node) * A;
         float prf[STEP_EPT];
-        // all loads of the level first, so that they are in flight together
+        // all loads of the level first, so that they are in flight together (and the level's sqrt under them)
 #pragma unroll
         for (int e = 0; e < STEP_EPT; e++) {
             const int a = e * TPG + tid;
@@ -372,6 +453,7 @@ __device__ __forceinline__ void tree_step_body(const mzgo_tree_t& t, const mzgo_
                 ch_r[e] = (int)t.child[base + a];
             }
         }
+        sq = level_sqrt(npar, v1);
         TSTAMP(min(6 + 2 * (depth - 2), 14), nv_r[0] + ch_r[STEP_EPT - 1] + __float_as_int(prf[0]));
         pos = 0u;
 #pragma unroll
@@ -379,6 +461,7 @@ __device__ __forceinline__ void tree_step_body(const mzgo_tree_t& t, const mzgo_
             cp[e] = (double)__fmul_rn((float)p.c_puct, prf[e]);   // c*P rounds in float32 (NEP 50)
             if (prf[e] > 0.f) pos |= 1u << e;
         }
+        level_terms<TPG>(nv_r, cp, vs_r, pos, sq, q_r, u_r);
     }
     if (tid == 0) {
         const int nn = act >= 0 ? nw + 1 : nn0;
