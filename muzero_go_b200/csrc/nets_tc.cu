@@ -894,16 +894,23 @@ k_tc_conv(const __grid_constant__ TcArgs a) {
         const int g_lo = rg.lo, g_hi = rg.hi;
         const int do_select = a.tree_mode == 1;
         const int sub128 = threadIdx.x >> 7;
+        const bool v1 = a.sp.variant == MZGO_VARIANT_SELFPLAY;     // a quarter of the step's code belongs to this variant
         if (a.tree.A <= STEP_EPT * 32) {
             StepShared<32>* sh = reinterpret_cast<StepShared<32>*>(sA) + sub128;      // a warp per game
-            for (int g = g_lo + warp; g < g_hi; g += TC_THREADS / 32)
-                tree_step_body<32, 2, false>(a.tree, a.sp, a.policy, a.reward, a.value, a.choice_stream, a.choice_stride, 1, do_select,
-                                      *sh, warp & 3, lane, g, [] {});
+            for (int g = g_lo + warp; g < g_hi; g += TC_THREADS / 32) {
+                if (v1) tree_step_body<32, 2, false, true>(a.tree, a.sp, a.policy, a.reward, a.value, a.choice_stream, a.choice_stride, 1,
+                                                           do_select, *sh, warp & 3, lane, g, [] {});
+                else tree_step_body<32, 2, false, false>(a.tree, a.sp, a.policy, a.reward, a.value, a.choice_stream, a.choice_stride, 1,
+                                                         do_select, *sh, warp & 3, lane, g, [] {});
+            }
         } else {
             StepShared<128>* sh = reinterpret_cast<StepShared<128>*>(sA) + sub128;    // 128 threads per game
-            for (int g = g_lo + sub128; g < g_hi; g += TC_THREADS / 128)
-                tree_step_body<128, 2, false>(a.tree, a.sp, a.policy, a.reward, a.value, a.choice_stream, a.choice_stride, 1, do_select,
-                                       *sh, 0, threadIdx.x & 127, g, [] {});
+            for (int g = g_lo + sub128; g < g_hi; g += TC_THREADS / 128) {
+                if (v1) tree_step_body<128, 2, false, true>(a.tree, a.sp, a.policy, a.reward, a.value, a.choice_stream, a.choice_stride, 1,
+                                                            do_select, *sh, 0, threadIdx.x & 127, g, [] {});
+                else tree_step_body<128, 2, false, false>(a.tree, a.sp, a.policy, a.reward, a.value, a.choice_stream, a.choice_stride, 1,
+                                                          do_select, *sh, 0, threadIdx.x & 127, g, [] {});
+            }
         }
         if (threadIdx.x == 0) tc_stamp(a, 31);
     }

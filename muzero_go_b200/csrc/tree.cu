@@ -376,7 +376,7 @@ k_tree_expand_backup(mzgo_tree_t t, mzgo_search_params_t p, const float* __restr
 // EARLY: behind the engine's own network kernel (see round trip 1 above; also the edge terms of every level are
 // computed as soon as its statistics arrive, which measures faster at 19x19, while the lazy form -- only on levels
 // that do not end in a draw -- is the faster one in the tree phase of the 9x9 network kernel)
-template <int TPG, bool EARLY>
+template <int TPG, bool EARLY, bool V1>
 __global__ void __launch_bounds__(STEP_THREADS, 7)
 k_tree_step(mzgo_tree_t t, mzgo_search_params_t p, const float* soft, const float* reward, const float* value,
             const uint32_t* __restrict__ choice_stream, int stride, int do_backup, int do_select) {
@@ -391,7 +391,7 @@ k_tree_step(mzgo_tree_t t, mzgo_search_params_t p, const float* soft, const floa
     if (g >= t.G) { griddep_wait(); return; }    // TPG == 128: the whole block; TPG == 32: whole warps
     // the grid-dependency wait (PDL, common.cuh) sits INSIDE the step, in front of the first read of what the kernel
     // before this one wrote (the network outputs): the tree data is fetched while that kernel drains
-    tree_step_body<TPG, 0, EARLY>(t, p, soft, reward, value, choice_stream, stride, do_backup, do_select, sh, sub, tid, g,
+    tree_step_body<TPG, 0, EARLY, V1>(t, p, soft, reward, value, choice_stream, stride, do_backup, do_select, sh, sub, tid, g,
                                   [] { griddep_wait(); });
 }
 
@@ -622,15 +622,19 @@ int mzgo_tree_step_impl(const mzgo_tree_t* tree, const mzgo_search_params_t* p, 
     MZGO_CHECK_ARG(p && (!do_backup || (soft && reward && value)), "NULL argument");
     if (tree->G == 0) return MZGO_OK;
     const dim3 block(STEP_THREADS);
-    if (tree->A <= STEP_EPT * 32) {
-        const dim3 grid(ceil_div(tree->G, STEP_THREADS / 32));
-        if (early) MZGO_CUDA(mzgo_launch_pdl(k_tree_step<32, true>, grid, block, 0, st, *tree, *p, soft, reward, value, choice_stream, stride, do_backup, do_select));
-        else MZGO_CUDA(mzgo_launch_pdl(k_tree_step<32, false>, grid, block, 0, st, *tree, *p, soft, reward, value, choice_stream, stride, do_backup, do_select));
+    const bool small = tree->A <= STEP_EPT * 32, v1 = p->variant == MZGO_VARIANT_SELFPLAY;
+    const dim3 grid(small ? ceil_div(tree->G, STEP_THREADS / 32) : tree->G);
+#define MZGO_STEP_LAUNCH(TPG, E, V)                                                                                          \
+    MZGO_CUDA(mzgo_launch_pdl(k_tree_step<TPG, E, V>, grid, block, 0, st, *tree, *p, soft, reward, value, choice_stream, stride, \
+                              do_backup, do_select))
+    if (small) {
+        if (early) { if (v1) MZGO_STEP_LAUNCH(32, true, true); else MZGO_STEP_LAUNCH(32, true, false); }
+        else { if (v1) MZGO_STEP_LAUNCH(32, false, true); else MZGO_STEP_LAUNCH(32, false, false); }
     } else {
-        const dim3 grid(tree->G);
-        if (early) MZGO_CUDA(mzgo_launch_pdl(k_tree_step<128, true>, grid, block, 0, st, *tree, *p, soft, reward, value, choice_stream, stride, do_backup, do_select));
-        else MZGO_CUDA(mzgo_launch_pdl(k_tree_step<128, false>, grid, block, 0, st, *tree, *p, soft, reward, value, choice_stream, stride, do_backup, do_select));
+        if (early) { if (v1) MZGO_STEP_LAUNCH(128, true, true); else MZGO_STEP_LAUNCH(128, true, false); }
+        else { if (v1) MZGO_STEP_LAUNCH(128, false, true); else MZGO_STEP_LAUNCH(128, false, false); }
     }
+#undef MZGO_STEP_LAUNCH
     mzgo_count_launch();
     MZGO_LAUNCH_CHECK();
     return MZGO_OK;

@@ -107,9 +107,13 @@ __device__ __forceinline__ double div_rn_with_rcp(double a, double b, double y) 
 constexpr int RCP_TABLE = 1024;
 __device__ double g_rcp_table[RCP_TABLE];
 
+// The generic IEEE division, out of line: the tree kernels reach it only outside the proven window of
+// div_rn_with_rcp, and inlined at every site it was a sixth of their code (they are instruction-cache sensitive).
+__device__ __noinline__ double ddiv_generic(double a, double b) { return __ddiv_rn(a, b); }
+
 __device__ __forceinline__ double div_by_count(double a, int d) {
     if (d < RCP_TABLE) return div_rn_with_rcp(a, (double)d, __ldg(&g_rcp_table[d]));
-    return __ddiv_rn(a, (double)d);
+    return ddiv_generic(a, (double)d);
 }
 
 // Fills this translation unit's reciprocal table once per device and host thread.

@@ -86,9 +86,9 @@ __device__ __forceinline__ int nth_set_bit(uint32_t v, int k) {
 // q = value_sum / visits (0 for an unvisited edge) and u = c P sqrt(N) / (1 + n).  sq = sqrt(N) of the level.
 __device__ __forceinline__ void edge_terms(int nv, double cp, double vs, double sq, double* q, double* u) {
     *q = 0.0;
-    if (nv > 0) *q = (fabs(vs) < 1e6) ? div_by_count(vs, nv) : __ddiv_rn(vs, (double)nv);
+    if (nv > 0) *q = (fabs(vs) < 1e6) ? div_by_count(vs, nv) : ddiv_generic(vs, (double)nv);
     const double num = __dmul_rn(cp, sq);
-    *u = (num < 1e6) ? div_by_count(num, 1 + nv) : __ddiv_rn(num, (double)(1 + nv));
+    *u = (num < 1e6) ? div_by_count(num, 1 + nv) : ddiv_generic(num, (double)(1 + nv));
 }
 // sqrt(N) of a level whose parent has npar visits: main.py:354 / self_play.py:297-300
 __device__ __forceinline__ double level_sqrt(int npar, bool v1) { return __dsqrt_rn((double)(v1 ? max(1, npar) : npar + 1)); }
@@ -162,17 +162,18 @@ __device__ __forceinline__ int step_level(StepShared<TPG>& sh, int sub, int tid,
     if (n_open > 0) {
         // random.choice(unexpanded), main.py:322-325
         int k = (int)(r % (uint32_t)n_open);
-        int a_sel = -1;
+        int w_sel = -1;
+        uint32_t word = 0u;
 #pragma unroll
         for (int w = 0; w < NW; w++) {
             const int c = __popc(ow[w]);
-            if (a_sel < 0) {
-                if (k < c) a_sel = w * 32 + nth_set_bit(ow[w], k);
+            if (w_sel < 0) {
+                if (k < c) { w_sel = w; word = ow[w]; }
                 else k -= c;
             }
         }
         // word w = e * WPG + wig covers the edges e * TPG + wig * 32 + [0, 32): the same numbering as the action index
-        *out_a = a_sel;
+        *out_a = w_sel * 32 + nth_set_bit(word, k);
         return 0;
     }
     if (!all_live) return 2;                     // nothing selectable: simulation dropped / terminal leaf
@@ -188,7 +189,7 @@ __device__ __forceinline__ int step_level(StepShared<TPG>& sh, int sub, int tid,
     for (int e = 0; e < STEP_EPT; e++) {
         if ((pos >> e) & 1u) {
             const double dq = __dsub_rn(q[e], qmin);
-            const double qn = norm ? (fast ? div_rn_with_rcp(dq, range, rrange) : __ddiv_rn(dq, range)) : q[e];
+            const double qn = norm ? (fast ? div_rn_with_rcp(dq, range, rrange) : ddiv_generic(dq, range)) : q[e];
             const double score = __dadd_rn(qn, u[e]);
             if (score > best) { best = score; best_a = e * TPG + tid; best_n = nv[e]; best_c = ch[e]; }   // e ascending = action ascending
         }
@@ -225,13 +226,13 @@ __device__ __forceinline__ int step_level(StepShared<TPG>& sh, int sub, int tid,
 // wait_outputs() returns once soft / reward / value of game g are readable (a no-op in the stand-alone kernel;
 // in the network kernel another warp of the CTA produces them, hence the ld.global.cg reads).  Everything
 // that does not depend on the network outputs is loaded BEFORE the wait.
-template <int TPG, int BAR, bool EARLY, class Wait>
+template <int TPG, int BAR, bool EARLY, bool V1, class Wait>
 __device__ __forceinline__ void tree_step_body(const mzgo_tree_t& t, const mzgo_search_params_t& p, const float* soft,
                                                const float* reward, const float* value, const uint32_t* choice_stream,
                                                int stride, int do_backup, int do_select, StepShared<TPG>& sh, int sub,
                                                int tid, int g, Wait wait_outputs) {
     constexpr bool early_loads = EARLY;
-    const bool v1 = p.variant == MZGO_VARIANT_SELFPLAY;
+    constexpr bool v1 = V1;                      // p.variant == MZGO_VARIANT_SELFPLAY, resolved by the caller (the variant's code is a quarter of the step)
     const int A = t.A, M = t.M;
     int* path = reinterpret_cast<int*>(t.prior + (size_t)g * M * A);   // scratch row of the root (its priors are float64, elsewhere)
     const size_t rbase = (size_t)g * M * A;      // edges of the root

@@ -897,12 +897,12 @@ k_tc_conv(const __grid_constant__ TcArgs a) {
         if (a.tree.A <= STEP_EPT * 32) {
             StepShared<32>* sh = reinterpret_cast<StepShared<32>*>(sA) + sub128;      // a warp per game
             for (int g = g_lo + warp; g < g_hi; g += TC_THREADS / 32)
-                tree_step_body<32, 2>(a.tree, a.sp, a.policy, a.reward, a.value, a.choice_stream, a.choice_stride, 1, do_select,
+                tree_step_body<32, 2, false>(a.tree, a.sp, a.policy, a.reward, a.value, a.choice_stream, a.choice_stride, 1, do_select,
                                       *sh, warp & 3, lane, g, [] {});
         } else {
             StepShared<128>* sh = reinterpret_cast<StepShared<128>*>(sA) + sub128;    // 128 threads per game
             for (int g = g_lo + sub128; g < g_hi; g += TC_THREADS / 128)
-                tree_step_body<128, 2>(a.tree, a.sp, a.policy, a.reward, a.value, a.choice_stream, a.choice_stride, 1, do_select,
+                tree_step_body<128, 2, false>(a.tree, a.sp, a.policy, a.reward, a.value, a.choice_stream, a.choice_stride, 1, do_select,
                                        *sh, 0, threadIdx.x & 127, g, [] {});
         }
         if (threadIdx.x == 0) tc_stamp(a, 31);

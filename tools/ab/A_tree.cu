@@ -373,10 +373,13 @@ k_tree_expand_backup(mzgo_tree_t t, mzgo_search_params_t p, const float* __restr
 //   4. one batch per level below the root (visits, priors, value sums and child links together).
 // (the step itself lives in tree_step.cuh: the network kernel of nets_tc.cu runs the same code as a warp-group role)
 
-template <int TPG>
+// EARLY: behind the engine's own network kernel (see round trip 1 above; also the edge terms of every level are
+// computed as soon as its statistics arrive, which measures faster at 19x19, while the lazy form -- only on levels
+// that do not end in a draw -- is the faster one in the tree phase of the 9x9 network kernel)
+template <int TPG, bool EARLY>
 __global__ void __launch_bounds__(STEP_THREADS, 7)
 k_tree_step(mzgo_tree_t t, mzgo_search_params_t p, const float* soft, const float* reward, const float* value,
-            const uint32_t* __restrict__ choice_stream, int stride, int do_backup, int do_select, int early_loads) {
+            const uint32_t* __restrict__ choice_stream, int stride, int do_backup, int do_select) {
     constexpr int GPB = STEP_THREADS / TPG;     // games per block
     __shared__ StepShared<TPG> sh;
     const int sub = threadIdx.x / TPG, tid = threadIdx.x % TPG;
@@ -388,8 +391,8 @@ k_tree_step(mzgo_tree_t t, mzgo_search_params_t p, const float* soft, const floa
     if (g >= t.G) { griddep_wait(); return; }    // TPG == 128: the whole block; TPG == 32: whole warps
     // the grid-dependency wait (PDL, common.cuh) sits INSIDE the step, in front of the first read of what the kernel
     // before this one wrote (the network outputs): the tree data is fetched while that kernel drains
-    tree_step_body<TPG, 0>(t, p, soft, reward, value, choice_stream, stride, do_backup, do_select, sh, sub, tid, g,
-                           [] { griddep_wait(); }, early_loads != 0);
+    tree_step_body<TPG, 0, EARLY>(t, p, soft, reward, value, choice_stream, stride, do_backup, do_select, sh, sub, tid, g,
+                                  [] { griddep_wait(); });
 }
 
 // main.py:666-669
@@ -618,12 +621,16 @@ int mzgo_tree_step_impl(const mzgo_tree_t* tree, const mzgo_search_params_t* p, 
     if (int e = ensure_rcp_table()) return e;
     MZGO_CHECK_ARG(p && (!do_backup || (soft && reward && value)), "NULL argument");
     if (tree->G == 0) return MZGO_OK;
-    if (tree->A <= STEP_EPT * 32)
-        MZGO_CUDA(mzgo_launch_pdl(k_tree_step<32>, dim3(ceil_div(tree->G, STEP_THREADS / 32)), dim3(STEP_THREADS), 0, st, *tree, *p,
-                                  soft, reward, value, choice_stream, stride, do_backup, do_select, early));
-    else
-        MZGO_CUDA(mzgo_launch_pdl(k_tree_step<128>, dim3(tree->G), dim3(STEP_THREADS), 0, st, *tree, *p, soft, reward, value,
-                                  choice_stream, stride, do_backup, do_select, early));
+    const dim3 block(STEP_THREADS);
+    if (tree->A <= STEP_EPT * 32) {
+        const dim3 grid(ceil_div(tree->G, STEP_THREADS / 32));
+        if (early) MZGO_CUDA(mzgo_launch_pdl(k_tree_step<32, true>, grid, block, 0, st, *tree, *p, soft, reward, value, choice_stream, stride, do_backup, do_select));
+        else MZGO_CUDA(mzgo_launch_pdl(k_tree_step<32, false>, grid, block, 0, st, *tree, *p, soft, reward, value, choice_stream, stride, do_backup, do_select));
+    } else {
+        const dim3 grid(tree->G);
+        if (early) MZGO_CUDA(mzgo_launch_pdl(k_tree_step<128, true>, grid, block, 0, st, *tree, *p, soft, reward, value, choice_stream, stride, do_backup, do_select));
+        else MZGO_CUDA(mzgo_launch_pdl(k_tree_step<128, false>, grid, block, 0, st, *tree, *p, soft, reward, value, choice_stream, stride, do_backup, do_select));
+    }
     mzgo_count_launch();
     MZGO_LAUNCH_CHECK();
     return MZGO_OK;

@@ -103,16 +103,19 @@ __device__ __forceinline__ void level_terms(const int (&nv)[STEP_EPT], const dou
     }
 }
 
-// One PUCT level (main.py:318-358) on register-resident edge data: visits nv, child links ch, the live set pos
-// (prior > 0) and the edge terms q / u of level_terms.  r = this step's random number (one unexpanded edge is drawn per
-// step at most).  Returns 0: an unexpanded edge was drawn (*out_a), 1: descend through *out_a into child *out_c (which
+// One PUCT level (main.py:318-358) on register-resident edge data: visits nv, value sums vs, c * prior cp, child links
+// ch, the live set pos (prior > 0), sq = sqrt(N).  The edge terms q / u (level_terms) are computed here unless the
+// caller has them (have_terms, uniform for the warp: the root level, in front of the wait) -- and only by warps that
+// hold no unexpanded edge, i.e. not on a level that ends in a draw.  r = this step's random number (one unexpanded
+// edge is drawn per step at most).  Returns 0: an unexpanded edge was drawn (*out_a), 1: descend through *out_a into child *out_c (which
 // has *out_n visits), 2: nothing selectable.
 // TPG == 128: two block barriers per PUCT level (ballots + the warps' q range; the warps' best edges), one per level
 // that ends in a draw; no barrier between levels -- every scratch array is written before one barrier of a level and
 // read before the next one, so a warp that runs ahead into the next level cannot overwrite what another still reads.
 template <int TPG, int BAR>
 __device__ __forceinline__ int step_level(StepShared<TPG>& sh, int sub, int tid, const int (&nv)[STEP_EPT],
-                                          const double (&q)[STEP_EPT], const double (&u)[STEP_EPT],
+                                          const double (&cp)[STEP_EPT], const double (&vs)[STEP_EPT], double sq,
+                                          bool have_terms, double (&q)[STEP_EPT], double (&u)[STEP_EPT],
                                           const int (&ch)[STEP_EPT], uint32_t pos, uint32_t r, int* out_a, int* out_n,
                                           int* out_c) {
     constexpr int WPG = TPG / 32, NW = STEP_EPT * WPG;
@@ -132,6 +135,7 @@ __device__ __forceinline__ int step_level(StepShared<TPG>& sh, int sub, int tid,
     // an unexpanded edge knows that the level ends in a draw and skips it
     unsigned long long kmin = dkey(INFINITY), kmax = dkey(-INFINITY);
     if (mine == 0u) {
+        if (!have_terms) level_terms<TPG>(nv, cp, vs, pos, sq, q, u);
         double qmin = INFINITY, qmax = -INFINITY;
 #pragma unroll
         for (int e = 0; e < STEP_EPT; e++) {
@@ -221,11 +225,12 @@ __device__ __forceinline__ int step_level(StepShared<TPG>& sh, int sub, int tid,
 // wait_outputs() returns once soft / reward / value of game g are readable (a no-op in the stand-alone kernel;
 // in the network kernel another warp of the CTA produces them, hence the ld.global.cg reads).  Everything
 // that does not depend on the network outputs is loaded BEFORE the wait.
-template <int TPG, int BAR, class Wait>
+template <int TPG, int BAR, bool EARLY, class Wait>
 __device__ __forceinline__ void tree_step_body(const mzgo_tree_t& t, const mzgo_search_params_t& p, const float* soft,
                                                const float* reward, const float* value, const uint32_t* choice_stream,
                                                int stride, int do_backup, int do_select, StepShared<TPG>& sh, int sub,
-                                               int tid, int g, Wait wait_outputs, bool early_loads = false) {
+                                               int tid, int g, Wait wait_outputs) {
+    constexpr bool early_loads = EARLY;
     const bool v1 = p.variant == MZGO_VARIANT_SELFPLAY;
     const int A = t.A, M = t.M;
     int* path = reinterpret_cast<int*>(t.prior + (size_t)g * M * A);   // scratch row of the root (its priors are float64, elsewhere)
@@ -294,8 +299,9 @@ __device__ __forceinline__ void tree_step_body(const mzgo_tree_t& t, const mzgo_
     uint32_t rnd = 0u;
     if (do_select) rnd = choice_stream ? choice_stream[stream_off + ctr0]
                                        : mzgo_rand_u32(p.seed, (uint32_t)(g + p.game_base), 0x20000u + move_index, ctr0);
-    // the root level's edge terms from the statistics as they are BEFORE this step's backup: the backup changes one
-    // root edge (the first edge of the path), whose terms are redone below from the patched statistics
+    // behind the wait shadow (early_loads) also the root level's edge terms, from the statistics as they are BEFORE this
+    // step's backup: the backup changes one root edge (the first edge of the path), whose terms are redone below from
+    // the patched statistics
     int npar = root_visit0 + (act >= 0 ? 1 : 0);
     double cp[STEP_EPT], q_r[STEP_EPT], u_r[STEP_EPT];
     uint32_t pos = 0u;
@@ -307,8 +313,35 @@ __device__ __forceinline__ void tree_step_body(const mzgo_tree_t& t, const mzgo_
             cp[e] = __dmul_rn(p.c_puct, pr_r[e]);    // root: float64 priors (main.py:276-282)
             if (e * TPG + tid < A && pr_r[e] > 0.0) pos |= 1u << e;
         }
-        level_terms<TPG>(nv_r, cp, vs_r, pos, sq, q_r, u_r);
+        if (early_loads) level_terms<TPG>(nv_r, cp, vs_r, pos, sq, q_r, u_r);   // else: by the level itself, if it needs them
     }
+
+    // The stores of expand + backup that need no network output: the new node's empty statistics, the visit counts
+    // along the path, the child / parent links and the per-game counters.  EARLY: issued here, in front of the wait
+    // (nobody reads or writes them while the network kernel runs); else as part of expand + backup below.
+    auto stores_without_outputs = [&]() {
+        if (act < 0) return;
+        const size_t nbase = ((size_t)g * M + nw) * A;
+#pragma unroll
+        for (int e = 0; e < STEP_EPT; e++) {
+            const int a = e * TPG + tid;
+            if (a < A) {
+                t.edge_visit[nbase + a] = 0;
+                t.edge_vsum[nbase + a] = 0.0;
+                t.child[nbase + a] = (int16_t)-1;
+            }
+        }
+        if (pk_mine >= 0) t.edge_visit[((size_t)g * M + (pk_mine >> 9)) * A + (pk_mine & 511)] = ev_mine + 1;
+        if (tid == 0) {
+            t.child[((size_t)g * M + par) * A + act] = (int16_t)nw;
+            t.parent[(size_t)g * M + nw] = par * 512 + act;
+            t.n_nodes[g] = nw + 1;
+            t.root_visit[g] = root_visit0 + 1;
+            t.sims_done[g] = sims_done0 + 1;
+            t.depth_sum[g] = depth_sum0 + depth_b;
+        }
+    };
+    if (EARLY) stores_without_outputs();
 
     // ---------------------------------------------------------------- the network outputs of this game's leaf
     if (early_loads) wait_outputs();
@@ -349,17 +382,14 @@ __device__ __forceinline__ void tree_step_body(const mzgo_tree_t& t, const mzgo_
                 float pr = mk[e] > 0.f ? sf[e] : 0.f;
                 if (v1) pr = renorm_child_prior(sh.pri[sub][a], sh.tot[sub], mk[e], a == A - 1, p.pass_epsilon, mask, A);
                 t.prior[nbase + a] = pr;
-                t.edge_visit[nbase + a] = 0;
-                t.edge_vsum[nbase + a] = 0.0;
-                t.child[nbase + a] = (int16_t)-1;
             }
         }
+        if (!EARLY) stores_without_outputs();
         // self_play.py:340-343: node i levels above the new leaf gets value * (-1)^i; edge d of the path holds the
         // statistics of the node at depth d + 1, i.e. i = depth - 1 - d, and the root has i = depth
         if (depth <= A) {
             if (pk_mine >= 0) {
                 const size_t e = ((size_t)g * M + (pk_mine >> 9)) * A + (pk_mine & 511);
-                t.edge_visit[e] = ev_mine + 1;
                 t.edge_vsum[e] = __dadd_rn(es_mine, (v1 && ((depth - 1 - tid) & 1)) ? -bv : bv);
             }
             for (int d = tid + TPG; d < depth; d += TPG) {
@@ -371,9 +401,6 @@ __device__ __forceinline__ void tree_step_body(const mzgo_tree_t& t, const mzgo_
             }
         }
         if (tid == 0) {
-            t.child[((size_t)g * M + par) * A + act] = (int16_t)nw;
-            t.parent[(size_t)g * M + nw] = par * 512 + act;
-            t.n_nodes[g] = nw + 1;
             if (depth > A) {                     // path longer than the scratch row: walk the parent links
                 int node = nw;
                 double sv = bv;
@@ -389,10 +416,7 @@ __device__ __forceinline__ void tree_step_body(const mzgo_tree_t& t, const mzgo_
                     node = pn;
                 }
             }
-            t.root_visit[g] = root_visit0 + 1;
             t.root_vsum[g] = __dadd_rn(root_vsum0, (v1 && (depth & 1)) ? -bv : bv);
-            t.sims_done[g] = sims_done0 + 1;
-            t.depth_sum[g] = depth_sum0 + depth;
         }
         // the root level fetched above predates this backup: patch the one root edge on the path (the same
         // float64 addition the backup thread performs on the same operands) and the new child link
@@ -405,10 +429,10 @@ __device__ __forceinline__ void tree_step_body(const mzgo_tree_t& t, const mzgo_
                 const double vs1 = __dadd_rn(e_first == 0 ? vs_r[0] : e_first == 1 ? vs_r[1] : vs_r[2], sv0);
                 const double cp1 = e_first == 0 ? cp[0] : e_first == 1 ? cp[1] : cp[2];
                 double q1 = 0.0, u1 = 0.0;
-                if ((pos >> e_first) & 1u) edge_terms(nv1, cp1, vs1, sq, &q1, &u1);
+                if (early_loads && ((pos >> e_first) & 1u)) edge_terms(nv1, cp1, vs1, sq, &q1, &u1);
 #pragma unroll
                 for (int e = 0; e < STEP_EPT; e++)
-                    if (e == e_first) { nv_r[e] = nv1; q_r[e] = q1; u_r[e] = u1; }
+                    if (e == e_first) { nv_r[e] = nv1; vs_r[e] = vs1; q_r[e] = q1; u_r[e] = u1; }
             }
 #pragma unroll
             for (int e = 0; e < STEP_EPT; e++)
@@ -432,7 +456,8 @@ __device__ __forceinline__ void tree_step_body(const mzgo_tree_t& t, const mzgo_
     // level code (the kernel is instruction-cache sensitive).
     while (true) {
         int oa = -1, on = 0, oc = -1;
-        const int rc = step_level<TPG, BAR>(sh, sub, tid, nv_r, q_r, u_r, ch_r, pos, rnd, &oa, &on, &oc);
+        const int rc = step_level<TPG, BAR>(sh, sub, tid, nv_r, cp, vs_r, sq, EARLY, q_r, u_r, ch_r, pos, rnd,
+                                            &oa, &on, &oc);
         TSTAMP(min(5 + 2 * (depth - 1), 13), rc + oa);
         if (rc == 0) { sel_parent = node; sel_action = oa; break; }
         if (rc == 2 || oc <= 0) break;           // terminal leaf / dropped simulation (node keeps the leaf)
@@ -461,7 +486,7 @@ __device__ __forceinline__ void tree_step_body(const mzgo_tree_t& t, const mzgo_
             cp[e] = (double)__fmul_rn((float)p.c_puct, prf[e]);   // c*P rounds in float32 (NEP 50)
             if (prf[e] > 0.f) pos |= 1u << e;
         }
-        level_terms<TPG>(nv_r, cp, vs_r, pos, sq, q_r, u_r);
+        if (EARLY) level_terms<TPG>(nv_r, cp, vs_r, pos, sq, q_r, u_r);
     }
     if (tid == 0) {
         const int nn = act >= 0 ? nw + 1 : nn0;
