@@ -369,7 +369,7 @@ int mzgo_train_conv3x3_bwd_weight_static(const float* x, const float* dy, const 
 /* Test / profiling hooks.  mzgo_debug_fastdiv_check: operand pairs on which the tree kernels' 5-operation
  * correctly rounded division differs from the generic IEEE division (must be 0; synchronous).
  * mzgo_debug_tc_trace: when buf != NULL every tensor-core conv launch stamps its role timeline into
- * buf[grid][32] (uint64 globaltimer values, tools/tc_trace.py). */
+ * buf[grid][64] (uint64 globaltimer values, tools/tc_trace.py). */
 long long mzgo_debug_fastdiv_check(unsigned long long seed, int blocks, long long per_thread);
 int mzgo_debug_tc_trace(void* buf /*device*/);
 

@@ -212,7 +212,7 @@ struct TcArgs {
     int want_softmax;
     int B;                       // items
     int n, ps, tiles_per_image, images_per_group, stages;
-    unsigned long long* trace;   // optional (tools/tc_trace.py): [grid][32] globaltimer stamps of the roles
+    unsigned long long* trace;   // optional (tools/tc_trace.py): [grid][64] globaltimer stamps of the roles
     // mzgo_net_recurrent_tree: items are the games' selected leaves (in_slot / action / out_slot = the tree's
     // leaf records), and once the CTA's roles are through, all of its threads run the tree step of the CTA's
     // games (expand + backup, and the next selection when tree_mode == 1): one launch per simulation
@@ -250,8 +250,8 @@ __device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 256;"
 __device__ __forceinline__ void tc_stamp(const TcArgs& a, int slot) {
     if (a.trace) {
         unsigned long long t;
-        asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
-        a.trace[(size_t)blockIdx.x * 32 + slot] = t;
+        asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)::"memory");     // (ordered against the barriers around it)
+        a.trace[(size_t)blockIdx.x * 64 + slot] = t;
     }
 }
 
@@ -466,6 +466,7 @@ __device__ __forceinline__ void tc_epilogue_role(const TcArgs& a, const TcCtx& c
         }
         tile_ctr += NT;
         if (warp == 2 && lane == 0 && it < 4) tc_stamp(a, 11 + 2 * it);
+        if (warp == 2 && lane == 0) tc_stamp(a, 56);                 // overwritten by every group: the last one stays
         it++;
         if (MODE != MODE_PLAIN) {
             __syncwarp();
@@ -611,6 +612,7 @@ __device__ __forceinline__ void tc_finaliser_role(const TcArgs& a, const TcCtx& 
         __syncwarp();
         if (lane == 0) mbar_arrive(cx.fin_empty + par);
         if (lane == 0 && it < 4) tc_stamp(a, 20 + it);
+        if (lane == 0) tc_stamp(a, 57);                              // the last group's stays
         it++;
     }
 }
@@ -658,6 +660,7 @@ __device__ __forceinline__ void tc_mma_group(const TcArgs& a, const TcMmaCtx& mx
     for (int h = 0; h < NH; h++) {
         mbar_wait(mx.a_full + h, it & 1);
         if (h == 0 && it < 4 && lane == 0) tc_stamp(a, 2 + 2 * it);
+        if (h == 0 && it < 12 && lane == 0) tc_stamp(a, 32 + 2 * it);      // slots 32..55: every group of a launch
         for (int tap = 0; tap < 9; tap++) {
             mbar_wait(mx.b_full + s, bph);
             tc_fence_after();
@@ -686,6 +689,7 @@ __device__ __forceinline__ void tc_mma_group(const TcArgs& a, const TcMmaCtx& mx
         for (int j = 0; j < NT; j++) umma_commit(mx.acc_full + ((tile_ctr + j) & (TC_SLOTS - 1)));
     }
     if (it < 4 && lane == 0) tc_stamp(a, 3 + 2 * it);
+    if (it < 12 && lane == 0) tc_stamp(a, 33 + 2 * it);
     __syncwarp();
     st.s = s;
     st.bph = bph;
@@ -919,6 +923,7 @@ k_tc_conv(const __grid_constant__ TcArgs a) {
     if (warp == 1) {
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, 512;" ::"r"(tmem_base) : "memory");
+        if (lane == 0) tc_stamp(a, 58);
     }
 }
 
@@ -1143,7 +1148,7 @@ int launch_tc_conv(TcArgs& a, int n, int B, cudaStream_t st) {
 }
 
 }  // namespace
-// Debug aid (tools/tc_trace.py): when set, every k_tc_conv launch stamps its role timeline into buf[grid][32].
+// Debug aid (tools/tc_trace.py): when set, every k_tc_conv launch stamps its role timeline into buf[grid][64].
 extern "C" int mzgo_debug_tc_trace(void* buf) {
     g_tc_trace = (unsigned long long*)buf;
     return MZGO_OK;

@@ -34,12 +34,12 @@ def main():
     for _ in range(3):
         group.run(1)
     torch.cuda.synchronize()
-    trace = torch.zeros(148 * 32, dtype=torch.int64, device=dev)
+    trace = torch.zeros(148 * 64, dtype=torch.int64, device=dev)
     lib.mzgo_debug_tc_trace(trace.data_ptr())
     group.run(1)
     torch.cuda.synchronize()
     lib.mzgo_debug_tc_trace(None)
-    t = trace.cpu().numpy().reshape(148, 32).astype(np.float64)
+    t = trace.cpu().numpy().reshape(148, 64).astype(np.float64)
     ok = t[:, 0] > 0
     t0 = t[ok, 0].min()
     roles = (t[ok, 30] - t0) / 1e3

@@ -33,7 +33,7 @@ for mixed in (False, True):
     e.tree.reset_roots(e.search, e.root_policy, e.boards, n, noise=None, move_index=7)
     p = e.search.to_struct()
     _lib.check(L.mzgo_tree_step(e.tree.desc, p, _lib.ptr(e.leaf_policy), _lib.ptr(e.leaf_reward), _lib.ptr(e.leaf_value), None, 0, 0, 1, s))
-    trace = torch.zeros(148 * 32, dtype=torch.int64, device=dev)
+    trace = torch.zeros(148 * 64, dtype=torch.int64, device=dev)
     for k in range(S):
         if k in (10, 30, 45):
             torch.cuda.synchronize()
@@ -44,7 +44,7 @@ for mixed in (False, True):
         if k in (10, 30, 45):
             torch.cuda.synchronize()
             L.mzgo_debug_tc_trace(None)
-            t = trace.cpu().numpy().reshape(148, 32).astype(np.float64)
+            t = trace.cpu().numpy().reshape(148, 64).astype(np.float64)
             t0 = t[:, 0].min()
             roles, done = (t[:, 30] - t0) / 1e3, (t[:, 31] - t0) / 1e3
             depth = e.tree.leaf_depth.cpu().numpy()

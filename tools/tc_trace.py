@@ -18,6 +18,12 @@ NAMES = {0: "entry", 1: "setup done", 2: "mma g0 start", 3: "mma g0 issued", 4: 
          13: "epi g1 done", 14: "epi g2 first acc", 15: "epi g2 done", 27: "fin g1 woke", 28: "fin g1 heads", 29: "fin g1 exps", 24: "fin g2 woke", 25: "fin g2 heads", 26: "fin g2 exps",
          18: "epi g2 acc in regs", 19: "epi g2 stored",
          20: "fin g0", 21: "fin g1", 22: "fin g2", 30: "exit"}
+for _g in range(12):            # every group of the launch (19x19: seven)
+    NAMES[32 + 2 * _g] = f"MMA group {_g} start"
+    NAMES[33 + 2 * _g] = f"MMA group {_g} issued"
+NAMES[56] = "epilogue of the last group done"
+NAMES[57] = "finaliser of the last group done"
+NAMES[58] = "TMEM released (leave)"
 
 
 def main():
@@ -56,12 +62,12 @@ def main():
     e1.record()
     torch.cuda.synchronize()
     print(f"n={n} leaves={B}: {e0.elapsed_time(e1) / 10 * 1e3:.1f} us per launch (no trace)")
-    trace = torch.zeros(148 * 32, dtype=torch.int64, device=dev)
+    trace = torch.zeros(148 * 64, dtype=torch.int64, device=dev)
     lib.mzgo_debug_tc_trace(trace.data_ptr())
     _lib.check(lib.mzgo_net_recurrent(*call))
     torch.cuda.synchronize()
     lib.mzgo_debug_tc_trace(None)
-    t = trace.cpu().numpy().reshape(148, 32).astype(np.float64)
+    t = trace.cpu().numpy().reshape(148, 64).astype(np.float64)
     t0 = t[:, 0][t[:, 0] > 0].min()
     print(f"{'event':18s} {'min':>8s} {'median':>8s} {'max':>8s}   (us after the first CTA entered; CTAs reporting)")
     for k in sorted(NAMES):
