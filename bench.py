@@ -286,8 +286,8 @@ def measure(args, wl, G, S, K, W, rank, world, dev, primary, positions="mixed"):
     # `streams` sets of search buffers are alive at once (waves on different streams overlap: one wave's tree step
     # under another wave's network kernel, muzero_go_b200.WaveGroup)
     streams = max(1, args.streams)
-    waves = streams
-    while streams * (G // waves) * per_game > 0.90 * free_b or G % waves:
+    waves = max(streams, (max(args.waves, 1) + streams - 1) // streams * streams)
+    while streams * (G // waves) * per_game > 0.92 * free_b or G % waves:
         waves += streams
     group = mz.WaveGroup(net, n, G, S, waves=waves, streams=streams, search=mz.SearchConfig(seed=1000, game_base=rank * G),
                          traj_capacity=2, restart_finished=True)
@@ -768,6 +768,9 @@ def main():
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--streams", type=int, default=1,
                     help="CUDA streams (sets of search buffers) the waves of games are spread over; 1 = one wave at a time")
+    ap.add_argument("--waves", type=int, default=0,
+                    help="split the games into at least this many waves that take turns on one set of search buffers "
+                         "(default: as few as the free HBM allows)")
     ap.add_argument("--games", type=int, default=0)
     ap.add_argument("--sims", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")

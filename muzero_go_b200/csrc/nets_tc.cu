@@ -53,7 +53,16 @@ constexpr int TC_SMEM_LIMIT = 232448;   // 227 KB
 enum { MODE_PLAIN = 0, MODE_HEADS = 1, MODE_DYN = 2 };
 unsigned long long* g_tc_trace = nullptr;
 
+// A latent slab in SHARED memory: [C/8][ps][8] bf16, position q = (n + 2) + r (n + 1) + c of pixel (r, c): rows of n
+// pixels and one zero (the right / left padding of neighbouring rows is the same position), n + 2 zero positions in
+// front (the top padding row and the left padding of row 0) and n + 3 behind -- every shifted view of the nine taps
+// of every accumulator tile stays inside the slab.
+// In GLOBAL memory (the latent arena, the activation buffers) only the positions [n + 1, n + 1 + n (n + 1)) are kept:
+// [C/8][psh][8], psh = n (n + 1), position q - (n + 1).  The zero positions in front of and behind them live in shared
+// memory alone (written once per launch, never overwritten by the bulk copies): 10 % less HBM per slot, which lets one
+// search hold all 2048 19x19 games of a GPU (160 GB of latents) instead of two waves of 1024.
 __host__ __device__ inline int tc_ps(int n) { return (n + 2) * (n + 1) + 2; }
+__host__ __device__ inline int tc_psh(int n) { return n * (n + 1); }
 __host__ __device__ inline int tc_tiles_per_image(int n) { return (n * (n + 1) + 127) / 128; }
 // A group (the images that share one pass over the weights) fills at most three of the four TMEM
 // accumulator slots: with a spare slot the MMAs of the next group start while the epilogue still holds
@@ -199,8 +208,8 @@ struct TcScalars {   // the scalar head parameters (main.py:93-94, :111-114), ho
 };
 
 struct TcArgs {
-    const __nv_bfloat16* in;     // input slabs: item i at in + in_slot(i) * (CIN/8)*ps*8
-    __nv_bfloat16* out;          // output slabs: item i at out + out_slot(i) * (COUT/8)*ps*8
+    const __nv_bfloat16* in;     // input slabs: item i at in + in_slot(i) * (CIN/8)*psh*8
+    __nv_bfloat16* out;          // output slabs: item i at out + out_slot(i) * (COUT/8)*psh*8
     const int32_t* in_slot;      // optional (identity when NULL)
     const int32_t* out_slot;     // optional (identity when NULL); < 0 skips the item
     const int32_t* action;       // MODE_DYN: table row; < 0 skips the item.  Otherwise optional gate.
@@ -211,7 +220,7 @@ struct TcArgs {
     float* policy;
     int want_softmax;
     int B;                       // items
-    int n, ps, tiles_per_image, images_per_group, stages;
+    int n, ps, psh, tiles_per_image, images_per_group, stages;      // ps / psh: positions of a slab in shared / global memory
     unsigned long long* trace;   // optional (tools/tc_trace.py): [grid][64] globaltimer stamps of the roles
     // mzgo_net_recurrent_tree: items are the games' selected leaves (in_slot / action / out_slot = the tree's
     // leaf records), and once the CTA's roles are through, all of its threads run the tree step of the CTA's
@@ -350,7 +359,7 @@ __device__ __forceinline__ void tc_epilogue_role(const TcArgs& a, const TcCtx& c
     constexpr int KC_OUT = COUT / 8;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int wq = warp & 3, pi = (warp - 2) >> 2;
-    const int n = a.n, ps = a.ps, q0 = n + 2;
+    const int n = a.n, psh = a.psh, q0 = n + 2;
     const int tpi = a.tiles_per_image;
     const TcRange rg = tc_range(a);
     // geometry of this thread's row in tile tt of an image (tt < 3 for n <= 19): r | c << 5 | cls << 10 | valid << 14
@@ -414,12 +423,12 @@ __device__ __forceinline__ void tc_epilogue_role(const TcArgs& a, const TcCtx& c
             const uint32_t g = tt == 0 ? geo[0] : (tt == 1 ? geo[1] : geo[2]);
             const int r = g & 31, cc = (g >> 5) & 31, cls = (g >> 10) & 15;
             const bool valid = (g >> 14) & 1u;
-            const int q = q0 + tt * 128 + wq * 32 + lane;
-            const bool store_ok = q < ps;
+            const int q = tt * 128 + wq * 32 + lane + 1;          // position in the global slab: shared position - (n + 1)
+            const bool store_ok = q < psh;
             const float* tb = (MODE == MODE_DYN) ? s_tbl + (img * 9 + cls) * COUT : s_tbl;
             const int oslot = __shfl_sync(FULL_MASK, my_osl, img);
             MZGO_DCHECK(oslot >= 0 && img < tc_group_cnt(a, rg.lo, rg.hi, gi) && slot < TC_SLOTS);
-            uint4* dst = reinterpret_cast<uint4*>(a.out) + (size_t)oslot * KC_OUT * ps + q;
+            uint4* dst = reinterpret_cast<uint4*>(a.out) + (size_t)oslot * KC_OUT * psh + q;
             float pol = 0.f, val = 0.f, rew = 0.f;
             const uint32_t keep = valid ? 0xffffffffu : 0u;
             float4 nb0 = *reinterpret_cast<const float4*>(tb), nb1 = *reinterpret_cast<const float4*>(tb + 4);
@@ -453,7 +462,7 @@ __device__ __forceinline__ void tc_epilogue_role(const TcArgs& a, const TcCtx& c
                 } else {
                     st_global_v4_hint_if(dst, w, pol_stream, store_ok);
                 }
-                dst += ps;
+                dst += psh;
                 asm volatile("" ::: "memory");
             }
             if (warp == 2 && lane == 0 && it == 2) tc_stamp(a, 19);
@@ -783,7 +792,7 @@ k_tc_conv(const __grid_constant__ TcArgs a) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int ps = a.ps;
     const uint32_t slab_bytes = (uint32_t)KC_IN * ps * 16;
-    const uint32_t half_bytes = slab_bytes / NH;
+    const uint32_t chunk_bytes_h = (uint32_t)a.psh * 16;          // one chunk of a slab in global memory
     const uint32_t rank = cluster_ctarank();
     const bool leader_cta = rank == 0;
 
@@ -800,6 +809,18 @@ k_tc_conv(const __grid_constant__ TcArgs a) {
     if (warp == 1) {            // the same warp of both CTAs: accumulators at the same TMEM address in both SMs
         asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(s_tmem)) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    }
+    // the zero positions of the input slabs that exist in shared memory only (tc_psh above): in front of and behind the
+    // run every bulk copy fills, in every chunk of every image buffer; the tensor core reads them (async proxy)
+    {
+        const int front = a.n + 1, back0 = a.n + 1 + a.psh, per_chunk = front + (ps - back0);
+        const int total = a.images_per_group * KC_IN * per_chunk;
+        for (int i = threadIdx.x; i < total; i += TC_THREADS) {
+            const int c = i / per_chunk, k = i - c * per_chunk;
+            const int q = k < front ? k : back0 + (k - front);
+            *reinterpret_cast<uint4*>(sA + ((size_t)c * ps + q) * 16) = make_uint4(0u, 0u, 0u, 0u);
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
     // everything above is private to the pair; what follows reads what the kernel before this one wrote (PDL, common.cuh)
     griddep_wait();
@@ -838,12 +859,17 @@ k_tc_conv(const __grid_constant__ TcArgs a) {
             }
             for (int h = 0; h < NH; h++) {
                 mbar_wait(a_empty + h, (it & 1) ^ 1);
-                if (lane == 0) mbar_expect_tx(a_full + h, half_bytes * __popc(live));
+                if (lane == 0) mbar_expect_tx(a_full + h, 8u * chunk_bytes_h * __popc(live));
                 __syncwarp();
-                if (lane < 8 && ((live >> lane) & 1u)) {
-                    const uint8_t* src = reinterpret_cast<const uint8_t*>(a.in) + (size_t)cur.isl * slab_bytes + (size_t)h * half_bytes;
-                    if (MODE == MODE_DYN) bulk_g2s_hint(sA + (size_t)lane * slab_bytes + (size_t)h * half_bytes, src, half_bytes, a_full + h, pol_stream);
-                    else bulk_g2s(sA + (size_t)lane * slab_bytes + (size_t)h * half_bytes, src, half_bytes, a_full + h);
+                // lane 8 i + kc: chunk kc (eight channels) of this half of image i -- the kept positions of the
+                // chunk are one contiguous run in both memories (tc_psh above)
+                const int img = lane >> 3, kc = h * 8 + (lane & 7);
+                const int isl = __shfl_sync(FULL_MASK, cur.isl, img);
+                if (img < a.images_per_group && ((live >> img) & 1u)) {
+                    const uint8_t* src = reinterpret_cast<const uint8_t*>(a.in) + ((size_t)isl * KC_IN + kc) * chunk_bytes_h;
+                    uint8_t* dst = sA + (size_t)img * slab_bytes + (size_t)kc * ps * 16 + (size_t)(a.n + 1) * 16;
+                    if (MODE == MODE_DYN) bulk_g2s_hint(dst, src, chunk_bytes_h, a_full + h, pol_stream);
+                    else bulk_g2s(dst, src, chunk_bytes_h, a_full + h);
                 }
                 for (int tap = 0; tap < 9; tap++) {
                     mbar_wait(b_empty + s, bph ^ 1);
@@ -1002,7 +1028,7 @@ k_rep_conv1_bf16(const float* __restrict__ obs, const uint32_t* __restrict__ boa
     __shared__ float s_b[64];
     const int item = blockIdx.x;
     if (gate && gate[item] < 0) return;
-    const int np = n * n, pw = n + 2, pp = pw * pw, ps = tc_ps(n);
+    const int np = n * n, pw = n + 2, pp = pw * pw, psh = tc_psh(n);
     for (int i = threadIdx.x; i < 54 * 64; i += C1_THREADS) {
         const int co = i & 63, k = i >> 6;
         s_w[i] = w[co * 54 + k];
@@ -1029,7 +1055,7 @@ k_rep_conv1_bf16(const float* __restrict__ obs, const uint32_t* __restrict__ boa
         s_x[i] = v;
     }
     __syncthreads();
-    uint4* o = reinterpret_cast<uint4*>(out) + (size_t)item * 8 * ps;
+    uint4* o = reinterpret_cast<uint4*>(out) + (size_t)item * 8 * psh;
     for (int i = threadIdx.x; i < 8 * np; i += C1_THREADS) {
         const int kc = i / np, p = i - kc * np;
         const int r = p / n, c = p - r * n;
@@ -1054,7 +1080,7 @@ k_rep_conv1_bf16(const float* __restrict__ obs, const uint32_t* __restrict__ boa
         v.y = pack_bf16(fmaxf(acc[2], 0.f), fmaxf(acc[3], 0.f));
         v.z = pack_bf16(fmaxf(acc[4], 0.f), fmaxf(acc[5], 0.f));
         v.w = pack_bf16(fmaxf(acc[6], 0.f), fmaxf(acc[7], 0.f));
-        o[(size_t)kc * ps + (r + 1) * (n + 1) + c + 1] = v;
+        o[(size_t)kc * psh + r * (n + 1) + c + 1] = v;              // the zeros between the rows are never rewritten
     }
 }
 
@@ -1064,12 +1090,12 @@ __global__ void k_tc_pack(const float* __restrict__ src, long src_stride, __nv_b
     const int item = blockIdx.y;
     const int s = slot ? slot[item] : item;
     if (s < 0) return;
-    const int ps = tc_ps(n), np = n * n, total = (TC_C / 8) * ps;
+    const int psh = tc_psh(n), np = n * n, total = (TC_C / 8) * psh;
     const float* in = src + (size_t)item * src_stride;
     uint4* out = reinterpret_cast<uint4*>(arena) + (size_t)s * total;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
-        const int kc = i / ps, q = i - kc * ps;
-        const int o = q - (n + 2);
+        const int kc = i / psh, q = i - kc * psh;
+        const int o = q - 1;
         float v[8] = {0, 0, 0, 0, 0, 0, 0, 0};
         if (o >= 0) {
             const int r = o / (n + 1), c = o - r * (n + 1);
@@ -1089,14 +1115,14 @@ __global__ void k_tc_unpack(const __nv_bfloat16* __restrict__ arena, const int32
     const int item = blockIdx.y;
     const int s = slot ? slot[item] : item;
     if (s < 0) return;
-    const int ps = tc_ps(n), np = n * n, total = TC_C * np;
-    const __nv_bfloat16* in = arena + (size_t)s * (TC_C / 8) * ps * 8;
+    const int psh = tc_psh(n), np = n * n, total = TC_C * np;
+    const __nv_bfloat16* in = arena + (size_t)s * (TC_C / 8) * psh * 8;
     float* out = dst + (size_t)item * dst_stride;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
         const int ch = i / np, p = i - ch * np;
         const int r = p / n, c = p - r * n;
-        const int q = (r + 1) * (n + 1) + c + 1;
-        out[i] = __bfloat162float(in[((size_t)(ch >> 3) * ps + q) * 8 + (ch & 7)]);
+        const int q = r * (n + 1) + c + 1;
+        out[i] = __bfloat162float(in[((size_t)(ch >> 3) * psh + q) * 8 + (ch & 7)]);
     }
 }
 
@@ -1129,6 +1155,7 @@ int launch_tc_conv(TcArgs& a, int n, int B, cudaStream_t st) {
     a.n = n;
     a.trace = g_tc_trace;
     a.ps = tc_ps(n);
+    a.psh = tc_psh(n);
     a.tiles_per_image = tc_tiles_per_image(n);
     a.images_per_group = tc_images_per_group(n);
     const int kblocks = 9 * CIN / 64;
@@ -1178,7 +1205,7 @@ int mzgo_net_prepare_tc(const mzgo_net_t* net, cudaStream_t st) {
     mzgo_count_launches(5);
     MZGO_LAUNCH_CHECK();
     // the bf16 activation slabs of the representation network rely on zero padding that is never rewritten
-    const size_t slab64 = (size_t)8 * tc_ps(net->n) * 16;
+    const size_t slab64 = (size_t)8 * tc_psh(net->n) * 16;
     MZGO_CUDA(cudaMemsetAsync(ws + w.tc_act1, 0, slab64 * net->max_batch, st));
     MZGO_CUDA(cudaMemsetAsync(ws + w.tc_act2, 0, slab64 * net->max_batch, st));
     HostHeads h;
@@ -1195,7 +1222,7 @@ int mzgo_net_prepare_tc(const mzgo_net_t* net, cudaStream_t st) {
 
 int mzgo_tc_pack_latent(const mzgo_net_t* net, const float* src, long src_stride, void* arena, const int32_t* slot,
                         int B, cudaStream_t st) {
-    dim3 grid(ceil_div((TC_C / 8) * tc_ps(net->n), 256), B);
+    dim3 grid(ceil_div((TC_C / 8) * tc_psh(net->n), 256), B);
     k_tc_pack<<<grid, 256, 0, st>>>(src, src_stride, (__nv_bfloat16*)arena, slot, net->n);
     mzgo_count_launch();
     MZGO_LAUNCH_CHECK();
