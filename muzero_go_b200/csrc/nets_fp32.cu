@@ -247,7 +247,7 @@ NetWorkspace mzgo_net_layout(int n, int C, int precision, int max_batch) {
     w.tc_headw = precision == 1 ? take((3L * C + 56) * 4) : 0;
     w.tc_w2 = precision == 1 ? take(64L * 9 * 64 * 2) : 0;
     w.tc_w3 = precision == 1 ? take(64L * 9 * C * 2) : 0;
-    const long slab64 = 8L * n * (n + 1) * 16;                 // nets_tc.cu: tc_psh positions of 64 bf16 channels
+    const long slab64 = 8L * ((n * (n + 1) - 1 + 7) / 8 * 8) * 16;   // nets_tc.cu: tc_psh positions of 64 bf16 channels
     w.tc_act1 = precision == 1 ? take(slab64 * max_batch) : 0;
     w.tc_act2 = precision == 1 ? take(slab64 * max_batch) : 0;
     w.total = o;
@@ -278,7 +278,7 @@ extern "C" int64_t mzgo_net_workspace_bytes(int n, int C, int precision, int max
 }
 
 extern "C" int64_t mzgo_net_slot_bytes(int n, int C, int precision) {
-    if (precision == 1) return (int64_t)C * ((long)n * (n + 1)) * 2;        // nets_tc.cu: tc_psh positions x C channels, bf16
+    if (precision == 1) return (int64_t)C * (((long)n * (n + 1) - 1 + 7) / 8 * 8) * 2;   // nets_tc.cu: tc_psh positions x C channels, bf16
     return (int64_t)C * n * n * 4;
 }
 

@@ -53,16 +53,20 @@ constexpr int TC_SMEM_LIMIT = 232448;   // 227 KB
 enum { MODE_PLAIN = 0, MODE_HEADS = 1, MODE_DYN = 2 };
 unsigned long long* g_tc_trace = nullptr;
 
-// A latent slab in SHARED memory: [C/8][ps][8] bf16, position q = (n + 2) + r (n + 1) + c of pixel (r, c): rows of n
-// pixels and one zero (the right / left padding of neighbouring rows is the same position), n + 2 zero positions in
-// front (the top padding row and the left padding of row 0) and n + 3 behind -- every shifted view of the nine taps
-// of every accumulator tile stays inside the slab.
-// In GLOBAL memory (the latent arena, the activation buffers) only the positions [n + 1, n + 1 + n (n + 1)) are kept:
-// [C/8][psh][8], psh = n (n + 1), position q - (n + 1).  The zero positions in front of and behind them live in shared
-// memory alone (written once per launch, never overwritten by the bulk copies): 10 % less HBM per slot, which lets one
-// search hold all 2048 19x19 games of a GPU (160 GB of latents) instead of two waves of 1024.
-__host__ __device__ inline int tc_ps(int n) { return (n + 2) * (n + 1) + 2; }
-__host__ __device__ inline int tc_psh(int n) { return n * (n + 1); }
+// A latent slab in SHARED memory: [C/8][ps][8] bf16, position q = q0 + r (n + 1) + c of pixel (r, c): rows of n pixels
+// and one zero (the right / left padding of neighbouring rows is the same position), q0 >= n + 2 zero positions in
+// front (the top padding row and the left padding of row 0) and n + 2 behind the last pixel -- every shifted view of
+// the nine taps of the pixels stays inside the slab.
+// In GLOBAL memory (the latent arena, the activation buffers) only the positions from the first to the last pixel
+// are kept: [C/8][psh][8], position q - q0, tc_plen(n) = n (n + 1) - 1 of the psh in use.  The zero positions in front
+// of and behind them live in shared memory alone (written once per launch, never overwritten by the bulk copies):
+// 9 % less HBM per slot, which lets one search hold all 2048 19x19 games of a GPU (161 GB of latents) instead of two
+// waves of 1024.  q0, ps and psh are multiples of 8 positions (128 B): every chunk of a slab is ONE bulk copy whose
+// source and destination are 128-byte aligned, and a warp of the epilogue stores 512 aligned bytes per chunk.
+__host__ __device__ inline int tc_q0(int n) { return (n + 2 + 7) / 8 * 8; }
+__host__ __device__ inline int tc_plen(int n) { return n * (n + 1) - 1; }
+__host__ __device__ inline int tc_ps(int n) { return (tc_q0(n) + tc_plen(n) + n + 2 + 7) / 8 * 8; }
+__host__ __device__ inline int tc_psh(int n) { return (tc_plen(n) + 7) / 8 * 8; }
 __host__ __device__ inline int tc_tiles_per_image(int n) { return (n * (n + 1) + 127) / 128; }
 // A group (the images that share one pass over the weights) fills at most three of the four TMEM
 // accumulator slots: with a spare slot the MMAs of the next group start while the epilogue still holds
@@ -220,7 +224,7 @@ struct TcArgs {
     float* policy;
     int want_softmax;
     int B;                       // items
-    int n, ps, psh, tiles_per_image, images_per_group, stages;      // ps / psh: positions of a slab in shared / global memory
+    int n, q0, ps, psh, plen, tiles_per_image, images_per_group, stages;    // slab geometry: tc_q0 / tc_ps / tc_psh / tc_plen
     unsigned long long* trace;   // optional (tools/tc_trace.py): [grid][64] globaltimer stamps of the roles
     // mzgo_net_recurrent_tree: items are the games' selected leaves (in_slot / action / out_slot = the tree's
     // leaf records), and once the CTA's roles are through, all of its threads run the tree step of the CTA's
@@ -359,7 +363,7 @@ __device__ __forceinline__ void tc_epilogue_role(const TcArgs& a, const TcCtx& c
     constexpr int KC_OUT = COUT / 8;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int wq = warp & 3, pi = (warp - 2) >> 2;
-    const int n = a.n, psh = a.psh, q0 = n + 2;
+    const int n = a.n, psh = a.psh, plen = a.plen;
     const int tpi = a.tiles_per_image;
     const TcRange rg = tc_range(a);
     // geometry of this thread's row in tile tt of an image (tt < 3 for n <= 19): r | c << 5 | cls << 10 | valid << 14
@@ -423,8 +427,8 @@ __device__ __forceinline__ void tc_epilogue_role(const TcArgs& a, const TcCtx& c
             const uint32_t g = tt == 0 ? geo[0] : (tt == 1 ? geo[1] : geo[2]);
             const int r = g & 31, cc = (g >> 5) & 31, cls = (g >> 10) & 15;
             const bool valid = (g >> 14) & 1u;
-            const int q = tt * 128 + wq * 32 + lane + 1;          // position in the global slab: shared position - (n + 1)
-            const bool store_ok = q < psh;
+            const int q = tt * 128 + wq * 32 + lane;              // position in the global slab: shared position - q0
+            const bool store_ok = q < plen;
             const float* tb = (MODE == MODE_DYN) ? s_tbl + (img * 9 + cls) * COUT : s_tbl;
             const int oslot = __shfl_sync(FULL_MASK, my_osl, img);
             MZGO_DCHECK(oslot >= 0 && img < tc_group_cnt(a, rg.lo, rg.hi, gi) && slot < TC_SLOTS);
@@ -710,7 +714,7 @@ template <int CIN, int COUT>
 __device__ __forceinline__ void tc_mma_role(const TcArgs& a, const TcMmaCtx& mx, const TcItems& first) {
     constexpr int KC_IN = CIN / 8;
     const int lane = threadIdx.x & 31;
-    const int ps = a.ps, q0 = a.n + 2;
+    const int ps = a.ps, q0 = a.q0;
     const int tpi = a.tiles_per_image;
     const uint32_t slab_bytes = (uint32_t)KC_IN * ps * 16;
     TcMmaState st;
@@ -792,7 +796,8 @@ k_tc_conv(const __grid_constant__ TcArgs a) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int ps = a.ps;
     const uint32_t slab_bytes = (uint32_t)KC_IN * ps * 16;
-    const uint32_t chunk_bytes_h = (uint32_t)a.psh * 16;          // one chunk of a slab in global memory
+    const uint32_t chunk_stride_h = (uint32_t)a.psh * 16;         // one chunk of a slab in global memory ...
+    const uint32_t chunk_bytes_h = (uint32_t)a.plen * 16;          // ... and what a bulk copy moves of it
     const uint32_t rank = cluster_ctarank();
     const bool leader_cta = rank == 0;
 
@@ -810,10 +815,10 @@ k_tc_conv(const __grid_constant__ TcArgs a) {
         asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(s_tmem)) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
     }
-    // the zero positions of the input slabs that exist in shared memory only (tc_psh above): in front of and behind the
+    // the zero positions of the input slabs that exist in shared memory only (tc_q0 above): in front of and behind the
     // run every bulk copy fills, in every chunk of every image buffer; the tensor core reads them (async proxy)
     {
-        const int front = a.n + 1, back0 = a.n + 1 + a.psh, per_chunk = front + (ps - back0);
+        const int front = a.q0, back0 = a.q0 + a.plen, per_chunk = front + (ps - back0);
         const int total = a.images_per_group * KC_IN * per_chunk;
         for (int i = threadIdx.x; i < total; i += TC_THREADS) {
             const int c = i / per_chunk, k = i - c * per_chunk;
@@ -862,12 +867,12 @@ k_tc_conv(const __grid_constant__ TcArgs a) {
                 if (lane == 0) mbar_expect_tx(a_full + h, 8u * chunk_bytes_h * __popc(live));
                 __syncwarp();
                 // lane 8 i + kc: chunk kc (eight channels) of this half of image i -- the kept positions of the
-                // chunk are one contiguous run in both memories (tc_psh above)
+                // chunk are one contiguous run in both memories (tc_plen above)
                 const int img = lane >> 3, kc = h * 8 + (lane & 7);
                 const int isl = __shfl_sync(FULL_MASK, cur.isl, img);
                 if (img < a.images_per_group && ((live >> img) & 1u)) {
-                    const uint8_t* src = reinterpret_cast<const uint8_t*>(a.in) + ((size_t)isl * KC_IN + kc) * chunk_bytes_h;
-                    uint8_t* dst = sA + (size_t)img * slab_bytes + (size_t)kc * ps * 16 + (size_t)(a.n + 1) * 16;
+                    const uint8_t* src = reinterpret_cast<const uint8_t*>(a.in) + ((size_t)isl * KC_IN + kc) * chunk_stride_h;
+                    uint8_t* dst = sA + (size_t)img * slab_bytes + (size_t)kc * ps * 16 + (size_t)a.q0 * 16;
                     if (MODE == MODE_DYN) bulk_g2s_hint(dst, src, chunk_bytes_h, a_full + h, pol_stream);
                     else bulk_g2s(dst, src, chunk_bytes_h, a_full + h);
                 }
@@ -1080,7 +1085,7 @@ k_rep_conv1_bf16(const float* __restrict__ obs, const uint32_t* __restrict__ boa
         v.y = pack_bf16(fmaxf(acc[2], 0.f), fmaxf(acc[3], 0.f));
         v.z = pack_bf16(fmaxf(acc[4], 0.f), fmaxf(acc[5], 0.f));
         v.w = pack_bf16(fmaxf(acc[6], 0.f), fmaxf(acc[7], 0.f));
-        o[(size_t)kc * psh + r * (n + 1) + c + 1] = v;              // the zeros between the rows are never rewritten
+        o[(size_t)kc * psh + r * (n + 1) + c] = v;                  // the zeros between the rows are never rewritten
     }
 }
 
@@ -1095,7 +1100,7 @@ __global__ void k_tc_pack(const float* __restrict__ src, long src_stride, __nv_b
     uint4* out = reinterpret_cast<uint4*>(arena) + (size_t)s * total;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
         const int kc = i / psh, q = i - kc * psh;
-        const int o = q - 1;
+        const int o = q;
         float v[8] = {0, 0, 0, 0, 0, 0, 0, 0};
         if (o >= 0) {
             const int r = o / (n + 1), c = o - r * (n + 1);
@@ -1121,7 +1126,7 @@ __global__ void k_tc_unpack(const __nv_bfloat16* __restrict__ arena, const int32
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
         const int ch = i / np, p = i - ch * np;
         const int r = p / n, c = p - r * n;
-        const int q = r * (n + 1) + c + 1;
+        const int q = r * (n + 1) + c;
         out[i] = __bfloat162float(in[((size_t)(ch >> 3) * psh + q) * 8 + (ch & 7)]);
     }
 }
@@ -1154,8 +1159,10 @@ int launch_tc_conv(TcArgs& a, int n, int B, cudaStream_t st) {
     a.B = B;
     a.n = n;
     a.trace = g_tc_trace;
+    a.q0 = tc_q0(n);
     a.ps = tc_ps(n);
     a.psh = tc_psh(n);
+    a.plen = tc_plen(n);
     a.tiles_per_image = tc_tiles_per_image(n);
     a.images_per_group = tc_images_per_group(n);
     const int kblocks = 9 * CIN / 64;

@@ -43,7 +43,7 @@ def test_argument_errors_do_not_need_a_gpu():
     assert b"NULL" in lib.mzgo_last_error()
     assert lib.mzgo_rules_reset(1, 4, 40, None) == -1
     assert lib.mzgo_net_slot_bytes(19, 128, 0) == 128 * 361 * 4
-    assert lib.mzgo_net_slot_bytes(19, 128, 1) == 128 * (19 * 20) * 2
+    assert lib.mzgo_net_slot_bytes(19, 128, 1) == 128 * 384 * 2          # 19 * 20 - 1 positions, rounded up to 128 B
 
 
 @pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-GPU behaviour")
