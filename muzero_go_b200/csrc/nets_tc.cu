@@ -32,6 +32,7 @@
 // instructions per tcgen05.mma) / relay in the other CTA (tells the leader's barriers that this CTA's operands have
 // landed), warps 2-9 epilogue (tcgen05.ld -> bias/ReLU -> heads with the 1x1 weights read as
 // kernel-parameter constants -> bf16 -> coalesced 16 B stores in the arena layout).
+#include <cuda.h>
 #include <cuda_bf16.h>
 
 #include <algorithm>
@@ -133,6 +134,21 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
 // (the next reader of a child latent is a later simulation, after > 200 MB of other traffic), while the tree
 // kernels re-read the same root rows every simulation: latents go through with evict_first so that the
 // trees' working set (about 20 MB per 1024 games) and the weights stay resident in the 126 MB L2.
+// One half of an input slab (eight chunks of eight channels, all ps positions) as ONE tensor copy: box
+// [8 positions x 8 channels = 128 B][ps / 8][8 chunks] of the map built by tc_make_in_map below; the positions in front
+// of and behind the kept run are out of bounds there and arrive as zeros.  c1 = first position / 8 (negative), c2 =
+// first chunk.
+__device__ __forceinline__ void tensor_g2s_3d(void* dst, const CUtensorMap* map, int c1, int c2, uint64_t* bar, uint64_t policy) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%2, %3, %4}], [%5], %6;"
+        ::"r"(smem_u32(dst)), "l"(map), "r"(0), "r"(c1), "r"(c2), "r"(smem_u32(bar)), "l"(policy)
+        : "memory");
+}
+__device__ __forceinline__ uint64_t l2_policy_evict_normal() {
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_normal.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
 __device__ __forceinline__ uint64_t l2_policy_evict_first() {
     uint64_t p;
     asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
@@ -212,6 +228,7 @@ struct TcScalars {   // the scalar head parameters (main.py:93-94, :111-114), ho
 };
 
 struct TcArgs {
+    CUtensorMap in_map;          // the input slabs as a tensor [chunk][position / 8][128 B] (tc_make_in_map)
     const __nv_bfloat16* in;     // input slabs: item i at in + in_slot(i) * (CIN/8)*psh*8
     __nv_bfloat16* out;          // output slabs: item i at out + out_slot(i) * (COUT/8)*psh*8
     const int32_t* in_slot;      // optional (identity when NULL)
@@ -796,8 +813,7 @@ k_tc_conv(const __grid_constant__ TcArgs a) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int ps = a.ps;
     const uint32_t slab_bytes = (uint32_t)KC_IN * ps * 16;
-    const uint32_t chunk_stride_h = (uint32_t)a.psh * 16;         // one chunk of a slab in global memory ...
-    const uint32_t chunk_bytes_h = (uint32_t)a.plen * 16;          // ... and what a bulk copy moves of it
+    const uint32_t half_bytes = slab_bytes / NH;                  // 64 channels of a slab in shared memory: one tensor copy
     const uint32_t rank = cluster_ctarank();
     const bool leader_cta = rank == 0;
 
@@ -815,18 +831,7 @@ k_tc_conv(const __grid_constant__ TcArgs a) {
         asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(s_tmem)) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
     }
-    // the zero positions of the input slabs that exist in shared memory only (tc_q0 above): in front of and behind the
-    // run every bulk copy fills, in every chunk of every image buffer; the tensor core reads them (async proxy)
-    {
-        const int front = a.q0, back0 = a.q0 + a.plen, per_chunk = front + (ps - back0);
-        const int total = a.images_per_group * KC_IN * per_chunk;
-        for (int i = threadIdx.x; i < total; i += TC_THREADS) {
-            const int c = i / per_chunk, k = i - c * per_chunk;
-            const int q = k < front ? k : back0 + (k - front);
-            *reinterpret_cast<uint4*>(sA + ((size_t)c * ps + q) * 16) = make_uint4(0u, 0u, 0u, 0u);
-        }
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    }
+    if (threadIdx.x == 0) asm volatile("prefetch.tensormap [%0];" ::"l"(&a.in_map) : "memory");     // the map is a kernel parameter: no dependency
     // everything above is private to the pair; what follows reads what the kernel before this one wrote (PDL, common.cuh)
     griddep_wait();
     griddep_launch();
@@ -844,7 +849,7 @@ k_tc_conv(const __grid_constant__ TcArgs a) {
         // ===================================================== TMA producer (lane 0 issues, the warp stays converged)
         // own images' slabs and bias tables, and THIS CTA's half (output channels [rank*COUT/2, ...)) of every k-block
         uint32_t it = 0, s = 0, bph = 0;
-        const uint64_t pol_stream = l2_policy_evict_first(), pol_keep = l2_policy_evict_last();
+        const uint64_t pol_stream = l2_policy_evict_first(), pol_keep = l2_policy_evict_last(), pol_normal = l2_policy_evict_normal();
         const uint8_t* w_half = reinterpret_cast<const uint8_t*>(a.wB) + (size_t)rank * STAGE_BYTES;
         TcItems nx = first;
         for (int gi = 0; gi < rg.ngroups; gi++) {
@@ -864,18 +869,12 @@ k_tc_conv(const __grid_constant__ TcArgs a) {
             }
             for (int h = 0; h < NH; h++) {
                 mbar_wait(a_empty + h, (it & 1) ^ 1);
-                if (lane == 0) mbar_expect_tx(a_full + h, 8u * chunk_bytes_h * __popc(live));
+                if (lane == 0) mbar_expect_tx(a_full + h, half_bytes * __popc(live));
                 __syncwarp();
-                // lane 8 i + kc: chunk kc (eight channels) of this half of image i -- the kept positions of the
-                // chunk are one contiguous run in both memories (tc_plen above)
-                const int img = lane >> 3, kc = h * 8 + (lane & 7);
-                const int isl = __shfl_sync(FULL_MASK, cur.isl, img);
-                if (img < a.images_per_group && ((live >> img) & 1u)) {
-                    const uint8_t* src = reinterpret_cast<const uint8_t*>(a.in) + ((size_t)isl * KC_IN + kc) * chunk_stride_h;
-                    uint8_t* dst = sA + (size_t)img * slab_bytes + (size_t)kc * ps * 16 + (size_t)a.q0 * 16;
-                    if (MODE == MODE_DYN) bulk_g2s_hint(dst, src, chunk_bytes_h, a_full + h, pol_stream);
-                    else bulk_g2s(dst, src, chunk_bytes_h, a_full + h);
-                }
+                // one tensor copy per image and half: the kept positions from global memory, zeros around them
+                if (lane < 8 && ((live >> lane) & 1u))
+                    tensor_g2s_3d(sA + (size_t)lane * slab_bytes + (size_t)h * half_bytes, &a.in_map, -(a.q0 >> 3),
+                                  cur.isl * KC_IN + h * 8, a_full + h, MODE == MODE_DYN ? pol_stream : pol_normal);
                 for (int tap = 0; tap < 9; tap++) {
                     mbar_wait(b_empty + s, bph ^ 1);
                     if (lane == 0) {
@@ -1149,6 +1148,40 @@ int num_sms() {
     return n;
 }
 
+// The input slabs of a launch as a rank-3 tensor map over global memory: [chunk][position / 8][8 positions x 8 channels]
+// with tc_psh(n) / 8 rows of 128 B per chunk (stride tc_psh(n) * 16 B between chunks) and a box of eight
+// chunks x ALL tc_ps(n) shared-memory positions starting tc_q0(n) positions in front of the first kept one: what lies
+// outside [0, tc_psh(n)) is out of bounds and is filled with zeros by the copy engine.  (The positions between
+// tc_plen(n) and tc_psh(n) are in bounds: they are zero in memory because nothing ever writes them.)  The chunk
+// dimension is unbounded (the library does not know how many slots the caller's arena has).
+typedef CUresult (*TcEncodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+int tc_make_in_map(CUtensorMap* map, const void* base, int n) {
+    static TcEncodeTiled encode = nullptr;
+    static std::mutex mu;
+    {
+        std::lock_guard<std::mutex> lk(mu);
+        if (!encode) {
+            void* fn = nullptr;
+            cudaDriverEntryPointQueryResult q;
+            MZGO_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q));
+            MZGO_CHECK_ARG(fn != nullptr && q == cudaDriverEntryPointSuccess, "cuTensorMapEncodeTiled is not available in this driver");
+            encode = (TcEncodeTiled)fn;
+        }
+    }
+    MZGO_CHECK_ARG(((uintptr_t)base & 15u) == 0, "latent slabs must be 16-byte aligned");
+    const cuuint64_t dims[3] = {64, (cuuint64_t)tc_psh(n) / 8, 1ull << 31};
+    const cuuint64_t strides[2] = {128, (cuuint64_t)tc_psh(n) * 16};
+    const cuuint32_t box[3] = {64, (cuuint32_t)tc_ps(n) / 8, 8};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    const CUresult r = encode(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
+                              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    MZGO_CHECK_ARG(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with %d (n=%d)", (int)r, n);
+    return MZGO_OK;
+}
+
 template <int CIN, int COUT, int MODE>
 int launch_tc_conv(TcArgs& a, int n, int B, cudaStream_t st) {
     static bool attr_set = false;
@@ -1159,6 +1192,7 @@ int launch_tc_conv(TcArgs& a, int n, int B, cudaStream_t st) {
     a.B = B;
     a.n = n;
     a.trace = g_tc_trace;
+    if (int e = tc_make_in_map(&a.in_map, a.in, n)) return e;
     a.q0 = tc_q0(n);
     a.ps = tc_ps(n);
     a.psh = tc_psh(n);
