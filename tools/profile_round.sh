@@ -4,7 +4,7 @@
 # Outputs land in gpurun_out/r02/; tools/summarise_ncu.py turns them into the tracked files under profiles/r02/.
 O=gpurun_out/r02
 mkdir -p $O
-C19="python bench.py --workload 19x19 --games 1024 --sims 100 --steps 1 --warmup 3 --no-cpu-baseline --no-secondary"
+C19="python bench.py --workload 19x19 --games 2048 --sims 100 --steps 1 --warmup 3 --no-cpu-baseline --no-secondary"
 C9="python bench.py --workload 9x9 --steps 2 --warmup 3 --no-cpu-baseline"
 # launch lists (per-launch times under ncu are cold-cache and serialised: compare SHARES)
 $C19 > $O/plain_19.log 2>&1 &&
