@@ -200,8 +200,12 @@ int mzgo_tree_choose_action(const mzgo_tree_t* tree, const mzgo_search_params_t*
  *
  * Latent arena: `slots` of one latent each, addressed by int32 slot indices.
  *   precision 0 (fp32 mode): slot = float32 [C][n*n]          (NCHW, the reference layout)
- *   precision 1 (bf16 mode): slot = bf16 [C/8][PS][8], PS = (n+2)(n+1)+2 zero-padded flat
- *                            positions (row stride n+1), see DESIGN.md "latent arena".
+ *   precision 1 (bf16 mode): slot = bf16 [C/8][PSH][8]: the n(n+1)-1 flat positions r(n+1)+c from the first to the
+ *                            last pixel (row stride n+1: one zero between two rows), PSH = that count rounded up to
+ *                            a multiple of 8; the padding around them exists in shared memory only (DESIGN.md
+ *                            "latent arena").  The arena must start out ZEROED (the zeros between the rows and
+ *                            behind the last pixel are never rewritten) and be 16-byte aligned; use
+ *                            mzgo_net_slot_bytes, mzgo_net_import_latent / _export_latent rather than the layout.
  * ------------------------------------------------------------------------------------------ */
 typedef struct mzgo_net {
     int32_t n;          /* board size */

@@ -218,3 +218,50 @@ def test_random_batches_match_torch_oracle(n, c, precision, tol):
         assert max(ulps.values()) <= 1.0, ulps
     record_errors(f"random_batches/{precision}_N{n}_C{c}", rec)
     assert max(errs.values()) < tol, errs
+
+
+@pytest.mark.parametrize("n", [5, 9, 13, 19])
+def test_bf16_slot_layout_is_the_documented_one(n):
+    """include/mzgo.h, bf16 mode: a slot is bf16 [C/8][PSH][8], pixel (r, c) at flat position r (n + 1) + c, PSH =
+    n (n + 1) - 1 rounded up to a multiple of 8, everything that is not a pixel ZERO -- in slots written by the
+    import entry point, by the initial inference and by the recurrent kernel's epilogue alike (the network kernels
+    rely on those zeros: the padding around them is generated on the way into shared memory)."""
+    import muzero_go_b200 as mz
+    from muzero_go_b200 import _lib
+    C, A, B = 128, n * n + 1, 5
+    plen = n * (n + 1) - 1
+    psh = (plen + 7) // 8 * 8
+    torch.manual_seed(n)
+    net = mz.MuZeroNet(C, A, precision="bf16").cuda().eval()
+    assert net.slot_bytes() == C * psh * 2
+    L, s = _lib.load(), _lib.stream_ptr()
+    d = net.descriptor(B)
+    arena = net.new_arena(3 * B)
+    slots = torch.arange(B, dtype=torch.int32, device="cuda")
+    latent = torch.randn(B, C, n, n, device="cuda").relu() + 0.25          # no pixel is zero
+    obs = (torch.rand(B, 6, n, n, device="cuda") < 0.3).float()
+    value, policy = torch.empty(B, 1, device="cuda"), torch.empty(B, A, device="cuda")
+    reward = torch.empty(B, 1, device="cuda")
+    action = torch.randint(0, A, (B,), dtype=torch.int32, device="cuda")
+    _lib.check(L.mzgo_net_import_latent(d, _lib.ptr(arena), _lib.ptr(slots), _lib.ptr(latent), B, s))
+    _lib.check(L.mzgo_net_initial(d, _lib.ptr(obs), None, _lib.ptr(arena), _lib.ptr(slots + B), _lib.ptr(value),
+                                  _lib.ptr(policy), 0, B, s))
+    _lib.check(L.mzgo_net_recurrent(d, _lib.ptr(arena), _lib.ptr(slots), _lib.ptr(action), _lib.ptr(slots + 2 * B),
+                                    _lib.ptr(reward), _lib.ptr(value), _lib.ptr(policy), 0, B, s))
+    torch.cuda.synchronize()
+    raw = arena.view(torch.bfloat16).view(3 * B, C // 8, psh, 8).float()
+    pixel = torch.zeros(psh, dtype=torch.bool, device="cuda")
+    rr, cc = torch.meshgrid(torch.arange(n, device="cuda"), torch.arange(n, device="cuda"), indexing="ij")
+    pixel[(rr * (n + 1) + cc).reshape(-1)] = True
+    assert int(pixel.sum()) == n * n and not pixel[plen:].any()
+    for which, lo in (("import", 0), ("initial inference", B), ("recurrent inference", 2 * B)):
+        blob = raw[lo:lo + B]
+        assert not blob[:, :, ~pixel, :].any(), f"{which}: a non-pixel position of a slot is not zero"
+        out = torch.empty(B, C, n, n, device="cuda")
+        _lib.check(L.mzgo_net_export_latent(d, _lib.ptr(arena), _lib.ptr(slots + lo), _lib.ptr(out), B, s))
+        torch.cuda.synchronize()
+        # [B][C/8][n*n][8] -> [B][C][n][n]
+        got = blob[:, :, pixel, :].permute(0, 1, 3, 2).reshape(B, C, n, n)
+        assert torch.equal(got, out), f"{which}: the pixels are not where the header says"
+    assert torch.equal(raw[:B][:, :, pixel, :].permute(0, 1, 3, 2).reshape(B, C, n, n), latent.bfloat16().float())
+    assert raw[B:].abs().sum() > 0
