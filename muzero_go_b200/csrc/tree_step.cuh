@@ -134,6 +134,29 @@ __device__ __forceinline__ int step_level(StepShared<TPG>& sh, int sub, int tid,
     // the range of q over the live edges (min-max normalisation set = prior > 0, main.py:328-339); a warp that holds
     // an unexpanded edge knows that the level ends in a draw and skips it
     unsigned long long kmin = dkey(INFINITY), kmax = dkey(-INFINITY);
+    if (WPG == 1 && mine == 0u) {
+        // A node with ONE live edge, already visited (late positions of small boards: only the pass is legal, and the
+        // tree is a chain as deep as the number of simulations): PUCT over one candidate picks it whenever its score
+        // is a number above -inf, i.e. whenever its statistics are finite -- no division, no normalisation, no argmax.
+        uint32_t lb[STEP_EPT];
+        int live_n = 0;
+#pragma unroll
+        for (int e = 0; e < STEP_EPT; e++) { lb[e] = __ballot_sync(FULL_MASK, (pos >> e) & 1u); live_n += __popc(lb[e]); }
+        if (live_n == 1) {
+            const int e_o = lb[0] ? 0 : (lb[1] ? 1 : 2);
+            const int lane_o = __ffs(lb[0] | lb[1] | lb[2]) - 1;
+            const int nv_o = __shfl_sync(FULL_MASK, e_o == 0 ? nv[0] : e_o == 1 ? nv[1] : nv[2], lane_o);
+            const int ch_o = __shfl_sync(FULL_MASK, e_o == 0 ? ch[0] : e_o == 1 ? ch[1] : ch[2], lane_o);
+            const double vs_o = __shfl_sync(FULL_MASK, e_o == 0 ? vs[0] : e_o == 1 ? vs[1] : vs[2], lane_o);
+            const double cp_o = __shfl_sync(FULL_MASK, e_o == 0 ? cp[0] : e_o == 1 ? cp[1] : cp[2], lane_o);
+            if (fabs(vs_o) < INFINITY && fabs(cp_o) < INFINITY && fabs(sq) < INFINITY) {
+                *out_a = e_o * TPG + lane_o;
+                *out_n = nv_o;
+                *out_c = ch_o;
+                return 1;
+            }
+        }
+    }
     if (mine == 0u) {
         if (!have_terms) level_terms<TPG>(nv, cp, vs, pos, sq, q, u);
         double qmin = INFINITY, qmax = -INFINITY;
