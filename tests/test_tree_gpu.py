@@ -184,3 +184,49 @@ def test_fast_division_is_correctly_rounded():
     _lib.require_device()
     for seed in (1, 2):
         assert lib.mzgo_debug_fastdiv_check(seed, 1024, 256) == 0
+
+
+@pytest.mark.parametrize("n,live_points", [(5, 0), (9, 0), (9, 1), (13, 0), (19, 0)])
+@pytest.mark.parametrize("driver", DRIVERS)
+def test_chains_of_single_live_edges_match_the_oracle(n, live_points, driver):
+    """Late positions: only the pass (live_points = 0) or the pass and one point are legal, so every node of the tree
+    has one or two live edges and the tree is a chain about as deep as the number of simulations.  The warp-per-game
+    step walks a node whose single live edge is visited without the PUCT arithmetic (tree_step.cuh): depths, visit
+    counts and value sums must still be those of the reference's loop, bit for bit."""
+    import muzero_go_b200 as mz
+    from oracle.make_golden import midgame_obs
+    A, sims, G = n * n + 1, 64, 3
+    rng = np.random.default_rng(77 + n + live_points)
+    cfg = mz.SearchConfig(c_puct=2.0, discount=0.99, dirichlet_epsilon=0.25, pass_epsilon=0.05, variant="main")
+    obs, init_soft, soft, rew, val, noise, streams, trees = [], [], [], [], [], [], [], []
+    for k in range(G):
+        o = midgame_obs(n, plies=n * n // 2, seed=int(rng.integers(1 << 30))).copy()
+        o[3] = 1                                              # no board point is legal ...
+        for p in rng.choice(n * n, size=live_points, replace=False):
+            o[3].flat[int(p)] = 0                             # ... but these
+        obs.append(o)
+        init_soft.append(torch.softmax(torch.from_numpy(rng.normal(0, 1.5, A).astype(np.float32)).view(1, -1), dim=1).numpy()[0])
+        soft.append(torch.softmax(torch.from_numpy(rng.normal(0, 2.0, (sims, A)).astype(np.float32)), dim=1).numpy())
+        rew.append(rng.normal(0, 0.1, sims).astype(np.float32))
+        val.append(rng.normal(0, 0.5, sims).astype(np.float32))
+        noise.append(rng.dirichlet([0.3] * A))
+        streams.append(rng.integers(0, 2 ** 32, size=sims + 8, dtype=np.uint64).astype(np.uint32))
+        calls = [0]
+
+        def recurrent(latent, action, k=k, calls=calls):
+            i = calls[0]
+            calls[0] += 1
+            return None, rew[k][i], val[k][i], soft[k][i]
+        trees.append(mcts_ref.run_mcts(o, lambda ob, k=k: (None, np.float32(0), init_soft[k]), recurrent, sims, noise[k],
+                                       streams[k], c_puct=2.0, discount=0.99, dirichlet_epsilon=0.25, pass_epsilon=0.05))
+    tree, depths = run_gpu_search(n, obs, init_soft, soft, rew, val, noise, streams, sims, cfg, driver)
+    if live_points == 0:
+        assert all(max(d) >= sims - 2 for d in depths), [max(d) for d in depths]     # one node per level
+    vc = tree.visit_counts().cpu().numpy()
+    for k, (t, mask) in enumerate(trees):
+        assert int(mask.sum() > 0) and int((mask > 0).sum()) == live_points + 1
+        assert depths[k] == t.depths, f"game {k}"
+        assert np.array_equal(vc[k], t.root_visit_counts(mask)), f"game {k}"
+        assert np.array_equal(tree.edge_vsum[k, 0].cpu().numpy(), t.root_child_value_sums())
+        assert int(tree.root_visit[k]) == t.visit[0] and int(tree.dropped[k]) == t.dropped
+        assert int(tree.n_nodes[k]) == len(t.visit)
