@@ -17,12 +17,13 @@ dev = torch.device("cuda")
 torch.manual_seed(0)
 net = mz.MuZeroNet(128, n * n + 1, precision="bf16").to(dev).eval()
 L = _lib.load()
+MOVES = int(os.environ.get("PROBE_MOVES", "2"))      # moves played before the probed search
 for mixed in (False, True):
-    group = mz.WaveGroup(net, n, G, S, waves=1, search=mz.SearchConfig(seed=1000), traj_capacity=2)
+    group = mz.WaveGroup(net, n, G, S, waves=1, search=mz.SearchConfig(seed=1000), traj_capacity=max(2, MOVES))
     if mixed:
         bench.advance_games(mz, torch, group, n, seed=77)
     e = group.engines[0]
-    group.run(2)
+    group.run(MOVES)
     torch.cuda.synchronize()
     d = e.descriptor()
     s = _lib.stream_ptr()
