@@ -368,7 +368,9 @@ k_tree_expand_backup(mzgo_tree_t t, mzgo_search_params_t p, const float* __restr
 //      sums, child links); the root statistics this very step changes (one edge of the backup path, the child link
 //      when the leaf hangs off the root) are patched in registers.  Behind the engine's own network kernel this batch
 //      and the next are issued BEFORE the grid-dependency wait (the blocks are resident while that kernel drains);
-//   2. the statistics of the path edges to back up (needed by the backup's stores only);
+//   2. the statistics of the path edges to back up (needed by the backup's stores only); in front of the wait too:
+//      the step's random number, the edge terms of the root level (all edges but the one the backup changes) and
+//      every store that needs no network output (the new node's empty statistics, visit counts, links, counters);
 //   3. behind the wait: the network outputs of the leaf (value, reward, softmax);
 //   4. one batch per level below the root (visits, priors, value sums and child links together).
 // (the step itself lives in tree_step.cuh: the network kernel of nets_tc.cu runs the same code as a warp-group role)
