@@ -44,6 +44,11 @@ def test_argument_errors_do_not_need_a_gpu():
     assert lib.mzgo_rules_reset(1, 4, 40, None) == -1
     assert lib.mzgo_net_slot_bytes(19, 128, 0) == 128 * 361 * 4
     assert lib.mzgo_net_slot_bytes(19, 128, 1) == 128 * 384 * 2          # 19 * 20 - 1 positions, rounded up to 128 B
+    for n in (2, 5, 6, 9, 13, 19):                                        # include/mzgo.h: PSH = n (n + 1) - 1, rounded up to 8
+        assert lib.mzgo_net_slot_bytes(n, 128, 1) == 128 * ((n * (n + 1) - 1 + 7) // 8 * 8) * 2
+        assert lib.mzgo_net_slot_bytes(n, 128, 0) == 128 * n * n * 4
+    # one search of BASELINE configs[3] (2048 games x 801 slots) fits a B200 beside its trees: DESIGN.md section 3
+    assert 2048 * 801 * (lib.mzgo_net_slot_bytes(19, 128, 1) + 362 * 18) < 0.92 * 190e9
 
 
 @pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-GPU behaviour")
